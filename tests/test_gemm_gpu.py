@@ -1,0 +1,184 @@
+"""tcgen05 GEMM / implicit-GEMM kernel vs a plain torch fp32 reference of the same op."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def L():
+    import vda_b200.lib as lib
+
+    lib.init()
+    return lib
+
+
+def _rand(*shape, scale=1.0, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).cuda()
+
+
+def _close(got, want, tol=2e-2):
+    got, want = got.float(), want.float()
+    err = (got - want).abs().max().item()
+    ref = want.abs().max().item()
+    assert err <= tol * max(ref, 1e-6), f"max abs err {err} vs ref max {ref}"
+
+
+@pytest.mark.parametrize("M,N,K,bn", [
+    (128, 256, 64, 256), (256, 256, 128, 0), (300, 384, 592, 0), (1000, 64, 1024, 64),
+    (1370, 1024, 1024, 128), (129, 32, 64, 32), (4096, 3072, 1024, 256), (777, 48, 256, 0),
+])
+def test_gemm_plain_bias(L, M, N, K, bn):
+    a = _rand(M, K, seed=1).bfloat16()
+    w = _rand(N, K, scale=K ** -0.5, seed=2).bfloat16()
+    b = _rand(N, seed=3)
+    out = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
+    L.gemm(a, w, L.make_epilogue(bias=b, out=out, ldo=N, block_n=bn))
+    torch.cuda.synchronize()
+    _close(out, a.float() @ w.float().T + b)
+
+
+def test_gemm_gelu_scale_residual_inplace(L):
+    M, N, K = 1370 * 2, 384, 1536
+    a = _rand(M, K, seed=1).bfloat16()
+    w = _rand(N, K, scale=K ** -0.5, seed=2).bfloat16()
+    b, g = _rand(N, seed=3), _rand(N, seed=4)
+    x = _rand(M, N, seed=5)
+    want = x + g * (a.float() @ w.float().T + b)
+    L.gemm(a, w, L.make_epilogue(bias=b, scale=g, res_f32=x, out_f32=x, ldo=N))
+    torch.cuda.synchronize()
+    _close(x, want, 1e-3)
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    L.gemm(a, w, L.make_epilogue(bias=b, out=out, ldo=N, act=L.ACT_GELU))
+    _close(out, F.gelu(a.float() @ w.float().T + b))
+
+
+def test_gemm_bf16_residuals_and_relu_copy(L):
+    M, N, K = 999, 256, 256
+    a = _rand(M, K, seed=1).bfloat16()
+    w = _rand(N, K, scale=K ** -0.5, seed=2).bfloat16()
+    b = _rand(N, seed=3)
+    r1, r2 = _rand(M, N, seed=4).bfloat16(), _rand(M, N, seed=5).bfloat16()
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    out_relu = torch.empty_like(out)
+    L.gemm(a, w, L.make_epilogue(bias=b, res1=r1, res2=r2, out=out, out_relu=out_relu, ldo=N))
+    want = a.float() @ w.float().T + b + r1.float() + r2.float()
+    _close(out, want)
+    _close(out_relu, want.relu())
+
+
+def test_gemm_geglu(L):
+    M, C = 1500, 256
+    a = _rand(M, C, seed=1).bfloat16()
+    w = _rand(8 * C, C, scale=C ** -0.5, seed=2).bfloat16()
+    b = _rand(8 * C, seed=3)
+    want = a.float() @ w.float().T + b
+    want = want[:, :4 * C] * F.gelu(want[:, 4 * C:])
+    # interleave value/gate rows in groups of 16 (what the weight repack does)
+    idx = torch.arange(8 * C, device="cuda").view(2, 4 * C // 16, 16).permute(1, 0, 2).reshape(-1)
+    out = torch.empty(M, 4 * C, device="cuda", dtype=torch.bfloat16)
+    L.gemm(a, w[idx].contiguous(), L.make_epilogue(bias=b[idx].contiguous(), out=out, ldo=4 * C, act=L.ACT_GEGLU))
+    _close(out, want)
+
+
+@pytest.mark.parametrize("s,cin,cout,h,w", [(4, 64, 48, 5, 7), (2, 128, 96, 9, 4), (4, 256, 256, 37, 37)])
+def test_gemm_convtranspose_store(L, s, cin, cout, h, w):
+    n = 3
+    x = _rand(n, cin, h, w, seed=1).bfloat16()
+    wt = _rand(cin, cout, s, s, scale=cin ** -0.5, seed=2).bfloat16()
+    b = _rand(cout, seed=3)
+    want = F.conv_transpose2d(x.float(), wt.float(), b, stride=s)  # [n,cout,h*s,w*s]
+    cp = (cout + 15) // 16 * 16
+    wk = torch.zeros(s, s, cp, cin, device="cuda", dtype=torch.bfloat16)
+    wk[:, :, :cout] = wt.permute(2, 3, 1, 0)
+    bk = torch.zeros(s, s, cp, device="cuda")
+    bk[:, :, :cout] = b
+    a = x.permute(0, 2, 3, 1).reshape(n * h * w, cin).contiguous()
+    out = torch.zeros(n, h * s, w * s, cp, device="cuda", dtype=torch.bfloat16)
+    L.gemm(a, wk.view(-1, cin), L.make_epilogue(bias=bk.view(-1), out=out, ldo=cp, store_mode=L.ST_CONVT,
+                                                 ct=(s, cp, h, w)))
+    _close(out[..., :cout].permute(0, 3, 1, 2), want)
+    assert out[..., cout:].abs().max().item() == 0 if cp > cout else True
+
+
+def test_gemm_qkv_store(L):
+    frames, S, heads = 3, 197, 6
+    D = heads * 64
+    spad = (S + 7) // 8 * 8
+    a = _rand(frames * S, D, seed=1).bfloat16()
+    w = _rand(3 * D, D, scale=D ** -0.5, seed=2).bfloat16()
+    b = _rand(3 * D, seed=3)
+    qk = torch.empty(frames * S, 2 * D, device="cuda", dtype=torch.bfloat16)
+    vt = torch.zeros(frames * heads, 64, spad, device="cuda", dtype=torch.bfloat16)
+    L.gemm(a, w, L.make_epilogue(bias=b, out=qk, ldo=2 * D, store_mode=L.ST_QKV, qkv=(vt, D, heads, S, spad)))
+    want = a.float() @ w.float().T + b
+    _close(qk, want[:, :2 * D])
+    v = want[:, 2 * D:].view(frames, S, heads, 64).permute(0, 2, 3, 1).reshape(frames * heads, 64, S)
+    _close(vt[:, :, :S], v)
+    assert vt[:, :, S:].abs().max().item() == 0
+
+
+@pytest.mark.parametrize("n,H,W,C,Cout", [(2, 19, 19, 64, 64), (1, 37, 37, 128, 256), (3, 8, 50, 64, 32),
+                                          (2, 74, 74, 256, 256), (1, 5, 200, 192, 48)])
+def test_conv3x3(L, n, H, W, C, Cout):
+    x = _rand(n, C, H, W, seed=1).bfloat16()
+    wt = _rand(Cout, C, 3, 3, scale=(9 * C) ** -0.5, seed=2).bfloat16()
+    b = _rand(Cout, seed=3)
+    r1 = _rand(n, H, W, Cout, seed=4).bfloat16()
+    want = F.conv2d(x.float(), wt.float(), b, padding=1).permute(0, 2, 3, 1) + r1.float()
+    xn = x.permute(0, 2, 3, 1).contiguous()
+    wk = wt.permute(0, 2, 3, 1).reshape(Cout, 9 * C).contiguous()
+    out = torch.full((n, H, W, Cout), float("nan"), device="cuda", dtype=torch.bfloat16)
+    out_relu = torch.empty_like(out)
+    L.conv3x3(xn, wk, L.make_epilogue(bias=b, res1=r1, out=out, out_relu=out_relu, ldo=Cout), n, H, W, C, Cout)
+    _close(out, want)
+    _close(out_relu, want.relu())
+
+
+def test_conv3x3_headdot(L):
+    n, H, W, C = 2, 42, 56, 64
+    x = _rand(n, C, H, W, seed=1).bfloat16()
+    wt = _rand(32, C, 3, 3, scale=(9 * C) ** -0.5, seed=2).bfloat16()
+    b, w2 = _rand(32, seed=3), _rand(32, seed=4)
+    b2 = 0.3
+    mid = F.conv2d(x.float(), wt.float(), b, padding=1).relu()
+    want = (torch.einsum("nchw,c->nhw", mid, w2) + b2).relu()
+    xn = x.permute(0, 2, 3, 1).contiguous()
+    wk = wt.permute(0, 2, 3, 1).reshape(32, 9 * C).contiguous()
+    out = torch.full((n, H, W), float("nan"), device="cuda")
+    L.conv3x3(xn, wk, L.make_epilogue(bias=b, out_f32=out, w2=w2, b2=b2, store_mode=L.ST_HEADDOT), n, H, W, C, 32)
+    _close(out, want, 1e-2)
+
+
+def test_gemm_throughput_report(L, capsys):
+    """Not an assertion on speed: prints the achieved TFLOP/s of the encoder-sized GEMMs."""
+    M = 32 * 1370
+    for N, K in [(3072, 1024), (1024, 1024), (4096, 1024), (1024, 4096)]:
+        a = _rand(M, K, seed=1).bfloat16()
+        w = _rand(N, K, scale=K ** -0.5, seed=2).bfloat16()
+        out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+        epi = L.make_epilogue(out=out, ldo=N)
+        for _ in range(3):
+            L.gemm(a, w, epi)
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for _ in range(10):
+            L.gemm(a, w, epi)
+        t1.record()
+        torch.cuda.synchronize()
+        ms = t0.elapsed_time(t1) / 10
+        ref0, ref1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for _ in range(3):
+            torch.matmul(a, w.T)
+        ref0.record()
+        for _ in range(10):
+            torch.matmul(a, w.T)
+        ref1.record()
+        torch.cuda.synchronize()
+        ms_ref = ref0.elapsed_time(ref1) / 10
+        with capsys.disabled():
+            print(f"\n[gemm] M={M} N={N} K={K}: {ms:.3f} ms = {2 * M * N * K / ms / 1e9:.0f} TFLOP/s "
+                  f"(cuBLAS {ms_ref:.3f} ms = {2 * M * N * K / ms_ref / 1e9:.0f} TFLOP/s)")
+        _close(out, a.float() @ w.float().T)

@@ -1,0 +1,205 @@
+// C ABI (include/vda_b200.h): argument checking, TMA descriptor encoding, kernel launches.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/vda_b200.h"
+#include "gemm_params.h"
+#include "api_internal.h"
+
+namespace vda {
+cudaError_t launch_gemm(const GemmParams& p, int block_n, int num_sms, cudaStream_t stream);
+
+static thread_local char g_err[512] = "";
+static int g_num_sms = 0;
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+
+int set_error(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+int check_cuda(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return 0;
+  return set_error(static_cast<int>(e), "%s: %s", what, cudaGetErrorString(e));
+}
+int num_sms() { return g_num_sms; }
+
+// bf16 tensor map, 128B swizzle, inner box = 64 elements (128 B); rank 2..4.
+int encode_bf16_map(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                    const uint32_t* box) {
+  if (!g_encode) return set_error(-2, "vda_init() has not been called");
+  cuuint64_t gdim[5], gstr[5];
+  cuuint32_t bdim[5], estr[5];
+  for (int i = 0; i < rank; ++i) {
+    gdim[i] = dims[i];
+    bdim[i] = box[i];
+    estr[i] = 1;
+    if (i > 0) {
+      gstr[i - 1] = strides_bytes[i - 1];
+      if (gstr[i - 1] % 16) return set_error(-3, "tensor map stride %llu not a multiple of 16 B", (unsigned long long)gstr[i - 1]);
+    }
+  }
+  if (reinterpret_cast<uintptr_t>(base) % 16) return set_error(-3, "tensor map base not 16 B aligned");
+  CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), gdim, gstr, bdim, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(-4, "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
+  return 0;
+}
+
+static int pick_block_n(int requested, int N, int m_tiles, int store_mode) {
+  if (store_mode == ST_HEADDOT) return 32;
+  if (requested) return requested;
+  const int cands[4] = {256, 128, 64, 32};
+  for (int i = 0; i < 4; ++i) {
+    const int bn = cands[i];
+    if (bn > 32 && bn > ((N + 31) / 32) * 32) continue;
+    if (static_cast<long long>(m_tiles) * ((N + bn - 1) / bn) >= g_num_sms) return bn;
+  }
+  return N >= 64 ? 64 : 32;
+}
+
+static int fill_epilogue(GemmParams& p, const vda_epilogue* e) {
+  p.act = e->act;
+  p.store_mode = e->store_mode;
+  p.bias = e->bias;
+  p.scale = e->scale;
+  p.res_f32 = e->res_f32;
+  p.res1 = static_cast<const __nv_bfloat16*>(e->res1);
+  p.res2 = static_cast<const __nv_bfloat16*>(e->res2);
+  p.out = static_cast<__nv_bfloat16*>(e->out);
+  p.out_relu = static_cast<__nv_bfloat16*>(e->out_relu);
+  p.out_f32 = e->out_f32;
+  p.ldo = e->ldo;
+  p.n_out = (e->act == ACT_GEGLU) ? p.N / 2 : p.N;
+  p.ct_s = e->ct_s, p.ct_cout = e->ct_cout, p.ct_h = e->ct_h, p.ct_w = e->ct_w;
+  p.vt = static_cast<__nv_bfloat16*>(e->vt);
+  p.qkv_d = e->qkv_d, p.qkv_heads = e->qkv_heads, p.qkv_s = e->qkv_s, p.qkv_spad = e->qkv_spad;
+  p.w2 = e->w2;
+  p.b2 = e->b2;
+  if (p.N % 16) return set_error(-1, "N=%d must be a multiple of 16", p.N);
+  if (e->act == ACT_GEGLU) {
+    if (p.N % 32 || !e->bias || !e->out) return set_error(-1, "GEGLU needs N%%32==0, bias and out");
+    if (e->store_mode != ST_PLAIN) return set_error(-1, "GEGLU supports plain stores only");
+  }
+  if (e->store_mode == ST_HEADDOT) {
+    if (p.N > 32 || !e->bias || !e->w2 || !e->out_f32) return set_error(-1, "HEADDOT needs N<=32, bias, w2, out_f32");
+  } else {
+    if (e->ldo % 8) return set_error(-1, "ldo=%d must be a multiple of 8", e->ldo);
+    if (!e->out && !e->out_f32 && !e->out_relu && e->store_mode != ST_QKV) return set_error(-1, "no output given");
+  }
+  if (e->store_mode == ST_CONVT && (e->ct_cout % 16 || e->ct_s * e->ct_s * e->ct_cout != p.N))
+    return set_error(-1, "CONVT needs ct_cout%%16==0 and N == s*s*cout");
+  if (e->store_mode == ST_QKV && (!e->vt || 3 * e->qkv_d != p.N || e->qkv_heads * 64 != e->qkv_d))
+    return set_error(-1, "QKV store needs vt, N == 3*d and head_dim 64");
+  return 0;
+}
+
+}  // namespace vda
+
+using namespace vda;
+
+extern "C" {
+
+int vda_init(int device) {
+  int rc = check_cuda(cudaSetDevice(device), "cudaSetDevice");
+  if (rc) return rc;
+  rc = check_cuda(cudaFree(0), "cudaFree(0)");
+  if (rc) return rc;
+  cudaDeviceProp prop;
+  rc = check_cuda(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
+  if (rc) return rc;
+  if (prop.major != 10) return set_error(-5, "device %d is sm_%d%d; this library is sm_100a only", device, prop.major, prop.minor);
+  g_num_sms = prop.multiProcessorCount;
+  if (!g_encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    rc = check_cuda(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q), "cudaGetDriverEntryPoint");
+    if (rc) return rc;
+    if (!fn || q != cudaDriverEntryPointSuccess) return set_error(-6, "cuTensorMapEncodeTiled not available");
+    g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+  }
+  return 0;
+}
+
+const char* vda_last_error(void) { return g_err; }
+int vda_num_sms(void) { return g_num_sms; }
+
+int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, int K, const vda_epilogue* epi,
+                  void* stream) {
+  if (!A || !W || !epi || M <= 0 || N <= 0 || K <= 0) return set_error(-1, "vda_gemm_bf16: bad arguments");
+  if (lda % 8 || ldw % 8) return set_error(-1, "vda_gemm_bf16: lda/ldw must be multiples of 8");
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = M, p.N = N, p.K = K;
+  p.a_mode = A_PLAIN;
+  p.num_k_blocks = (K + 63) / 64;
+  p.m_tiles = (M + 127) / 128;
+  int rc = fill_epilogue(p, epi);
+  if (rc) return rc;
+  const int bn = pick_block_n(epi->block_n, N, p.m_tiles, epi->store_mode);
+  p.n_tiles = (N + bn - 1) / bn;
+  {
+    const uint64_t dims[2] = {(uint64_t)K, (uint64_t)M};
+    const uint64_t str[1] = {(uint64_t)lda * 2};
+    const uint32_t box[2] = {64, 128};
+    if ((rc = encode_bf16_map(&p.tmA, A, 2, dims, str, box))) return rc;
+  }
+  {
+    const uint64_t dims[2] = {(uint64_t)K, (uint64_t)N};
+    const uint64_t str[1] = {(uint64_t)ldw * 2};
+    const uint32_t box[2] = {64, (uint32_t)bn};
+    if ((rc = encode_bf16_map(&p.tmB, W, 2, dims, str, box))) return rc;
+  }
+  return check_cuda(launch_gemm(p, bn, g_num_sms, static_cast<cudaStream_t>(stream)), "gemm launch");
+}
+
+int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W, int C, int Cout,
+                     const vda_epilogue* epi, void* stream) {
+  if (!x || !w || !epi || n <= 0 || H <= 0 || W <= 0) return set_error(-1, "vda_conv3x3_nhwc: bad arguments");
+  if (C % 64 || ldx % 8 || ldx < C) return set_error(-1, "vda_conv3x3_nhwc: C=%d must be a multiple of 64 (ldx=%d)", C, ldx);
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = n * H * W, p.N = Cout, p.K = 9 * C;
+  p.a_mode = A_CONV3X3;
+  p.H = H, p.W = W, p.C = C;
+  p.num_k_blocks = 9 * (C / 64);
+  // spatial tile TH x TW = 128 pixels: pick the power-of-two TW with the fewest tiles
+  long long best = -1;
+  for (int l = 3; l <= 7; ++l) {
+    const int tw = 1 << l, th = 128 >> l;
+    const long long t = (long long)((W + tw - 1) / tw) * ((H + th - 1) / th);
+    if (best < 0 || t < best) best = t, p.tw_log2 = l;
+  }
+  const int tw = 1 << p.tw_log2, th = 128 >> p.tw_log2;
+  p.tiles_w = (W + tw - 1) / tw, p.tiles_h = (H + th - 1) / th;
+  p.m_tiles = n * p.tiles_w * p.tiles_h;
+  int rc = fill_epilogue(p, epi);
+  if (rc) return rc;
+  if (epi->store_mode != ST_PLAIN && epi->store_mode != ST_HEADDOT) return set_error(-1, "conv3x3: unsupported store mode");
+  const int bn = pick_block_n(epi->block_n, Cout, p.m_tiles, epi->store_mode);
+  p.n_tiles = (Cout + bn - 1) / bn;
+  {
+    const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)n};
+    const uint64_t str[3] = {(uint64_t)ldx * 2, (uint64_t)W * ldx * 2, (uint64_t)H * W * ldx * 2};
+    const uint32_t box[4] = {64, (uint32_t)tw, (uint32_t)th, 1};
+    if ((rc = encode_bf16_map(&p.tmA, x, 4, dims, str, box))) return rc;
+  }
+  {
+    const uint64_t dims[2] = {(uint64_t)(9 * C), (uint64_t)Cout};
+    const uint64_t str[1] = {(uint64_t)(9 * C) * 2};
+    const uint32_t box[2] = {64, (uint32_t)bn};
+    if ((rc = encode_bf16_map(&p.tmB, w, 2, dims, str, box))) return rc;
+  }
+  return check_cuda(launch_gemm(p, bn, g_num_sms, static_cast<cudaStream_t>(stream)), "conv3x3 launch");
+}
+
+}  // extern "C"

@@ -1,0 +1,54 @@
+// Parameter block of the tcgen05 GEMM / implicit-GEMM kernel (host + device).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+namespace vda {
+
+// A-operand addressing
+enum : int { A_PLAIN = 0, A_CONV3X3 = 1 };
+// output-row addressing
+enum : int {
+  ST_PLAIN = 0,    // out[row*ldo + col]
+  ST_CONVT = 1,    // ConvTranspose k=s: col=(kh,kw,co) scattered to the s-times larger NHWC map
+  ST_QKV = 2,      // plain store + V columns also written transposed per (frame, head)
+  ST_HEADDOT = 3,  // relu(acc+bias) . w2 + b2 -> relu -> out_f32[row]   (N <= BLOCK_N)
+};
+enum : int { ACT_NONE = 0, ACT_GELU = 1, ACT_RELU = 2, ACT_GEGLU = 3 };
+
+struct alignas(64) GemmParams {
+  CUtensorMap tmA;  // 2D [M,K] or 4D [N,H,W,C] bf16, box 64 x 128 rows, SWIZZLE_128B
+  CUtensorMap tmB;  // 2D [N,K] bf16, box 64 x BLOCK_N
+  int M, N, K;      // GEMM extents (conv: M = images*H*W, K = 9*C)
+  int num_k_blocks;
+  int m_tiles, n_tiles;
+  int a_mode;
+  // conv geometry (a_mode == A_CONV3X3): stride 1, pad 1, output map = input map
+  int H, W, C;
+  int tw_log2;           // spatial tile is TH x TW pixels with TW = 1<<tw_log2, TH = 128/TW
+  int tiles_w, tiles_h;  // tiles per image
+  // epilogue: v = acc + bias[col]; v = act(v); v *= scale[col]; v += residuals; store
+  int act;
+  int store_mode;
+  const float* bias;      // [N] or null
+  const float* scale;     // [N] or null (LayerScale gamma)
+  const float* res_f32;   // fp32 residual (same addressing as out) or null
+  const __nv_bfloat16* res1;  // bf16 residuals or null
+  const __nv_bfloat16* res2;
+  __nv_bfloat16* out;         // bf16 output or null
+  __nv_bfloat16* out_relu;    // second bf16 output holding relu(v), or null
+  float* out_f32;             // fp32 output or null
+  int ldo;                    // row pitch (elements) of out/out_relu/out_f32/res*
+  int n_out;                  // number of stored columns (N, or N/2 for GEGLU)
+  // ST_CONVT
+  int ct_s, ct_cout, ct_h, ct_w;  // stride(=kernel), padded Cout per tap, input map h, w
+  // ST_QKV
+  __nv_bfloat16* vt;  // [frames*heads, 64, s_pad]
+  int qkv_d, qkv_heads, qkv_s, qkv_spad;
+  // ST_HEADDOT
+  const float* w2;
+  float b2;
+};
+
+}  // namespace vda

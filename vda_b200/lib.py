@@ -1,0 +1,127 @@
+"""ctypes binding of libvda_b200.so (C ABI declared in include/vda_b200.h).
+
+There is deliberately no fallback: if the library is missing or the device is not sm_100 the
+import/first call raises.  torch is used only to own device memory and streams.
+"""
+import ctypes as C
+import os
+
+import torch
+
+from . import build as _build
+
+ACT_NONE, ACT_GELU, ACT_RELU, ACT_GEGLU = 0, 1, 2, 3
+ST_PLAIN, ST_CONVT, ST_QKV, ST_HEADDOT = 0, 1, 2, 3
+
+
+class Epilogue(C.Structure):
+    _fields_ = [
+        ("bias", C.c_void_p), ("scale", C.c_void_p), ("res_f32", C.c_void_p),
+        ("res1", C.c_void_p), ("res2", C.c_void_p),
+        ("out", C.c_void_p), ("out_relu", C.c_void_p), ("out_f32", C.c_void_p),
+        ("ldo", C.c_int), ("act", C.c_int), ("store_mode", C.c_int), ("block_n", C.c_int),
+        ("ct_s", C.c_int), ("ct_cout", C.c_int), ("ct_h", C.c_int), ("ct_w", C.c_int),
+        ("vt", C.c_void_p),
+        ("qkv_d", C.c_int), ("qkv_heads", C.c_int), ("qkv_s", C.c_int), ("qkv_spad", C.c_int),
+        ("w2", C.c_void_p), ("b2", C.c_float),
+    ]
+
+
+class VdaError(RuntimeError):
+    pass
+
+
+_lib = None
+_inited = set()
+
+
+def load():
+    """Load (building if the in-tree .so is absent) and return the ctypes library handle."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.LIB
+    if not os.path.exists(path):
+        path = _build.build()
+    lib = C.CDLL(path)
+    lib.vda_last_error.restype = C.c_char_p
+    _declare(lib)
+    _lib = lib
+    return lib
+
+
+def _declare(lib):
+    vp, i, f = C.c_void_p, C.c_int, C.c_float
+    ep = C.POINTER(Epilogue)
+    sig = {
+        "vda_init": [i],
+        "vda_num_sms": [],
+        "vda_gemm_bf16": [vp, i, vp, i, i, i, i, ep, vp],
+        "vda_conv3x3_nhwc": [vp, i, vp, i, i, i, i, i, ep, vp],
+    }
+    for name, args in sig.items():
+        fn = getattr(lib, name)
+        fn.argtypes = args
+        fn.restype = i
+    return sig
+
+
+def exported_symbols():
+    """Names every include/vda_b200.h declaration must resolve to (used by the CPU-side test)."""
+    return sorted(_declare(load()).keys()) + ["vda_last_error"]
+
+
+def check(rc):
+    if rc != 0:
+        raise VdaError(f"libvda_b200 error {rc}: {load().vda_last_error().decode()}")
+
+
+def init(device=None):
+    """Initialise the library for a CUDA device (idempotent). Raises if no sm_100 GPU."""
+    if not torch.cuda.is_available():
+        raise VdaError("libvda_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    dev = torch.cuda.current_device() if device is None else torch.device(device).index or 0
+    if dev not in _inited:
+        check(load().vda_init(dev))
+        _inited.add(dev)
+    return dev
+
+
+def stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def make_epilogue(bias=None, scale=None, res_f32=None, res1=None, res2=None, out=None, out_relu=None,
+                  out_f32=None, ldo=0, act=ACT_NONE, store_mode=ST_PLAIN, block_n=0, ct=None, qkv=None,
+                  w2=None, b2=0.0):
+    e = Epilogue()
+    e.bias, e.scale, e.res_f32 = ptr(bias), ptr(scale), ptr(res_f32)
+    e.res1, e.res2 = ptr(res1), ptr(res2)
+    e.out, e.out_relu, e.out_f32 = ptr(out), ptr(out_relu), ptr(out_f32)
+    e.ldo, e.act, e.store_mode, e.block_n = ldo, act, store_mode, block_n
+    if ct is not None:
+        e.ct_s, e.ct_cout, e.ct_h, e.ct_w = ct
+    if qkv is not None:
+        vt, d, heads, s, spad = qkv
+        e.vt, e.qkv_d, e.qkv_heads, e.qkv_s, e.qkv_spad = ptr(vt), d, heads, s, spad
+    e.w2, e.b2 = ptr(w2), b2
+    return e
+
+
+def gemm(a, w, epi, M=None, N=None, K=None, lda=None, ldw=None):
+    """epi(A[M,K] @ W[N,K]^T); a, w bf16 row-major 2-D CUDA tensors."""
+    M = a.shape[0] if M is None else M
+    K = a.shape[1] if K is None else K
+    N = w.shape[0] if N is None else N
+    lda = a.stride(0) if lda is None else lda
+    ldw = w.stride(0) if ldw is None else ldw
+    check(load().vda_gemm_bf16(ptr(a), lda, ptr(w), ldw, M, N, K, C.byref(epi), stream_ptr()))
+
+
+def conv3x3(x, w, epi, n, H, W, Cin, Cout, ldx=None):
+    ldx = Cin if ldx is None else ldx
+    check(load().vda_conv3x3_nhwc(ptr(x), ldx, ptr(w), n, H, W, Cin, Cout, C.byref(epi), stream_ptr()))
