@@ -216,7 +216,7 @@ def net_input_size(h0, w0, input_size=518):
 
     def mult(x):
         y = int(np.round(x / 14) * 14)
-        if y < 0:                                  # min_val = 0 -> never triggers; kept for fidelity
+        if y < input_size:                         # min_val = target size (transform.py:95-97)
             y = int(np.ceil(x / 14) * 14)
         return y
 
@@ -275,7 +275,7 @@ def align_windows(depth_list, metric=False):
             continue
         cur = [depth_list[base + i] for i in range(n_align)]
         s, t = (1.0, 0.0) if metric else scale_and_shift(np.concatenate(cur), np.concatenate(ref))
-        fix = lambda d: np.maximum(d * s + t, 0) * 1 if False else _affine_clamp(d, s, t)
+        fix = lambda d: _affine_clamp(d, s, t)
         pre = aligned[-INTERP_LEN:]
         post = [fix(depth_list[base + i]) for i in range(n_align, OVERLAP)]
         w = [0.0] + [i * (1.0 / (INTERP_LEN - 1)) for i in range(1, INTERP_LEN - 1)] + [1.0]   # util.py:65-74
