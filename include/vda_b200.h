@@ -63,6 +63,57 @@ int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, 
 int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W, int C, int Cout,
                      const vda_epilogue* epi, void* stream);
 
+
+/* Flash-style spatial attention, head_dim 64, non-causal (dinov2_layers/attention.py:53-59 / :76).
+ * qk: [frames*S, 2D] bf16 (Q | K), vt: [frames*heads, 64, s_pad] bf16 (V transposed, zero padded,
+ * s_pad % 8 == 0) -- both written by vda_gemm_bf16 with VDA_ST_QKV.  out: [frames*S, D] bf16. */
+int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int frames, int S, int heads, int s_pad,
+                       void* stream);
+
+/* LayerNorm over the last dim (dinov2_layers/block.py:84,87; dinov2.py:310; motion_module.py:175,186).
+ * x: [rows, C] f32 (x_is_f32) or bf16; out bf16.  If tokens_per_frame > 0 the first `skip` tokens of
+ * every frame are dropped from the output (cls token, dinov2.py:311-312).  If pe != NULL,
+ * pe[(row / pe_rows_per_t) % pe_T][:] is added after normalisation (motion_module.py:207-209) and
+ * out_nope (optional) receives the value before the add (the streaming cache, motion_module.py:251). */
+int vda_layernorm(const void* x, int x_is_f32, const float* gamma, const float* beta, void* out, void* out_nope,
+                  const float* pe, int rows, int C, float eps, int tokens_per_frame, int skip, int pe_rows_per_t,
+                  int pe_T, void* stream);
+
+/* GroupNorm(32 groups) on an NHWC bf16 map [n, hw, ldx>=C] -> [n, hw, C] bf16 (motion_module.py:112).
+ * stats_ws: 64*n doubles of scratch. */
+int vda_groupnorm_nhwc(const void* x, int ldx, const float* gamma, const float* beta, void* out, double* stats_ws,
+                       int n, int hw, int C, float eps, void* stream);
+
+/* 14x14/stride-14 patch gather: x f32 NCHW [frames,3,H,W] -> A bf16 [frames*(H/14)*(W/14), ldk],
+ * k = (c,kh,kw), zero padded to ldk (dinov2_layers/patch_embed.py:66,76-78). */
+int vda_patch_im2col(const float* x, void* a, int frames, int H, int W, int ldk, void* stream);
+
+/* tokens[f,0]=cls+pos[0]; tokens[f,1+i]=patch[f*hw+i]+pos[1+i], all f32 (dinov2.py:218-219). */
+int vda_add_cls_pos(const float* patch, const float* cls, const float* pos, float* tokens, int frames, int hw, int D,
+                    void* stream);
+
+/* Bilinear resampling with align_corners=True: NHWC bf16 (util/blocks.py:156-158,
+ * dpt_temporal.py:116-118) and single-channel f32 with optional ReLU (video_depth.py:66-67,111-112). */
+int vda_bilinear_nhwc(const void* x, int ldx, void* out, int ldo, int n, int h, int w, int H, int W, int C,
+                      void* stream);
+int vda_bilinear_f32(const float* x, float* out, int n, int h, int w, int H, int W, int relu, void* stream);
+
+/* 3x3 stride-2 pad-1 patch gather for dpt.py:85-90: x NHWC bf16 [n,h,w,C] -> [n*ho*wo, 9*C]. */
+int vda_im2col_s2(const void* x, void* a, int n, int h, int w, int C, void* stream);
+
+/* Temporal attention core (motion_module/motion_module.py:268-308, attention.py:187-207): element
+ * (t, token, c) at row t*hw + token; softmax over Tk <= 32 frames for each of Tq query frames. */
+int vda_temporal_attn(const void* q, int ldq, const void* k, int ldk, const void* v, int ldv, void* out, int ldo,
+                      int hw, int heads, int head_dim, int Tq, int Tk, void* stream);
+
+/* Alignment (utils/util.py:40-74, video_depth.py:120-160).  sums5 = {sum p*p, sum p, n, sum p*t,
+ * sum t} accumulated in FP64 (caller zeroes it); solve writes {scale, shift} (metric: {1,0}). */
+int vda_lsq_accum(const float* pred, const float* target, long long n, double* sums5, void* stream);
+int vda_lsq_solve(const double* sums5, float* scale_shift, int metric, void* stream);
+int vda_affine_clamp(const float* src, float* dst, long long n, const float* scale_shift, void* stream);
+int vda_affine_clamp_blend(float* pre, const float* post, long long per_frame, int frames, const float* scale_shift,
+                           void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,201 @@
+"""Attention / normalisation / resampling / alignment kernels vs plain torch fp32 references."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def L():
+    import vda_b200.lib as lib
+
+    lib.init()
+    return lib
+
+
+def _rand(*shape, scale=1.0, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).cuda()
+
+
+def _close(got, want, tol=2e-2):
+    got, want = got.float(), want.float()
+    assert torch.isfinite(got).all()
+    err = (got - want).abs().max().item()
+    ref = want.abs().max().item()
+    assert err <= tol * max(ref, 1e-6), f"max abs err {err} vs ref max {ref}"
+
+
+@pytest.mark.parametrize("frames,S,heads", [(1, 128, 1), (2, 197, 2), (3, 1370, 6), (1, 2443, 3), (2, 64, 1), (32, 1370, 16)])
+def test_flash_attention(L, frames, S, heads):
+    D = heads * 64
+    spad = (S + 7) // 8 * 8
+    q = _rand(frames, S, heads, 64, scale=1.5, seed=1).bfloat16()
+    k = _rand(frames, S, heads, 64, scale=1.5, seed=2).bfloat16()
+    v = _rand(frames, S, heads, 64, seed=3).bfloat16()
+    qk = torch.cat([q.reshape(frames * S, D), k.reshape(frames * S, D)], dim=1).contiguous()
+    vt = torch.zeros(frames * heads, 64, spad, device="cuda", dtype=torch.bfloat16)
+    vt[:, :, :S] = v.permute(0, 2, 3, 1).reshape(frames * heads, 64, S)
+    out = torch.full((frames * S, D), float("nan"), device="cuda", dtype=torch.bfloat16)
+    L.flash_attn(qk, vt, out, frames, S, heads, spad)
+    torch.cuda.synchronize()
+    want = F.scaled_dot_product_attention(q.float().transpose(1, 2), k.float().transpose(1, 2), v.float().transpose(1, 2))
+    _close(out.view(frames, S, heads, 64), want.transpose(1, 2), 2e-2)
+
+
+@pytest.mark.parametrize("rows,C,f32", [(100, 384, True), (2740, 1024, True), (77, 256, False), (50, 64, False), (33, 768, True), (10, 192, False)])
+def test_layernorm(L, rows, C, f32):
+    x = _rand(rows, C, scale=2.0, seed=1) + 0.5
+    if not f32:
+        x = x.bfloat16()
+    g, b = _rand(C, seed=2), _rand(C, seed=3)
+    out = torch.empty(rows, C, device="cuda", dtype=torch.bfloat16)
+    L.layernorm(x, g, b, out, 1e-6)
+    _close(out, F.layer_norm(x.float(), (C,), g, b, 1e-6), 1e-2)
+
+
+def test_layernorm_skip_cls_and_pe(L):
+    frames, S, C = 4, 11, 384
+    x = _rand(frames * S, C, seed=1)
+    g, b = _rand(C, seed=2), _rand(C, seed=3)
+    want = F.layer_norm(x, (C,), g, b, 1e-6).view(frames, S, C)[:, 1:].reshape(-1, C)
+    out = torch.empty(frames * (S - 1), C, device="cuda", dtype=torch.bfloat16)
+    L.layernorm(x, g, b, out, 1e-6, tokens_per_frame=S, skip=1)
+    _close(out, want, 1e-2)
+    T, hw = 4, 11
+    pe = _rand(32, C, seed=4)
+    out = torch.empty(T * hw, C, device="cuda", dtype=torch.bfloat16)
+    nope = torch.empty_like(out)
+    L.layernorm(x, g, b, out, 1e-5, pe=pe, out_nope=nope, pe_rows_per_t=hw, pe_T=32)
+    base = F.layer_norm(x, (C,), g, b, 1e-5)
+    _close(nope, base, 1e-2)
+    _close(out, (base.view(T, hw, C) + pe[:T, None]).view(-1, C), 1e-2)
+
+
+@pytest.mark.parametrize("n,h,w,C", [(3, 19, 19, 1024), (2, 37, 37, 256), (4, 5, 7, 192), (2, 10, 10, 64)])
+def test_groupnorm_nhwc(L, n, h, w, C):
+    x = (_rand(n, C, h, w, scale=2.0, seed=1) + 1.0).bfloat16()
+    g, b = _rand(C, seed=2), _rand(C, seed=3)
+    want = F.group_norm(x.float(), 32, g, b, 1e-6).permute(0, 2, 3, 1)
+    xn = x.permute(0, 2, 3, 1).contiguous()
+    out = torch.empty(n, h, w, C, device="cuda", dtype=torch.bfloat16)
+    ws = torch.empty(64 * n, device="cuda", dtype=torch.float64)
+    L.groupnorm_nhwc(xn, g, b, out, ws, n, h * w, C, 1e-6)
+    _close(out, want, 1e-2)
+
+
+def test_patch_embed_path(L):
+    frames, H, W, D = 2, 42, 70, 384
+    x = _rand(frames, 3, H, W, seed=1)
+    wt = _rand(D, 3, 14, 14, scale=588 ** -0.5, seed=2)
+    b = _rand(D, seed=3)
+    cls, pos = _rand(D, seed=4), _rand(1 + 15, D, seed=5)
+    hw = 15
+    a = torch.empty(frames * hw, 592, device="cuda", dtype=torch.bfloat16)
+    L.patch_im2col(x, a, frames, H, W, 592)
+    wk = torch.zeros(D, 592, device="cuda", dtype=torch.bfloat16)
+    wk[:, :588] = wt.reshape(D, 588)
+    patch = torch.empty(frames * hw, D, device="cuda")
+    L.gemm(a, wk, L.make_epilogue(bias=b, out_f32=patch, ldo=D), K=588)
+    tokens = torch.empty(frames, hw + 1, D, device="cuda")
+    L.add_cls_pos(patch, cls, pos, tokens, frames, hw, D)
+    want = F.conv2d(x, wt, b, stride=14).flatten(2).transpose(1, 2)
+    want = torch.cat([cls.expand(frames, 1, D), want], dim=1) + pos
+    _close(tokens, want, 1e-2)
+
+
+@pytest.mark.parametrize("h,w,H,W,C", [(19, 19, 37, 37, 64), (37, 66, 74, 132, 128), (296, 296, 518, 518, 8), (5, 5, 5, 5, 16)])
+def test_bilinear_nhwc(L, h, w, H, W, C):
+    n = 2
+    x = _rand(n, C, h, w, seed=1).bfloat16()
+    want = F.interpolate(x.float(), size=(H, W), mode="bilinear", align_corners=True).permute(0, 2, 3, 1)
+    out = torch.empty(n, H, W, C, device="cuda", dtype=torch.bfloat16)
+    L.bilinear_nhwc(x.permute(0, 2, 3, 1).contiguous(), out, n, h, w, H, W, C)
+    _close(out, want, 1e-2)
+
+
+def test_bilinear_f32(L):
+    x = _rand(3, 1, 70, 98, seed=1)
+    out = torch.empty(3, 123, 77, device="cuda")
+    L.bilinear_f32(x, out, 3, 70, 98, 123, 77, relu=True)
+    want = F.interpolate(x, size=(123, 77), mode="bilinear", align_corners=True).relu()[:, 0]
+    assert (out - want).abs().max().item() < 1e-5
+
+
+def test_im2col_s2_conv(L):
+    n, h, w, C, Co = 2, 37, 37, 64, 64
+    x = _rand(n, C, h, w, seed=1).bfloat16()
+    wt = _rand(Co, C, 3, 3, scale=(9 * C) ** -0.5, seed=2).bfloat16()
+    b = _rand(Co, seed=3)
+    want = F.conv2d(x.float(), wt.float(), b, stride=2, padding=1).permute(0, 2, 3, 1)
+    ho = wo = 19
+    a = torch.empty(n * ho * wo, 9 * C, device="cuda", dtype=torch.bfloat16)
+    L.im2col_s2(x.permute(0, 2, 3, 1).contiguous(), a, n, h, w, C)
+    out = torch.empty(n, ho, wo, Co, device="cuda", dtype=torch.bfloat16)
+    L.gemm(a, wt.permute(0, 2, 3, 1).reshape(Co, 9 * C).contiguous(), L.make_epilogue(bias=b, out=out, ldo=Co))
+    _close(out, want)
+
+
+@pytest.mark.parametrize("T,hw,C,Tq", [(32, 50, 1024, 32), (32, 37, 256, 32), (4, 35, 192, 4), (32, 12, 384, 1), (32, 9, 64, 32), (7, 20, 128, 7)])
+def test_temporal_attention(L, T, hw, C, Tq):
+    heads, hd = 8, C // 8
+    qkv = _rand(T * hw, 3 * C, seed=1).bfloat16()
+    q = qkv[(T - Tq) * hw:, :C]
+    out = torch.full((Tq * hw, C), float("nan"), device="cuda", dtype=torch.bfloat16)
+    L.temporal_attn(q, 3 * C, qkv[:, C:], 3 * C, qkv[:, 2 * C:], 3 * C, out, C, hw, heads, hd, Tq, T)
+    f = qkv.float().view(T, hw, 3, heads, hd).permute(2, 1, 3, 0, 4)       # [3, hw, heads, T, hd]
+    want = F.scaled_dot_product_attention(f[0][:, :, T - Tq:], f[1], f[2])   # [hw, heads, Tq, hd]
+    _close(out.view(Tq, hw, heads, hd), want.permute(2, 0, 1, 3), 2e-2)
+
+
+def test_lsq_and_blend(L):
+    from oracle import vda_oracle as O
+
+    rng = np.random.default_rng(0)
+    h, w = 60, 80
+    pred = rng.uniform(0.5, 8, (2, h, w)).astype(np.float32)
+    target = (pred * 1.7 - 0.4 + rng.normal(0, 0.05, pred.shape)).astype(np.float32)
+    s_ref, t_ref = O.scale_and_shift(pred.reshape(2 * h, w), target.reshape(2 * h, w))
+    sums = torch.zeros(5, device="cuda", dtype=torch.float64)
+    ss = torch.zeros(2, device="cuda")
+    p, t = torch.from_numpy(pred).cuda(), torch.from_numpy(target).cuda()
+    L.lsq_accum(p[0], t[0], h * w, sums)
+    L.lsq_accum(p[1], t[1], h * w, sums)
+    L.lsq_solve(sums, ss)
+    assert abs(ss[0].item() - s_ref) < 1e-4 * abs(s_ref) and abs(ss[1].item() - t_ref) < 1e-3
+    L.lsq_solve(sums, ss, metric=True)
+    assert ss.tolist() == [1.0, 0.0]
+    ss = torch.tensor([1.3, -2.0], device="cuda")
+    pre = rng.uniform(0, 5, (8, h, w)).astype(np.float32)
+    post = rng.uniform(0, 5, (8, h, w)).astype(np.float32)
+    fixed = [O._affine_clamp(post[i].copy(), np.float32(1.3), np.float32(-2.0)) for i in range(8)]
+    wts = [0.0] + [i * (1.0 / 7) for i in range(1, 7)] + [1.0]
+    want = np.stack([pre[i] * (1 - wts[i]) + fixed[i] * wts[i] for i in range(8)])
+    pre_d, post_d = torch.from_numpy(pre).cuda(), torch.from_numpy(post).cuda()
+    L.affine_clamp_blend(pre_d, post_d, h * w, 8, ss)
+    np.testing.assert_allclose(pre_d.cpu().numpy(), want, rtol=1e-6, atol=1e-6)
+    dst = torch.empty_like(post_d)
+    L.affine_clamp(post_d, dst, post_d.numel(), ss)
+    np.testing.assert_allclose(dst.cpu().numpy(), np.stack(fixed), rtol=1e-6, atol=1e-6)
+
+
+def test_attention_throughput_report(L, capsys):
+    frames, S, heads = 32, 1370, 16
+    D, spad = heads * 64, 1376
+    qk = _rand(frames * S, 2 * D, seed=1).bfloat16()
+    vt = _rand(frames * heads, 64, spad, seed=2).bfloat16()
+    out = torch.empty(frames * S, D, device="cuda", dtype=torch.bfloat16)
+    for _ in range(3):
+        L.flash_attn(qk, vt, out, frames, S, heads, spad)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(10):
+        L.flash_attn(qk, vt, out, frames, S, heads, spad)
+    t1.record()
+    torch.cuda.synchronize()
+    ms = t0.elapsed_time(t1) / 10
+    fl = 4 * frames * heads * S * S * 64
+    with capsys.disabled():
+        print(f"\n[attn] vitl block: {ms:.3f} ms = {fl / ms / 1e9:.0f} TFLOP/s")

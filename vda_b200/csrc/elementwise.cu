@@ -1,0 +1,355 @@
+// Bandwidth-bound kernels of the window path: LayerNorm, GroupNorm (NHWC), patch im2col,
+// cls/pos-embed assembly, bilinear (align_corners=True) resampling, stride-2 im2col.
+// All are coalesced along the channel (innermost) dimension with 8/16-byte vector accesses.
+#include <string.h>
+
+#include "common.cuh"
+#include "api_internal.h"
+#include "../../include/vda_b200.h"
+
+namespace vda {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// ------------------------------------------------------------------ LayerNorm
+// One warp per row; the row lives in registers (C <= 64*MAXV).  Two-pass (mean, then centred variance) like torch's CPU/GPU kernels.
+// Output row remap: input rows are [frames, S] tokens; the first `skip` tokens of every frame are
+// dropped (cls token for the DPT taps, dinov2.py:311-312).  Optional positional-encoding add
+// (motion_module.py:207-209) after normalisation: pe[(row / pe_rows_per_t) % pe_T][c].
+template <typename TIn, int MAXV>
+__global__ void layernorm_kernel(const TIn* __restrict__ x, const float* __restrict__ gamma,
+                                 const float* __restrict__ beta, bf16* __restrict__ out, bf16* __restrict__ out_nope,
+                                 const float* __restrict__ pe, int rows, int C, float eps, int S, int skip,
+                                 int pe_rows_per_t, int pe_T) {
+  const int warps_per_block = blockDim.x >> 5;
+  const int row = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const int f = row / S, s = row - f * S;
+  if (s < skip) return;
+  const long long orow = static_cast<long long>(f) * (S - skip) + (s - skip);
+  const TIn* xr = x + static_cast<long long>(row) * C;
+  float v[MAXV], w[MAXV];  // even / odd element of each channel pair owned by this lane
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int c = (i * 32 + lane) * 2;
+    v[i] = 0.f, w[i] = 0.f;
+    if (c < C) {
+      float2 t;
+      if constexpr (sizeof(TIn) == 4) {
+        t = *reinterpret_cast<const float2*>(xr + c);
+      } else {
+        t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(xr + c));
+      }
+      v[i] = t.x, w[i] = t.y;
+      sum += t.x + t.y;
+    }
+  }
+  const float mean = warp_sum(sum) / C;
+  float sq = 0.f;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int c = (i * 32 + lane) * 2;
+    if (c < C) {
+      const float da = v[i] - mean, db = w[i] - mean;
+      sq += da * da + db * db;
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(sq) / C + eps);
+  const float* per = pe ? pe + static_cast<long long>((row / pe_rows_per_t) % pe_T) * C : nullptr;
+  bf16* o = out + orow * C;
+  bf16* o2 = out_nope ? out_nope + orow * C : nullptr;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int c = (i * 32 + lane) * 2;
+    if (c < C) {
+      const float2 g = *reinterpret_cast<const float2*>(gamma + c);
+      const float2 bb = *reinterpret_cast<const float2*>(beta + c);
+      float a = (v[i] - mean) * rstd * g.x + bb.x;
+      float b = (w[i] - mean) * rstd * g.y + bb.y;
+      if (o2) *reinterpret_cast<__nv_bfloat162*>(o2 + c) = __floats2bfloat162_rn(a, b);
+      if (per) {
+        const float2 pp = *reinterpret_cast<const float2*>(per + c);
+        a += pp.x, b += pp.y;
+      }
+      *reinterpret_cast<__nv_bfloat162*>(o + c) = __floats2bfloat162_rn(a, b);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ GroupNorm (NHWC, 32 groups)
+// stats: one block per (image, row-chunk); thread t owns channel pair 2t; per-group partial sums
+// go through shared memory then one double atomicAdd per (group, block).
+__global__ void groupnorm_stats_kernel(const bf16* __restrict__ x, double* __restrict__ stats, int hw, int C, int ldx,
+                                       int rows_per_block) {
+  __shared__ float sh[64];
+  const int img = blockIdx.y;
+  const int r0 = blockIdx.x * rows_per_block;
+  const int r1 = min(hw, r0 + rows_per_block);
+  if (threadIdx.x < 64) sh[threadIdx.x] = 0.f;
+  __syncthreads();
+  const int cg = C / 32;
+  for (int c = threadIdx.x * 2; c < C; c += blockDim.x * 2) {
+    float s = 0.f, ss = 0.f;
+    for (int r = r0; r < r1; ++r) {
+      const float2 t = __bfloat1622float2(
+          *reinterpret_cast<const __nv_bfloat162*>(x + (static_cast<long long>(img) * hw + r) * ldx + c));
+      s += t.x + t.y;
+      ss += t.x * t.x + t.y * t.y;
+    }
+    const int g = c / cg;
+    atomicAdd(&sh[2 * g], s);
+    atomicAdd(&sh[2 * g + 1], ss);
+  }
+  __syncthreads();
+  if (threadIdx.x < 64) atomicAdd(&stats[static_cast<long long>(img) * 64 + threadIdx.x], static_cast<double>(sh[threadIdx.x]));
+}
+
+__global__ void groupnorm_apply_kernel(const bf16* __restrict__ x, const double* __restrict__ stats,
+                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                       bf16* __restrict__ out, int hw, int C, int ldx, float eps, long long total_pairs) {
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= total_pairs) return;
+  const int half_c = C / 2;
+  const long long pix = idx / half_c;
+  const int c = static_cast<int>(idx - pix * half_c) * 2;
+  const int img = static_cast<int>(pix / hw);
+  const int g = c / (C / 32);
+  const double n = static_cast<double>(hw) * (C / 32);
+  const double mean = stats[img * 64 + 2 * g] / n;
+  const double var = stats[img * 64 + 2 * g + 1] / n - mean * mean;
+  const float rstd = rsqrtf(static_cast<float>(var > 0 ? var : 0) + eps);
+  const float m = static_cast<float>(mean);
+  const float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(x + pix * ldx + c));
+  const float a = (t.x - m) * rstd * gamma[c] + beta[c];
+  const float b = (t.y - m) * rstd * gamma[c + 1] + beta[c + 1];
+  *reinterpret_cast<__nv_bfloat162*>(out + pix * C + c) = __floats2bfloat162_rn(a, b);
+}
+
+// ------------------------------------------------------------------ patch im2col (14x14, stride 14)
+// x fp32 NCHW [frames,3,H,W] -> A bf16 [frames*gh*gw, ldk] with k = (c, kh, kw) (patch_embed.py:66).
+__global__ void patch_im2col_kernel(const float* __restrict__ x, bf16* __restrict__ a, int H, int W, int gh, int gw,
+                                    int ldk) {
+  const long long row = blockIdx.x;
+  const int f = static_cast<int>(row / (gh * gw));
+  const int p = static_cast<int>(row - static_cast<long long>(f) * gh * gw);
+  const int ph = p / gw, pw = p - ph * gw;
+  for (int k = threadIdx.x; k < ldk; k += blockDim.x) {
+    float v = 0.f;
+    if (k < 588) {
+      const int c = k / 196, r = k - c * 196;
+      const int kh = r / 14, kw = r - kh * 14;
+      v = x[((static_cast<long long>(f) * 3 + c) * H + ph * 14 + kh) * W + pw * 14 + kw];
+    }
+    a[row * ldk + k] = __float2bfloat16(v);
+  }
+}
+
+// tokens[f, 0] = cls + pos[0]; tokens[f, 1+i] = patch[f*hw+i] + pos[1+i]   (dinov2.py:218-219)
+__global__ void add_cls_pos_kernel(const float* __restrict__ patch, const float* __restrict__ cls,
+                                   const float* __restrict__ pos, float* __restrict__ tokens, int hw, int D,
+                                   long long total4) {
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= total4) return;
+  const int d4 = D / 4;
+  const long long row = idx / d4;
+  const int c = static_cast<int>(idx - row * d4) * 4;
+  const int S = hw + 1;
+  const int f = static_cast<int>(row / S), s = static_cast<int>(row - static_cast<long long>(f) * S);
+  float4 v = (s == 0) ? *reinterpret_cast<const float4*>(cls + c)
+                      : *reinterpret_cast<const float4*>(patch + (static_cast<long long>(f) * hw + s - 1) * D + c);
+  const float4 pp = *reinterpret_cast<const float4*>(pos + static_cast<long long>(s) * D + c);
+  v.x += pp.x, v.y += pp.y, v.z += pp.z, v.w += pp.w;
+  *reinterpret_cast<float4*>(tokens + row * D + c) = v;
+}
+
+// ------------------------------------------------------------------ bilinear, align_corners=True, NHWC bf16
+// (util/blocks.py:156-158, dpt_temporal.py:116-118).  One thread per (output pixel, 8 channels).
+__global__ void bilinear_nhwc_kernel(const bf16* __restrict__ x, bf16* __restrict__ out, int h, int w, int H, int W,
+                                     int C, int ldx, int ldo, float sy, float sx, long long total) {
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int c8 = C / 8;
+  const long long pix = idx / c8;
+  const int c = static_cast<int>(idx - pix * c8) * 8;
+  const int X = static_cast<int>(pix % W);
+  const long long t = pix / W;
+  const int Y = static_cast<int>(t % H);
+  const int n = static_cast<int>(t / H);
+  const float fy = sy * Y, fx = sx * X;
+  int y0 = static_cast<int>(fy), x0 = static_cast<int>(fx);
+  y0 = min(y0, h - 1), x0 = min(x0, w - 1);
+  const int y1 = min(y0 + 1, h - 1), x1 = min(x0 + 1, w - 1);
+  const float ly = fy - y0, lx = fx - x0;
+  const float w00 = (1.f - ly) * (1.f - lx), w01 = (1.f - ly) * lx, w10 = ly * (1.f - lx), w11 = ly * lx;
+  const bf16* base = x + static_cast<long long>(n) * h * w * ldx + c;
+  const uint4 a = __ldg(reinterpret_cast<const uint4*>(base + (static_cast<long long>(y0) * w + x0) * ldx));
+  const uint4 b = __ldg(reinterpret_cast<const uint4*>(base + (static_cast<long long>(y0) * w + x1) * ldx));
+  const uint4 cc = __ldg(reinterpret_cast<const uint4*>(base + (static_cast<long long>(y1) * w + x0) * ldx));
+  const uint4 d = __ldg(reinterpret_cast<const uint4*>(base + (static_cast<long long>(y1) * w + x1) * ldx));
+  const uint32_t* pa = &a.x;
+  const uint32_t* pb = &b.x;
+  const uint32_t* pc = &cc.x;
+  const uint32_t* pd = &d.x;
+  uint32_t o[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 fa = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(pa + i));
+    const float2 fb = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(pb + i));
+    const float2 fc = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(pc + i));
+    const float2 fd = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(pd + i));
+    const __nv_bfloat162 r = __floats2bfloat162_rn(w00 * fa.x + w01 * fb.x + w10 * fc.x + w11 * fd.x,
+                                                   w00 * fa.y + w01 * fb.y + w10 * fc.y + w11 * fd.y);
+    o[i] = *reinterpret_cast<const uint32_t*>(&r);
+  }
+  *reinterpret_cast<uint4*>(out + pix * ldo + c) = make_uint4(o[0], o[1], o[2], o[3]);
+}
+
+// fp32 single-channel bilinear (video_depth.py:66,111-112), optional ReLU.
+__global__ void bilinear_f32_kernel(const float* __restrict__ x, float* __restrict__ out, int h, int w, int H, int W,
+                                    float sy, float sx, int relu, long long total) {
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int X = static_cast<int>(idx % W);
+  const long long t = idx / W;
+  const int Y = static_cast<int>(t % H);
+  const long long n = t / H;
+  const float fy = sy * Y, fx = sx * X;
+  int y0 = min(static_cast<int>(fy), h - 1), x0 = min(static_cast<int>(fx), w - 1);
+  const int y1 = min(y0 + 1, h - 1), x1 = min(x0 + 1, w - 1);
+  const float ly = fy - y0, lx = fx - x0;
+  const float* b = x + n * h * w;
+  float v = (1.f - ly) * ((1.f - lx) * b[y0 * w + x0] + lx * b[y0 * w + x1]) +
+            ly * ((1.f - lx) * b[y1 * w + x0] + lx * b[y1 * w + x1]);
+  if (relu) v = fmaxf(v, 0.f);
+  out[idx] = v;
+}
+
+// 3x3 stride-2 pad-1 im2col for dpt.py:85-90: x NHWC [n,h,w,C] -> A [n*ho*wo, 9*C], k = (kh,kw,c)
+__global__ void im2col_s2_kernel(const bf16* __restrict__ x, bf16* __restrict__ a, int h, int w, int ho, int wo, int C,
+                                 long long total) {
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int c8 = C / 8;
+  const int c = static_cast<int>(idx % c8) * 8;
+  long long t = idx / c8;
+  const int tap = static_cast<int>(t % 9);
+  t /= 9;
+  const int X = static_cast<int>(t % wo);
+  t /= wo;
+  const int Y = static_cast<int>(t % ho);
+  const int n = static_cast<int>(t / ho);
+  const int kh = tap / 3, kw = tap - kh * 3;
+  const int iy = Y * 2 - 1 + kh, ix = X * 2 - 1 + kw;
+  uint4 v = make_uint4(0, 0, 0, 0);
+  if (iy >= 0 && iy < h && ix >= 0 && ix < w)
+    v = __ldg(reinterpret_cast<const uint4*>(x + ((static_cast<long long>(n) * h + iy) * w + ix) * C + c));
+  const long long orow = (static_cast<long long>(n) * ho + Y) * wo + X;
+  *reinterpret_cast<uint4*>(a + orow * (9LL * C) + tap * C + c) = v;
+}
+
+}  // namespace vda
+
+using namespace vda;
+
+template <typename TIn>
+static int launch_ln(const void* x, const float* gamma, const float* beta, void* out, void* out_nope, const float* pe,
+                     int rows, int C, float eps, int S, int skip, int pe_rows_per_t, int pe_T, cudaStream_t st) {
+  const int warps = 8;
+  dim3 grid((rows + warps - 1) / warps), block(warps * 32);
+#define VDA_LN(MAXV)                                                                                              \
+  layernorm_kernel<TIn, MAXV><<<grid, block, 0, st>>>(static_cast<const TIn*>(x), gamma, beta, static_cast<bf16*>(out), \
+                                                      static_cast<bf16*>(out_nope), pe, rows, C, eps, S, skip,  \
+                                                      pe_rows_per_t, pe_T)
+  if (C <= 256) VDA_LN(4);
+  else if (C <= 512) VDA_LN(8);
+  else if (C <= 1024) VDA_LN(16);
+  else return set_error(-1, "layernorm: C=%d > 1024 unsupported", C);
+#undef VDA_LN
+  return check_cuda(cudaGetLastError(), "layernorm launch");
+}
+
+extern "C" {
+
+int vda_layernorm(const void* x, int x_is_f32, const float* gamma, const float* beta, void* out, void* out_nope,
+                  const float* pe, int rows, int C, float eps, int tokens_per_frame, int skip, int pe_rows_per_t,
+                  int pe_T, void* stream) {
+  if (!x || !gamma || !beta || !out || rows <= 0 || C % 2) return set_error(-1, "vda_layernorm: bad arguments");
+  if (tokens_per_frame <= 0) tokens_per_frame = rows, skip = 0;
+  if (pe && (pe_rows_per_t <= 0 || pe_T <= 0)) return set_error(-1, "vda_layernorm: pe needs rows_per_t and T");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return x_is_f32 ? launch_ln<float>(x, gamma, beta, out, out_nope, pe, rows, C, eps, tokens_per_frame, skip,
+                                     pe_rows_per_t, pe_T, st)
+                  : launch_ln<bf16>(x, gamma, beta, out, out_nope, pe, rows, C, eps, tokens_per_frame, skip,
+                                    pe_rows_per_t, pe_T, st);
+}
+
+int vda_groupnorm_nhwc(const void* x, int ldx, const float* gamma, const float* beta, void* out, double* stats_ws,
+                       int n, int hw, int C, float eps, void* stream) {
+  if (!x || !out || !stats_ws || C % 64 || n <= 0 || hw <= 0) return set_error(-1, "vda_groupnorm_nhwc: bad arguments (C%%64)");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = check_cuda(cudaMemsetAsync(stats_ws, 0, sizeof(double) * 64 * n, st), "groupnorm memset");
+  if (rc) return rc;
+  const int rows_per_block = 32;
+  dim3 grid((hw + rows_per_block - 1) / rows_per_block, n);
+  const int threads = C / 2 < 512 ? C / 2 : 512;
+  groupnorm_stats_kernel<<<grid, threads, 0, st>>>(static_cast<const bf16*>(x), stats_ws, hw, C, ldx, rows_per_block);
+  const long long total = static_cast<long long>(n) * hw * (C / 2);
+  groupnorm_apply_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(
+      static_cast<const bf16*>(x), stats_ws, gamma, beta, static_cast<bf16*>(out), hw, C, ldx, eps, total);
+  return check_cuda(cudaGetLastError(), "groupnorm launch");
+}
+
+int vda_patch_im2col(const float* x, void* a, int frames, int H, int W, int ldk, void* stream) {
+  if (!x || !a || H % 14 || W % 14 || ldk < 588 || ldk % 8) return set_error(-1, "vda_patch_im2col: bad arguments");
+  const int gh = H / 14, gw = W / 14;
+  patch_im2col_kernel<<<frames * gh * gw, 160, 0, static_cast<cudaStream_t>(stream)>>>(x, static_cast<bf16*>(a), H, W,
+                                                                                       gh, gw, ldk);
+  return check_cuda(cudaGetLastError(), "patch_im2col launch");
+}
+
+int vda_add_cls_pos(const float* patch, const float* cls, const float* pos, float* tokens, int frames, int hw, int D,
+                    void* stream) {
+  if (!patch || !cls || !pos || !tokens || D % 4) return set_error(-1, "vda_add_cls_pos: bad arguments");
+  const long long total = static_cast<long long>(frames) * (hw + 1) * (D / 4);
+  add_cls_pos_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      patch, cls, pos, tokens, hw, D, total);
+  return check_cuda(cudaGetLastError(), "add_cls_pos launch");
+}
+
+int vda_bilinear_nhwc(const void* x, int ldx, void* out, int ldo, int n, int h, int w, int H, int W, int C,
+                      void* stream) {
+  if (!x || !out || C % 8 || ldx % 8 || ldo % 8) return set_error(-1, "vda_bilinear_nhwc: bad arguments");
+  const float sy = H > 1 ? static_cast<float>(h - 1) / (H - 1) : 0.f;
+  const float sx = W > 1 ? static_cast<float>(w - 1) / (W - 1) : 0.f;
+  const long long total = static_cast<long long>(n) * H * W * (C / 8);
+  bilinear_nhwc_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const bf16*>(x), static_cast<bf16*>(out), h, w, H, W, C, ldx, ldo, sy, sx, total);
+  return check_cuda(cudaGetLastError(), "bilinear_nhwc launch");
+}
+
+int vda_bilinear_f32(const float* x, float* out, int n, int h, int w, int H, int W, int relu, void* stream) {
+  if (!x || !out) return set_error(-1, "vda_bilinear_f32: bad arguments");
+  const float sy = H > 1 ? static_cast<float>(h - 1) / (H - 1) : 0.f;
+  const float sx = W > 1 ? static_cast<float>(w - 1) / (W - 1) : 0.f;
+  const long long total = static_cast<long long>(n) * H * W;
+  bilinear_f32_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      x, out, h, w, H, W, sy, sx, relu, total);
+  return check_cuda(cudaGetLastError(), "bilinear_f32 launch");
+}
+
+int vda_im2col_s2(const void* x, void* a, int n, int h, int w, int C, void* stream) {
+  if (!x || !a || C % 8) return set_error(-1, "vda_im2col_s2: bad arguments");
+  const int ho = (h - 1) / 2 + 1, wo = (w - 1) / 2 + 1;
+  const long long total = static_cast<long long>(n) * ho * wo * 9 * (C / 8);
+  im2col_s2_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const bf16*>(x), static_cast<bf16*>(a), h, w, ho, wo, C, total);
+  return check_cuda(cudaGetLastError(), "im2col_s2 launch");
+}
+
+}  // extern "C"

@@ -1,0 +1,154 @@
+// Temporal attention core of the motion modules (motion_module/motion_module.py:242-321,
+// motion_module/attention.py:187-207): for every spatial token and each of the 8 heads,
+// softmax(q k^T / sqrt(hd)) v over the T <= 32 frames of the window.  The q/k/v projections and
+// to_out are plain GEMMs (gemm.cu); the "(b f) d c <-> (b d) f c" rearranges of the reference are
+// pure index math here: element (t, d, c) lives at row t*hw + d.
+//
+// One warp per (token, head): K and V rows staged in shared memory (broadcast reads), lane t owns
+// query frame t, the 32 scores and the softmax live in that lane's registers (no shuffles), the
+// output row is staged back through shared memory for coalesced 16-byte stores.
+#include <string.h>
+
+#include "common.cuh"
+#include "api_internal.h"
+#include "../../include/vda_b200.h"
+
+namespace vda {
+
+constexpr int kTWarps = 4;
+
+struct TemporalParams {
+  const bf16* q;
+  const bf16* k;
+  const bf16* v;
+  bf16* out;
+  int ldq, ldk, ldv, ldo;
+  int hw, heads, hd;
+  int Tq, Tk;
+  float scale;
+};
+
+__device__ __forceinline__ float2 bf2(uint32_t w) {
+  return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w));
+}
+
+__global__ void __launch_bounds__(kTWarps * 32) temporal_attn_kernel(const TemporalParams p) {
+  extern __shared__ __align__(16) uint8_t tsm[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int unit = blockIdx.x * kTWarps + warp;
+  if (unit >= p.hw * p.heads) return;
+  const int d = unit / p.heads, head = unit - d * p.heads;
+  const int hd = p.hd, chunks = hd >> 3;  // 16-byte chunks per row
+  const int q_stride = hd + 2;            // bf16 elements; odd word stride -> conflict-free per-lane rows
+  const int per_warp = 32 * q_stride * 2 + 2 * 32 * hd * 2;
+  uint8_t* base = tsm + warp * per_warp;
+  bf16* sK = reinterpret_cast<bf16*>(base);
+  bf16* sV = sK + 32 * hd;
+  bf16* sQ = sV + 32 * hd;
+
+  // cooperative 16-byte loads of the K, V (Tk rows) and Q (Tq rows) slices of this (token, head)
+  for (int i = lane; i < p.Tk * chunks; i += 32) {
+    const int t = i / chunks, c = i - t * chunks;
+    const long long row = static_cast<long long>(t) * p.hw + d;
+    const uint4 kk = __ldg(reinterpret_cast<const uint4*>(p.k + row * p.ldk + head * hd + c * 8));
+    const uint4 vv = __ldg(reinterpret_cast<const uint4*>(p.v + row * p.ldv + head * hd + c * 8));
+    *reinterpret_cast<uint4*>(sK + t * hd + c * 8) = kk;
+    *reinterpret_cast<uint4*>(sV + t * hd + c * 8) = vv;
+  }
+  for (int i = lane; i < p.Tq * chunks; i += 32) {
+    const int t = i / chunks, c = i - t * chunks;
+    const long long row = static_cast<long long>(t) * p.hw + d;
+    const uint4 qq = __ldg(reinterpret_cast<const uint4*>(p.q + row * p.ldq + head * hd + c * 8));
+    uint32_t* dst = reinterpret_cast<uint32_t*>(sQ + t * q_stride + c * 8);
+    dst[0] = qq.x, dst[1] = qq.y, dst[2] = qq.z, dst[3] = qq.w;
+  }
+  __syncwarp();
+
+  const int t = lane;  // query frame of this lane (idle if >= Tq)
+  float s[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) s[j] = 0.f;
+  const uint32_t* qrow = reinterpret_cast<const uint32_t*>(sQ + (t < p.Tq ? t : 0) * q_stride);
+  for (int c = 0; c < chunks; ++c) {
+    const float2 q0 = bf2(qrow[c * 4]), q1 = bf2(qrow[c * 4 + 1]), q2 = bf2(qrow[c * 4 + 2]), q3 = bf2(qrow[c * 4 + 3]);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      if (j < p.Tk) {
+        const uint4 kk = *reinterpret_cast<const uint4*>(sK + j * hd + c * 8);
+        const float2 k0 = bf2(kk.x), k1 = bf2(kk.y), k2 = bf2(kk.z), k3 = bf2(kk.w);
+        s[j] += q0.x * k0.x + q0.y * k0.y + q1.x * k1.x + q1.y * k1.y + q2.x * k2.x + q2.y * k2.y + q3.x * k3.x +
+                q3.y * k3.y;
+      }
+    }
+  }
+  float m = -INFINITY;
+#pragma unroll
+  for (int j = 0; j < 32; ++j)
+    if (j < p.Tk) m = fmaxf(m, s[j] * p.scale);
+  float l = 0.f;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    s[j] = (j < p.Tk) ? __expf(s[j] * p.scale - m) : 0.f;
+    l += s[j];
+  }
+  const float inv = 1.f / l;
+  __syncwarp();  // every lane is done reading its q row before it is overwritten with the output
+  uint32_t* orow = reinterpret_cast<uint32_t*>(sQ + (t < p.Tq ? t : 0) * q_stride);
+  for (int c = 0; c < chunks; ++c) {
+    float o[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o[i] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      if (j < p.Tk) {
+        const uint4 vv = *reinterpret_cast<const uint4*>(sV + j * hd + c * 8);
+        const float2 v0 = bf2(vv.x), v1 = bf2(vv.y), v2 = bf2(vv.z), v3 = bf2(vv.w);
+        o[0] += s[j] * v0.x, o[1] += s[j] * v0.y, o[2] += s[j] * v1.x, o[3] += s[j] * v1.y;
+        o[4] += s[j] * v2.x, o[5] += s[j] * v2.y, o[6] += s[j] * v3.x, o[7] += s[j] * v3.y;
+      }
+    }
+    if (t < p.Tq) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const __nv_bfloat162 h = __floats2bfloat162_rn(o[2 * i] * inv, o[2 * i + 1] * inv);
+        orow[c * 4 + i] = *reinterpret_cast<const uint32_t*>(&h);
+      }
+    }
+  }
+  __syncwarp();
+  for (int i = lane; i < p.Tq * chunks; i += 32) {
+    const int tt = i / chunks, c = i - tt * chunks;
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(sQ + tt * q_stride + c * 8);
+    const long long row = static_cast<long long>(tt) * p.hw + d;
+    *reinterpret_cast<uint4*>(p.out + row * p.ldo + head * hd + c * 8) = make_uint4(src[0], src[1], src[2], src[3]);
+  }
+}
+
+}  // namespace vda
+
+using namespace vda;
+
+extern "C" int vda_temporal_attn(const void* q, int ldq, const void* k, int ldk, const void* v, int ldv, void* out,
+                                 int ldo, int hw, int heads, int head_dim, int Tq, int Tk, void* stream) {
+  if (!q || !k || !v || !out || hw <= 0 || heads <= 0 || head_dim % 8 || head_dim > 128 || Tq < 1 || Tq > 32 || Tk < 1 ||
+      Tk > 32 || ldq % 8 || ldk % 8 || ldv % 8 || ldo % 8)
+    return set_error(-1, "vda_temporal_attn: bad arguments (head_dim%%8, T<=32, ld%%8)");
+  TemporalParams p;
+  p.q = static_cast<const bf16*>(q), p.k = static_cast<const bf16*>(k), p.v = static_cast<const bf16*>(v);
+  p.out = static_cast<bf16*>(out);
+  p.ldq = ldq, p.ldk = ldk, p.ldv = ldv, p.ldo = ldo;
+  p.hw = hw, p.heads = heads, p.hd = head_dim, p.Tq = Tq, p.Tk = Tk;
+  p.scale = 1.0f / sqrtf(static_cast<float>(head_dim));
+  const int per_warp = 32 * (head_dim + 2) * 2 + 2 * 32 * head_dim * 2;
+  const int smem = per_warp * kTWarps;
+  static int configured = 0;
+  if (smem > configured) {
+    int rc = check_cuda(cudaFuncSetAttribute(temporal_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 101376),
+                        "temporal smem attribute");
+    if (rc) return rc;
+    configured = 101376;
+  }
+  const int units = hw * heads;
+  temporal_attn_kernel<<<(units + kTWarps - 1) / kTWarps, kTWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  return check_cuda(cudaGetLastError(), "temporal_attn launch");
+}

@@ -58,6 +58,19 @@ def _declare(lib):
         "vda_num_sms": [],
         "vda_gemm_bf16": [vp, i, vp, i, i, i, i, ep, vp],
         "vda_conv3x3_nhwc": [vp, i, vp, i, i, i, i, i, ep, vp],
+        "vda_flash_attn_fwd": [vp, vp, vp, i, i, i, i, vp],
+        "vda_layernorm": [vp, i, vp, vp, vp, vp, vp, i, i, f, i, i, i, i, vp],
+        "vda_groupnorm_nhwc": [vp, i, vp, vp, vp, vp, i, i, i, f, vp],
+        "vda_patch_im2col": [vp, vp, i, i, i, i, vp],
+        "vda_add_cls_pos": [vp, vp, vp, vp, i, i, i, vp],
+        "vda_bilinear_nhwc": [vp, i, vp, i, i, i, i, i, i, i, vp],
+        "vda_bilinear_f32": [vp, vp, i, i, i, i, i, i, vp],
+        "vda_im2col_s2": [vp, vp, i, i, i, i, vp],
+        "vda_temporal_attn": [vp, i, vp, i, vp, i, vp, i, i, i, i, i, i, vp],
+        "vda_lsq_accum": [vp, vp, C.c_longlong, vp, vp],
+        "vda_lsq_solve": [vp, vp, i, vp],
+        "vda_affine_clamp": [vp, vp, C.c_longlong, vp, vp],
+        "vda_affine_clamp_blend": [vp, vp, C.c_longlong, i, vp, vp],
     }
     for name, args in sig.items():
         fn = getattr(lib, name)
@@ -125,3 +138,62 @@ def gemm(a, w, epi, M=None, N=None, K=None, lda=None, ldw=None):
 def conv3x3(x, w, epi, n, H, W, Cin, Cout, ldx=None):
     ldx = Cin if ldx is None else ldx
     check(load().vda_conv3x3_nhwc(ptr(x), ldx, ptr(w), n, H, W, Cin, Cout, C.byref(epi), stream_ptr()))
+
+
+def flash_attn(qk, vt, out, frames, S, heads, s_pad):
+    check(load().vda_flash_attn_fwd(ptr(qk), ptr(vt), ptr(out), frames, S, heads, s_pad, stream_ptr()))
+
+
+def layernorm(x, gamma, beta, out, eps, rows=None, C=None, tokens_per_frame=0, skip=0, pe=None, out_nope=None,
+              pe_rows_per_t=0, pe_T=0):
+    rows = x.shape[0] if rows is None else rows
+    C = x.shape[-1] if C is None else C
+    check(load().vda_layernorm(ptr(x), int(x.dtype == torch.float32), ptr(gamma), ptr(beta), ptr(out), ptr(out_nope),
+                               ptr(pe), rows, C, eps, tokens_per_frame, skip, pe_rows_per_t, pe_T, stream_ptr()))
+
+
+def groupnorm_nhwc(x, gamma, beta, out, stats_ws, n, hw, C, eps, ldx=None):
+    check(load().vda_groupnorm_nhwc(ptr(x), C if ldx is None else ldx, ptr(gamma), ptr(beta), ptr(out), ptr(stats_ws),
+                                    n, hw, C, eps, stream_ptr()))
+
+
+def patch_im2col(x, a, frames, H, W, ldk):
+    check(load().vda_patch_im2col(ptr(x), ptr(a), frames, H, W, ldk, stream_ptr()))
+
+
+def add_cls_pos(patch, cls, pos, tokens, frames, hw, D):
+    check(load().vda_add_cls_pos(ptr(patch), ptr(cls), ptr(pos), ptr(tokens), frames, hw, D, stream_ptr()))
+
+
+def bilinear_nhwc(x, out, n, h, w, H, W, C, ldx=None, ldo=None):
+    check(load().vda_bilinear_nhwc(ptr(x), C if ldx is None else ldx, ptr(out), C if ldo is None else ldo,
+                                   n, h, w, H, W, C, stream_ptr()))
+
+
+def bilinear_f32(x, out, n, h, w, H, W, relu=False):
+    check(load().vda_bilinear_f32(ptr(x), ptr(out), n, h, w, H, W, int(relu), stream_ptr()))
+
+
+def im2col_s2(x, a, n, h, w, C):
+    check(load().vda_im2col_s2(ptr(x), ptr(a), n, h, w, C, stream_ptr()))
+
+
+def temporal_attn(q, ldq, k, ldk, v, ldv, out, ldo, hw, heads, head_dim, Tq, Tk):
+    check(load().vda_temporal_attn(ptr(q), ldq, ptr(k), ldk, ptr(v), ldv, ptr(out), ldo, hw, heads, head_dim, Tq, Tk,
+                                   stream_ptr()))
+
+
+def lsq_accum(pred, target, n, sums5):
+    check(load().vda_lsq_accum(ptr(pred), ptr(target), n, ptr(sums5), stream_ptr()))
+
+
+def lsq_solve(sums5, scale_shift, metric=False):
+    check(load().vda_lsq_solve(ptr(sums5), ptr(scale_shift), int(metric), stream_ptr()))
+
+
+def affine_clamp(src, dst, n, scale_shift):
+    check(load().vda_affine_clamp(ptr(src), ptr(dst), n, ptr(scale_shift), stream_ptr()))
+
+
+def affine_clamp_blend(pre, post, per_frame, frames, scale_shift):
+    check(load().vda_affine_clamp_blend(ptr(pre), ptr(post), per_frame, frames, ptr(scale_shift), stream_ptr()))
