@@ -1,0 +1,124 @@
+"""Whole-window and driver parity of the CUDA path against the oracle / reference golden vectors.
+
+Tolerance (BASELINE.json north_star): the BF16 path must agree with the reference FP32 output within
+a mean absolute-relative depth error of 1e-2 (definition: benchmark/eval/metric.py:3-13)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import make_golden as G
+from oracle import refload
+from oracle import vda_oracle as O
+
+pytestmark = pytest.mark.gpu
+ABSREL_TOL = 1e-2
+
+
+def absrel(got, want):
+    got, want = np.asarray(got, np.float64), np.asarray(want, np.float64)
+    m = want > 1e-6
+    return float(np.mean(np.abs(got[m] - want[m]) / want[m]))
+
+
+def build(arch, seed=0, metric=False):
+    from video_depth_anything.video_depth import VideoDepthAnything
+
+    cfg = O.ARCH[arch]
+    m = VideoDepthAnything(encoder=arch, features=cfg["features"], out_channels=cfg["out_channels"], metric=metric)
+    sd = refload.seeded_state_dict(arch, seed)
+    m.load_state_dict(sd, strict=True)
+    return m.to("cuda").eval(), sd
+
+
+@pytest.fixture(autouse=True)
+def _exact_fp32_oracle():
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    yield
+
+
+@pytest.mark.parametrize("name", sorted(G.FORWARD_CASES))
+def test_forward_vs_reference_golden(name):
+    arch, T, H, W = G.FORWARD_CASES[name]
+    model, _ = build(arch)
+    x = G.window_input(T, H, W).cuda()
+    with torch.no_grad():
+        got = model(x).cpu().numpy()
+    want = np.load(os.path.join(G.GOLDEN_DIR, name + ".npz"))["depth"]
+    assert got.shape == want.shape and np.isfinite(got).all() and (got >= 0).all()
+    e = absrel(got, want)
+    print(f"{name}: absrel {e:.2e}")
+    assert e <= ABSREL_TOL
+
+
+def test_stagewise_vits_diagnostics():
+    """Encoder taps and head checked separately so a failure names the stage."""
+    arch, T, H, W = "vits", 8, 70, 98
+    model, sd = build(arch)
+    sd_gpu = {k: v.cuda() for k, v in sd.items()}
+    x = G.window_input(T, H, W, seed=7).cuda()
+    eng = model.engine()
+    ws = eng._ws(("diag", T, H, W))
+    with torch.no_grad():
+        taps = eng.encoder(x[0], ws)
+        want = O.encoder_taps(sd_gpu, x[0], arch)
+        for i, (g, w_) in enumerate(zip(taps, want)):
+            err = (g.float().view_as(w_) - w_).abs().max().item() / w_.abs().max().item()
+            print(f"tap{i}: rel max err {err:.2e}")
+            assert err < 5e-2
+        # head on the ORACLE's taps (rounded to bf16) isolates the head kernels
+        taps_b = [w_.reshape(-1, w_.shape[-1]).bfloat16().contiguous() for w_ in want]
+        depth = eng.head(taps_b, H // 14, W // 14, T, ws).cpu().numpy()
+        ref, _ = O.head_forward(sd_gpu, want, H // 14, W // 14, T)
+        e = absrel(depth, ref[:, 0].cpu().numpy())
+        print(f"head: absrel {e:.2e}")
+        assert e <= ABSREL_TOL
+
+
+@pytest.mark.parametrize("arch,T,H,W", [("vits", 32, 518, 518), ("vitb", 8, 518, 924), ("vitl", 32, 518, 518)])
+def test_full_size_window_vs_oracle_on_gpu(arch, T, H, W):
+    """BASELINE configs 2/4 shapes: oracle evaluated in fp32 on the same GPU (TF32 off) as checker."""
+    model, sd = build(arch)
+    x = G.window_input(T, H, W, seed=3).cuda()
+    with torch.no_grad():
+        got = model(x)[0]
+        sd_gpu = {k: v.cuda() for k, v in sd.items()}
+        want = torch.cat([O.forward(sd_gpu, x[:, :T], arch)[0]]) if T <= 32 else None
+    e = absrel(got.cpu().numpy(), want.cpu().numpy())
+    print(f"{arch} {T}x{H}x{W}: absrel {e:.2e}, range {want.min().item():.3f}..{want.max().item():.3f}")
+    assert e <= ABSREL_TOL
+
+
+def test_video_driver_vs_reference_golden():
+    v = G.VIDEO_CASE
+    frames = G.video_frames(v["n"], v["h"], v["w"])
+    gold = np.load(os.path.join(G.GOLDEN_DIR, "video_vits_46x44x60.npz"))
+    model, _ = build(v["arch"])
+    got, fps = model.infer_video_depth(frames, 24, input_size=v["input_size"], device="cuda")
+    assert fps == 24 and got.shape == gold["offline"].shape and got.dtype == np.float32
+    e = absrel(got, gold["offline"])
+    print(f"driver: absrel {e:.2e}")
+    assert e <= ABSREL_TOL
+    model_m, _ = build(v["arch"], metric=True)
+    got_m, _ = model_m.infer_video_depth(frames, 24, input_size=v["input_size"], device="cuda")
+    e = absrel(got_m, gold["metric"])
+    print(f"driver(metric): absrel {e:.2e}")
+    assert e <= ABSREL_TOL
+
+
+def test_alignment_scan_matches_oracle_exactly_on_same_raw_depth():
+    """Feed identical raw per-window depth to the GPU scan and to the oracle's numpy scan."""
+    from vda_b200.video_depth import align_windows_device
+    import vda_b200.lib as L
+
+    L.init()
+    rng = np.random.default_rng(1)
+    n_win, h, w = 4, 33, 47
+    base = rng.uniform(1, 6, (h, w)).astype(np.float32)
+    raw = np.stack([base * rng.uniform(0.5, 2) + rng.uniform(-0.5, 0.5) + rng.normal(0, 0.05, (h, w))
+                    for _ in range(n_win * 32)]).astype(np.float32)
+    want = np.stack(O.align_windows([raw[i].copy() for i in range(raw.shape[0])]))
+    got = align_windows_device(torch.from_numpy(raw).cuda()).cpu().numpy()
+    np.testing.assert_allclose(got, want, rtol=2e-4, atol=2e-4)

@@ -91,7 +91,7 @@ __global__ void groupnorm_stats_kernel(const bf16* __restrict__ x, double* __res
   const int img = blockIdx.y;
   const int r0 = blockIdx.x * rows_per_block;
   const int r1 = min(hw, r0 + rows_per_block);
-  if (threadIdx.x < 64) sh[threadIdx.x] = 0.f;
+  for (int i = threadIdx.x; i < 64; i += blockDim.x) sh[i] = 0.f;
   __syncthreads();
   const int cg = C / 32;
   for (int c = threadIdx.x * 2; c < C; c += blockDim.x * 2) {
@@ -107,7 +107,8 @@ __global__ void groupnorm_stats_kernel(const bf16* __restrict__ x, double* __res
     atomicAdd(&sh[2 * g + 1], ss);
   }
   __syncthreads();
-  if (threadIdx.x < 64) atomicAdd(&stats[static_cast<long long>(img) * 64 + threadIdx.x], static_cast<double>(sh[threadIdx.x]));
+  for (int i = threadIdx.x; i < 64; i += blockDim.x)
+    atomicAdd(&stats[static_cast<long long>(img) * 64 + i], static_cast<double>(sh[i]));
 }
 
 __global__ void groupnorm_apply_kernel(const bf16* __restrict__ x, const double* __restrict__ stats,

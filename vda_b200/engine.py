@@ -1,0 +1,311 @@
+"""Window executor: VideoDepthAnything.forward (video_depth.py:61-68) as a fixed sequence of
+libvda_b200 kernel launches on the current CUDA stream.
+
+Data layout: activations are row-major [rows, channels] -- tokens
+[frame*S + s, D] in the encoder, NHWC pixels [((frame*h)+y)*w + x, C] in the head -- bf16, with the
+two residual streams (ViT tokens, motion-module hidden states) kept in fp32.  torch only owns the
+buffers (one workspace per input shape, reused for every window); no torch op runs per window.
+"""
+import torch
+
+from . import lib as L
+from . import packing as P
+from .modules import ARCH, PATCH, POS_GRID
+
+
+def _pad(n, m):
+    return (n + m - 1) // m * m
+
+
+class Workspace:
+    """Named device buffers, allocated on first use and reused for every window of the same shape."""
+
+    def __init__(self, device):
+        self.device = device
+        self.bufs = {}
+
+    def get(self, name, shape, dtype=torch.bfloat16, zero=False):
+        key = (name, tuple(shape), dtype)
+        t = self.bufs.get(key)
+        if t is None:
+            t = (torch.zeros if zero else torch.empty)(tuple(shape), dtype=dtype, device=self.device)
+            self.bufs[key] = t
+        return t
+
+    def nbytes(self):
+        return sum(t.numel() * t.element_size() for t in self.bufs.values())
+
+
+class _Motion:
+    """Packed weights of one TemporalModule (motion_module.py:68-134)."""
+
+    def __init__(self, mod, dev):
+        tt = mod.temporal_transformer
+        blk = tt.transformer_blocks[0]
+        self.C = tt.proj_in.weight.shape[0]
+        self.gn_w, self.gn_b = P.vec(tt.norm.weight, dev), P.vec(tt.norm.bias, dev)
+        self.w_in, self.b_in = P.linear(tt.proj_in.weight, tt.proj_in.bias, device=dev)
+        self.w_out, self.b_out = P.linear(tt.proj_out.weight, tt.proj_out.bias, device=dev)
+        self.attn = []
+        for a, n in zip(blk.attention_blocks, blk.norms):
+            wqkv, _ = P.linear(torch.cat([a.to_q.weight, a.to_k.weight, a.to_v.weight], 0), device=dev)
+            wo, bo = P.linear(a.to_out[0].weight, a.to_out[0].bias, device=dev)
+            self.attn.append(dict(ln_w=P.vec(n.weight, dev), ln_b=P.vec(n.bias, dev), wqkv=wqkv, wo=wo, bo=bo,
+                                  pe=a.pos_encoder.pe.detach().float().reshape(-1, self.C).contiguous().to(dev)))
+        self.ffn_w, self.ffn_b = P.vec(blk.ff_norm.weight, dev), P.vec(blk.ff_norm.bias, dev)
+        self.w_geglu, self.b_geglu = P.geglu(blk.ff.net[0].proj.weight, blk.ff.net[0].proj.bias, dev)
+        self.w_ff2, self.b_ff2 = P.linear(blk.ff.net[2].weight, blk.ff.net[2].bias, device=dev)
+
+
+class _Fusion:
+    def __init__(self, mod, dev):
+        self.rcu = []
+        for u in (mod.resConfUnit1, mod.resConfUnit2):
+            w1, b1 = P.conv3x3(u.conv1.weight, u.conv1.bias, device=dev)
+            w2, b2 = P.conv3x3(u.conv2.weight, u.conv2.bias, device=dev)
+            self.rcu.append((w1, b1, w2, b2))
+        self.w_out, self.b_out = P.linear(mod.out_conv.weight, mod.out_conv.bias, device=dev)
+
+
+class Packed:
+    """All kernel-layout weights of one VideoDepthAnything module."""
+
+    def __init__(self, model, dev):
+        enc, head = model.pretrained, model.head
+        self.arch = model.encoder
+        cfg = ARCH[self.arch]
+        self.D, self.heads, self.taps = cfg["dim"], cfg["heads"], cfg["taps"]
+        D = self.D
+        wp = torch.zeros(D, 592, dtype=torch.bfloat16, device=dev)
+        wp[:, :588] = enc.patch_embed.proj.weight.detach().reshape(D, 588).to(dev).bfloat16()
+        self.w_patch, self.b_patch = wp, P.vec(enc.patch_embed.proj.bias, dev)
+        self.cls = P.vec(enc.cls_token, dev)
+        self.pos_embed = enc.pos_embed.detach().float().to(dev)
+        self.pos_cache = {}
+        self.blocks = []
+        for b in enc.blocks:
+            wqkv, bqkv = P.linear(b.attn.qkv.weight, b.attn.qkv.bias, device=dev)
+            wpr, bpr = P.linear(b.attn.proj.weight, b.attn.proj.bias, device=dev)
+            w1, b1 = P.linear(b.mlp.fc1.weight, b.mlp.fc1.bias, device=dev)
+            w2, b2 = P.linear(b.mlp.fc2.weight, b.mlp.fc2.bias, device=dev)
+            self.blocks.append(dict(
+                n1w=P.vec(b.norm1.weight, dev), n1b=P.vec(b.norm1.bias, dev), wqkv=wqkv, bqkv=bqkv, wproj=wpr, bproj=bpr,
+                g1=P.vec(b.ls1.gamma, dev), n2w=P.vec(b.norm2.weight, dev), n2b=P.vec(b.norm2.bias, dev),
+                w1=w1, b1=b1, w2=w2, b2=b2, g2=P.vec(b.ls2.gamma, dev)))
+        self.norm_w, self.norm_b = P.vec(enc.norm.weight, dev), P.vec(enc.norm.bias, dev)
+        # ---- head
+        self.F = head.features
+        self.oc = list(head.out_channels)
+        self.ocp = [_pad(c, 64) for c in self.oc]      # channel counts as 3x3-conv inputs
+        self.proj = [P.linear(m.weight, m.bias, device=dev) for m in head.projects]
+        r0, r1, r3 = head.resize_layers[0], head.resize_layers[1], head.resize_layers[3]
+        self.ct0 = P.conv_transpose(r0.weight, r0.bias, device=dev)
+        self.ct1 = P.conv_transpose(r1.weight, r1.bias, device=dev)
+        self.w_rs3, self.b_rs3 = P.conv3x3(r3.weight, r3.bias, cin_pad=8, device=dev)   # explicit im2col: no cin pad
+        sc = head.scratch
+        self.rn = [P.conv3x3(getattr(sc, f"layer{i + 1}_rn").weight, None, device=dev)[0] for i in range(4)]
+        self.fusion = {i: _Fusion(getattr(sc, f"refinenet{i}"), dev) for i in range(1, 5)}
+        self.F2p = _pad(self.F // 2, 64)
+        self.w_oc1, self.b_oc1 = P.conv3x3(sc.output_conv1.weight, sc.output_conv1.bias, cout_pad=64, device=dev)
+        self.w_oc2, self.b_oc2 = P.conv3x3(sc.output_conv2[0].weight, sc.output_conv2[0].bias, device=dev)
+        self.w_last = P.vec(sc.output_conv2[2].weight, dev)
+        self.b_last = float(sc.output_conv2[2].bias.detach().float().item())
+        self.motion = [_Motion(m, dev) for m in head.motion_modules]
+
+    def pos_for(self, gh, gw):
+        """Positional table [1+gh*gw, D] f32 for a gh x gw grid (dinov2.py:179-210).  The bicubic
+        resample of the 37x37 table for non-square inputs happens once per shape and is cached."""
+        key = (gh, gw)
+        if key not in self.pos_cache:
+            pe = self.pos_embed
+            if gh == POS_GRID and gw == POS_GRID:
+                tab = pe[0]
+            else:
+                D = pe.shape[-1]
+                grid = pe[:, 1:].reshape(1, POS_GRID, POS_GRID, D).permute(0, 3, 1, 2)
+                grid = torch.nn.functional.interpolate(
+                    grid, scale_factor=((gh + 0.1) / POS_GRID, (gw + 0.1) / POS_GRID), mode="bicubic", antialias=False)
+                assert grid.shape[-2:] == (gh, gw)
+                tab = torch.cat([pe[0, :1], grid.permute(0, 2, 3, 1).reshape(-1, D)], 0)
+            self.pos_cache[key] = tab.contiguous()
+        return self.pos_cache[key]
+
+
+class Engine:
+    """Executes the window forward for one model on one device."""
+
+    def __init__(self, model, device):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise L.VdaError("vda_b200 runs on sm_100a GPUs only; there is no CPU path")
+        L.init(self.device)
+        with torch.cuda.device(self.device):
+            self.w = Packed(model, self.device)
+        self.ws = {}
+
+    def _ws(self, key):
+        if key not in self.ws:
+            self.ws[key] = Workspace(self.device)
+        return self.ws[key]
+
+    # ------------------------------------------------------------------ encoder
+    def encoder(self, x, ws):
+        """x f32 [T,3,H,W] -> 4 taps, each bf16 [T*gh*gw, D] (final-norm applied, cls dropped)."""
+        w = self.w
+        T, _, H, W = x.shape
+        gh, gw = H // PATCH, W // PATCH
+        hw, D, heads = gh * gw, w.D, w.heads
+        S, M = hw + 1, T * (hw + 1)
+        spad = _pad(S, 8)
+        a = ws.get("patch_a", (T * hw, 592))
+        L.patch_im2col(x, a, T, H, W, 592)
+        patch = ws.get("patch_f32", (T * hw, D), torch.float32)
+        L.gemm(a, w.w_patch, L.make_epilogue(bias=w.b_patch, out_f32=patch, ldo=D), K=588)
+        tok = ws.get("tokens", (M, D), torch.float32)
+        L.add_cls_pos(patch, w.cls, w.pos_for(gh, gw), tok, T, hw, D)
+        xn = ws.get("xn", (M, D))
+        qk = ws.get("qk", (M, 2 * D))
+        vt = ws.get("vt", (T * heads, 64, spad), zero=True)
+        ao = ws.get("attn_out", (M, D))
+        h1 = ws.get("mlp_h", (M, 4 * D))
+        taps = []
+        for i, b in enumerate(w.blocks):
+            L.layernorm(tok, b["n1w"], b["n1b"], xn, 1e-6)
+            L.gemm(xn, b["wqkv"], L.make_epilogue(bias=b["bqkv"], out=qk, ldo=2 * D, store_mode=L.ST_QKV,
+                                                  qkv=(vt, D, heads, S, spad)))
+            L.flash_attn(qk, vt, ao, T, S, heads, spad)
+            L.gemm(ao, b["wproj"], L.make_epilogue(bias=b["bproj"], scale=b["g1"], res_f32=tok, out_f32=tok, ldo=D))
+            L.layernorm(tok, b["n2w"], b["n2b"], xn, 1e-6)
+            L.gemm(xn, b["w1"], L.make_epilogue(bias=b["b1"], out=h1, ldo=4 * D, act=L.ACT_GELU))
+            L.gemm(h1, b["w2"], L.make_epilogue(bias=b["b2"], scale=b["g2"], res_f32=tok, out_f32=tok, ldo=D))
+            if i in w.taps:
+                t = ws.get(f"tap{len(taps)}", (T * hw, D))
+                L.layernorm(tok, w.norm_w, w.norm_b, t, 1e-6, tokens_per_frame=S, skip=1)
+                taps.append(t)
+        return taps
+
+    # ------------------------------------------------------------------ motion module
+    def motion(self, idx, x, T, hw, ws, out, out_relu=None, stream_ctx=None):
+        """x, out: NHWC bf16 [T*hw, C].  motion_module.py:102-134 / :172-189 / :242-321."""
+        m = self.w.motion[idx]
+        C, rows = m.C, T * hw
+        tag = f"mm{idx}_"
+        gn = ws.get(tag + "gn", (rows, C))
+        stats = ws.get(tag + "gnstats", (64 * T,), torch.float64)
+        L.groupnorm_nhwc(x, m.gn_w, m.gn_b, gn, stats, T, hw, C, 1e-6)
+        h = ws.get(tag + "h", (rows, C), torch.float32)
+        L.gemm(gn, m.w_in, L.make_epilogue(bias=m.b_in, out_f32=h, ldo=C))
+        n = ws.get(tag + "n", (rows, C))
+        o = ws.get(tag + "o", (rows, C))
+        for a_i, a in enumerate(m.attn):
+            if stream_ctx is None:
+                qkv = ws.get(tag + "qkv", (rows, 3 * C))
+                L.layernorm(h, a["ln_w"], a["ln_b"], n, 1e-5, pe=a["pe"], pe_rows_per_t=hw, pe_T=32)
+                L.gemm(n, a["wqkv"], L.make_epilogue(out=qkv, ldo=3 * C))
+                L.temporal_attn(qkv, 3 * C, qkv[:, C:], 3 * C, qkv[:, 2 * C:], 3 * C, o, C, hw, 8, C // 8, T, T)
+            else:
+                stream_ctx.attend(self, idx, a_i, a, h, n, o, hw, C, ws)
+            L.gemm(o, a["wo"], L.make_epilogue(bias=a["bo"], res_f32=h, out_f32=h, ldo=C))
+        L.layernorm(h, m.ffn_w, m.ffn_b, n, 1e-5)
+        g = ws.get(tag + "geglu", (rows, 4 * C))
+        L.gemm(n, m.w_geglu, L.make_epilogue(bias=m.b_geglu, out=g, ldo=4 * C, act=L.ACT_GEGLU))
+        hb = ws.get(tag + "hb", (rows, C))
+        L.gemm(g, m.w_ff2, L.make_epilogue(bias=m.b_ff2, res_f32=h, out=hb, ldo=C))
+        L.gemm(hb, m.w_out, L.make_epilogue(bias=m.b_out, res1=x, out=out, out_relu=out_relu, ldo=C))
+        return out
+
+    # ------------------------------------------------------------------ DPT head
+    def _fusion(self, idx, ws, T, h, w_, x0, skip, skip_relu, size):
+        """FeatureFusionBlock (util/blocks.py:135-162) on NHWC bf16 maps of h x w_ pixels.
+        x0: first input (None for refinenet4, whose only input arrives as skip/skip_relu);
+        skip/skip_relu: layerN_rn output and its rectified copy.  The 1x1 out_conv is applied BEFORE
+        the bilinear upsample (both linear, interpolation weights sum to 1 => same result, 1/4 FLOPs)."""
+        f = self.w.fusion[idx]
+        Fc = self.w.F
+        rows = T * h * w_
+        tag = f"rf{idx}_"
+        t = ws.get(tag + "t", (rows, Fc))
+        if x0 is not None:
+            w1, b1, w2, b2 = f.rcu[0]
+            L.conv3x3(skip_relu, w1, L.make_epilogue(bias=b1, out=t, ldo=Fc, act=L.ACT_RELU), T, h, w_, Fc, Fc)
+            s = ws.get(tag + "s", (rows, Fc))
+            sr = ws.get(tag + "sr", (rows, Fc))
+            L.conv3x3(t, w2, L.make_epilogue(bias=b2, res1=skip, res2=x0, out=s, out_relu=sr, ldo=Fc), T, h, w_, Fc, Fc)
+        else:
+            s, sr = skip, skip_relu
+        w1, b1, w2, b2 = f.rcu[1]
+        L.conv3x3(sr, w1, L.make_epilogue(bias=b1, out=t, ldo=Fc, act=L.ACT_RELU), T, h, w_, Fc, Fc)
+        u = ws.get(tag + "u", (rows, Fc))
+        L.conv3x3(t, w2, L.make_epilogue(bias=b2, res1=s, out=u, ldo=Fc), T, h, w_, Fc, Fc)
+        v = ws.get(tag + "v", (rows, Fc))
+        L.gemm(u, f.w_out, L.make_epilogue(bias=f.b_out, out=v, ldo=Fc))
+        H2, W2 = size
+        up = ws.get(tag + "up", (T * H2 * W2, Fc))
+        L.bilinear_nhwc(v, up, T, h, w_, H2, W2, Fc)
+        return up
+
+    def head(self, taps, gh, gw, T, ws, stream_ctx=None):
+        """DPTHeadTemporal.forward (dpt_temporal.py:53-125) -> depth f32 [T, 14gh, 14gw]."""
+        w = self.w
+        Fc, oc, ocp, hw = w.F, w.oc, w.ocp, gh * gw
+        rows = T * hw
+        pr = []
+        for i in range(4):
+            wk, bk = w.proj[i]
+            p = ws.get(f"proj{i}", (rows, wk.shape[0]))
+            L.gemm(taps[i], wk, L.make_epilogue(bias=bk, out=p, ldo=wk.shape[0]))
+            pr.append(p)
+        wk, bk, s, cop = w.ct0
+        l1 = ws.get("layer1", (T * 16 * hw, cop))
+        L.gemm(pr[0], wk, L.make_epilogue(bias=bk, out=l1, ldo=cop, store_mode=L.ST_CONVT, ct=(s, cop, gh, gw)), K=oc[0])
+        wk, bk, s, cop = w.ct1
+        l2 = ws.get("layer2", (T * 4 * hw, cop))
+        L.gemm(pr[1], wk, L.make_epilogue(bias=bk, out=l2, ldo=cop, store_mode=L.ST_CONVT, ct=(s, cop, gh, gw)), K=oc[1])
+        gh4, gw4 = (gh - 1) // 2 + 1, (gw - 1) // 2 + 1
+        hw4 = gh4 * gw4
+        col = ws.get("rs3_col", (T * hw4, 9 * oc[3]))
+        L.im2col_s2(pr[3], col, T, gh, gw, oc[3])
+        l4 = ws.get("layer4", (T * hw4, oc[3]))
+        L.gemm(col, w.w_rs3, L.make_epilogue(bias=w.b_rs3, out=l4, ldo=oc[3]))
+        l3m = self.motion(0, pr[2], T, hw, ws, ws.get("layer3m", (rows, oc[2])), stream_ctx=stream_ctx)
+        l4m = self.motion(1, l4, T, hw4, ws, ws.get("layer4m", (T * hw4, oc[3])), stream_ctx=stream_ctx)
+
+        def rn(i, src, n_h, n_w, cin):
+            r = ws.get(f"rn{i}", (T * n_h * n_w, Fc))
+            rr = ws.get(f"rn{i}r", (T * n_h * n_w, Fc))
+            L.conv3x3(src, w.rn[i], L.make_epilogue(out=r, out_relu=rr, ldo=Fc), T, n_h, n_w, cin, Fc)
+            return r, rr
+
+        r1, r1r = rn(0, l1, 4 * gh, 4 * gw, ocp[0])
+        r2, r2r = rn(1, l2, 2 * gh, 2 * gw, ocp[1])
+        r3, r3r = rn(2, l3m, gh, gw, ocp[2])
+        r4, r4r = rn(3, l4m, gh4, gw4, ocp[3])
+        p4 = self._fusion(4, ws, T, gh4, gw4, None, r4, r4r, (gh, gw))
+        p4m = self.motion(2, p4, T, hw, ws, ws.get("path4m", (rows, Fc)), stream_ctx=stream_ctx)
+        p3 = self._fusion(3, ws, T, gh, gw, p4m, r3, r3r, (2 * gh, 2 * gw))
+        p3m = self.motion(3, p3, T, 4 * hw, ws, ws.get("path3m", (T * 4 * hw, Fc)), stream_ctx=stream_ctx)
+        p2 = self._fusion(2, ws, T, 2 * gh, 2 * gw, p3m, r2, r2r, (4 * gh, 4 * gw))
+        p1 = self._fusion(1, ws, T, 4 * gh, 4 * gw, p2, r1, r1r, (8 * gh, 8 * gw))
+        o1 = ws.get("out1", (T * 64 * hw, w.F2p))
+        L.conv3x3(p1, w.w_oc1, L.make_epilogue(bias=w.b_oc1, out=o1, ldo=w.F2p), T, 8 * gh, 8 * gw, Fc, w.F2p)
+        Ho, Wo = gh * PATCH, gw * PATCH
+        up = ws.get("out1_up", (T * Ho * Wo, w.F2p))
+        L.bilinear_nhwc(o1, up, T, 8 * gh, 8 * gw, Ho, Wo, w.F2p)
+        depth = ws.get("depth", (T, Ho, Wo), torch.float32)
+        L.conv3x3(up, w.w_oc2, L.make_epilogue(bias=w.b_oc2, out_f32=depth, w2=w.w_last, b2=w.b_last,
+                                               store_mode=L.ST_HEADDOT), T, Ho, Wo, w.F2p, 32)
+        return depth
+
+    # ------------------------------------------------------------------ whole window
+    def forward(self, x):
+        """x f32 [T,3,H,W] on this device -> depth f32 [T,H,W] (a workspace buffer: copy before reuse)."""
+        assert x.dim() == 4 and x.shape[1] == 3 and x.dtype == torch.float32 and x.is_cuda
+        T, _, H, W = x.shape
+        if H % PATCH or W % PATCH:
+            raise AssertionError(f"Input image size {H}x{W} is not a multiple of patch size {PATCH}")
+        if T > 32:
+            raise AssertionError("temporal attention supports at most 32 frames per window")
+        ws = self._ws(("win", T, H, W))
+        with torch.cuda.device(self.device):
+            taps = self.encoder(x.contiguous(), ws)
+            return self.head(taps, H // PATCH, W // PATCH, T, ws)

@@ -1,0 +1,51 @@
+"""Host-side frame pre-processing (util/transform.py:51-157 as composed in video_depth.py:77-89):
+keep-aspect "lower_bound" resize to a multiple of 14 with cv2 INTER_CUBIC on float32 [0,1] RGB,
+ImageNet normalisation evaluated in float64 then cast to float32, HWC -> CHW.
+
+The reference re-runs this for every slot of every window on one Python thread; here every source
+frame is converted exactly once, on a small thread pool (cv2 releases the GIL), straight into one
+pinned staging buffer that is uploaded with a single async copy.
+"""
+from concurrent.futures import ThreadPoolExecutor
+import os
+
+import cv2
+import numpy as np
+import torch
+
+_MEAN = np.array([0.485, 0.456, 0.406])
+_STD = np.array([0.229, 0.224, 0.225])
+_POOL = None
+
+
+def net_input_size(h0, w0, input_size=518):
+    """Network input (height, width) for a source frame (video_depth.py:71-75, transform.py:51-107)."""
+    ratio = max(h0, w0) / min(h0, w0)
+    if ratio > 1.78:
+        input_size = int(input_size * 1.777 / ratio)
+        input_size = round(input_size / 14) * 14
+    scale = max(input_size / w0, input_size / h0)
+
+    def snap(v):
+        y = int(np.round(v / 14) * 14)
+        return y if y >= input_size else int(np.ceil(v / 14) * 14)
+
+    return snap(scale * h0), snap(scale * w0)
+
+
+def _one(frame, nh, nw, dst):
+    img = frame.astype(np.float32) / 255.0
+    img = cv2.resize(img, (nw, nh), interpolation=cv2.INTER_CUBIC)
+    img = (img - _MEAN) / _STD
+    dst[...] = np.transpose(img, (2, 0, 1))
+
+
+def preprocess_frames(frames, indices, nh, nw, device):
+    """frames uint8 [N,H0,W0,3]; returns f32 [len(indices),3,nh,nw] on `device`."""
+    global _POOL
+    if _POOL is None:
+        _POOL = ThreadPoolExecutor(max_workers=min(16, os.cpu_count() or 1))
+    host = torch.empty(len(indices), 3, nh, nw, dtype=torch.float32, pin_memory=torch.cuda.is_available())
+    arr = host.numpy()
+    list(_POOL.map(lambda j: _one(frames[indices[j]], nh, nw, arr[j]), range(len(indices))))
+    return host.to(device, non_blocking=True)

@@ -1,0 +1,144 @@
+"""Drop-in `VideoDepthAnything` (offline, 32-frame windows) on the B200 kernel library.
+
+Mirrors the reference's public surface (video_depth_anything/video_depth.py:35-162): same ctor
+kwargs, same state_dict keys, `forward(x[B,T,3,H,W]) -> [B,T,H,W]`, and
+`infer_video_depth(frames, target_fps, input_size, device, fp32) -> (float32 [N,H0,W0], fps)`.
+What differs is underneath: every window is a fixed launch sequence of libvda_b200 kernels
+(vda_b200.engine); each source frame is pre-processed once; all windows' depth maps stay on the
+GPU; the sequential scale/shift alignment and the cross-fade run as GPU kernels without host
+synchronisation; one device->host copy returns the result.
+"""
+import numpy as np
+import torch
+from torch import nn
+
+from . import lib as L
+from .engine import Engine
+from .modules import ARCH, DinoEncoder, DPTTemporalHead
+from .preprocess import net_input_size, preprocess_frames
+
+# window semantics of the reference, "do not change" (video_depth.py:29-33)
+INFER_LEN = 32
+OVERLAP = 10
+KEYFRAMES = [0, 12, 24, 25, 26, 27, 28, 29, 30, 31]
+INTERP_LEN = 8
+
+
+def window_frame_indices(n_frames):
+    """Raw-frame indices of every window (closed form of video_depth.py:92-115: the keyframe slots
+    are copied from the previous window's already-substituted input, so slot 0 is always frame 0)."""
+    step = INFER_LEN - OVERLAP
+    last = n_frames - 1
+    wins = []
+    for start in range(0, n_frames, step):
+        cur = [min(start + i, last) for i in range(INFER_LEN)]
+        if wins:
+            cur[:OVERLAP] = [wins[-1][j] for j in KEYFRAMES]
+        wins.append(cur)
+    return wins
+
+
+class VideoDepthAnything(nn.Module):
+    def __init__(self, encoder="vitl", features=256, out_channels=[256, 512, 1024, 1024], use_bn=False,
+                 use_clstoken=False, num_frames=32, pe="ape", metric=False):
+        super().__init__()
+        if use_bn or use_clstoken or pe != "ape":
+            raise NotImplementedError("use_bn / use_clstoken / pe='rope' are never selected by the reference's "
+                                      "callers and are out of scope (SURVEY.md section 2)")
+        if encoder not in ARCH:
+            raise KeyError(encoder)
+        self.intermediate_layer_idx = {k: list(v["taps"]) for k, v in ARCH.items()}
+        self.encoder = encoder
+        self.pretrained = DinoEncoder(encoder)
+        self.head = DPTTemporalHead(self.pretrained.embed_dim, features, out_channels, num_frames)
+        self.metric = metric
+        self._engine = None
+
+    # -- lifecycle: packed weights are rebuilt lazily after .to()/.cuda()/load_state_dict()
+    def _apply(self, fn, *a, **k):
+        self._engine = None
+        return super()._apply(fn, *a, **k)
+
+    def load_state_dict(self, *a, **k):
+        self._engine = None
+        return super().load_state_dict(*a, **k)
+
+    def engine(self):
+        dev = self.pretrained.cls_token.device
+        if self._engine is None or self._engine.device != dev:
+            self._engine = Engine(self, dev)
+        return self._engine
+
+    def forward(self, x):
+        """x f32 [B,T,3,H,W], H and W multiples of 14 -> depth f32 [B,T,H,W] (>= 0)."""
+        B, T = x.shape[:2]
+        eng = self.engine()
+        out = [eng.forward(x[b].float()).clone() for b in range(B)]
+        return torch.stack(out, 0)
+
+    # ------------------------------------------------------------------ offline driver
+    @torch.no_grad()
+    def infer_video_depth(self, frames, target_fps, input_size=518, device="cuda", fp32=False):
+        """frames uint8 [N,H0,W0,3] RGB -> (float32 [N,H0,W0], target_fps).
+
+        `fp32=True` is accepted for interface parity; this build's only arithmetic path is BF16
+        tensor-core GEMMs with FP32 accumulation/statistics (precision policy)."""
+        depth = self.infer_video_depth_device(frames, input_size=input_size, device=device)
+        host = torch.empty(depth.shape, dtype=torch.float32, pin_memory=True)
+        host.copy_(depth, non_blocking=True)
+        torch.cuda.current_stream(depth.device).synchronize()
+        return host.numpy(), target_fps
+
+    @torch.no_grad()
+    def infer_video_depth_device(self, frames, input_size=518, device="cuda", windows=None, return_raw=False):
+        """Same as infer_video_depth but leaves the aligned depth [N,H0,W0] on the GPU.
+        `windows` restricts the forward passes to a subset (multi-GPU sharding, vda_b200.parallel)."""
+        dev = torch.device(device if device != "cuda" else f"cuda:{torch.cuda.current_device()}")
+        if self.pretrained.cls_token.device != dev:
+            raise RuntimeError(f"model is on {self.pretrained.cls_token.device}, call .to('{dev}') first")
+        frames = np.asarray(frames)
+        n, h0, w0 = frames.shape[:3]
+        nh, nw = net_input_size(h0, w0, input_size)
+        wins = window_frame_indices(n)
+        mine = list(range(len(wins))) if windows is None else list(windows)
+        eng = self.engine()
+        with torch.cuda.device(dev):
+            needed = sorted({i for k in mine for i in wins[k]})
+            slot = {f: j for j, f in enumerate(needed)}
+            net_in = preprocess_frames(frames, needed, nh, nw, dev)            # [len(needed),3,nh,nw] f32 on GPU
+            raw = torch.empty(len(mine) * INFER_LEN, h0, w0, dtype=torch.float32, device=dev)
+            for j, k in enumerate(mine):
+                idx = torch.tensor([slot[f] for f in wins[k]], device=dev)
+                d = eng.forward(net_in.index_select(0, idx))
+                L.bilinear_f32(d, raw[j * INFER_LEN:(j + 1) * INFER_LEN], INFER_LEN, nh, nw, h0, w0)
+            if return_raw:
+                return raw
+            return align_windows_device(raw, self.metric)[:n]
+
+
+def align_windows_device(raw, metric=False, out=None):
+    """Sequential scale/shift alignment + 8-frame cross-fade (video_depth.py:120-160) on the GPU.
+    raw: f32 [n_windows*32, H0, W0] -> f32 [32 + 22*(n_windows-1), H0, W0].  No host sync."""
+    n_win = raw.shape[0] // INFER_LEN
+    per = raw.shape[1] * raw.shape[2]
+    step = INFER_LEN - OVERLAP
+    n_align = OVERLAP - INTERP_LEN
+    total = INFER_LEN + step * (n_win - 1)
+    if out is None:
+        out = torch.empty(total, raw.shape[1], raw.shape[2], dtype=torch.float32, device=raw.device)
+    out[:INFER_LEN].copy_(raw[:INFER_LEN])
+    ref = [raw[KEYFRAMES[0]], raw[KEYFRAMES[1]]]
+    sums = torch.zeros(5, dtype=torch.float64, device=raw.device)
+    ss = torch.empty(2, dtype=torch.float32, device=raw.device)
+    filled = INFER_LEN
+    for k in range(1, n_win):
+        base = k * INFER_LEN
+        sums.zero_()
+        for i in range(n_align):
+            L.lsq_accum(raw[base + i], ref[i], per, sums)
+        L.lsq_solve(sums, ss, metric)
+        L.affine_clamp_blend(out[filled - INTERP_LEN:filled], raw[base + n_align:base + OVERLAP], per, INTERP_LEN, ss)
+        L.affine_clamp(raw[base + OVERLAP:base + INFER_LEN], out[filled:filled + step], per * step, ss)
+        ref = [ref[0], out[filled + KEYFRAMES[1] - OVERLAP]]
+        filled += step
+    return out
