@@ -35,7 +35,11 @@ def import_reference():
     saved = {k: v for k, v in sys.modules.items() if k.split(".")[0] in ("video_depth_anything", "utils")}
     for k in saved:
         del sys.modules[k]
-    sys.path.insert(0, REF_ROOT)
+    # the reference's packages have no __init__.py (namespace packages), so any regular package of the
+    # same name further down sys.path (this repo's shims) would win: hide those entries meanwhile.
+    old_path = list(sys.path)
+    sys.path[:] = [REF_ROOT] + [p for p in old_path
+                                if not os.path.isfile(os.path.join(p or ".", "video_depth_anything", "__init__.py"))]
     try:
         import contextlib
         import io
@@ -44,7 +48,7 @@ def import_reference():
             from video_depth_anything.video_depth import VideoDepthAnything as Offline
             from video_depth_anything.video_depth_stream import VideoDepthAnything as Stream
     finally:
-        sys.path.remove(REF_ROOT)
+        sys.path[:] = old_path
         for k in [k for k in sys.modules if k.split(".")[0] in ("video_depth_anything", "utils")]:
             sys.modules["_vda_reference_." + k] = sys.modules.pop(k)
         sys.modules.update(saved)

@@ -34,6 +34,34 @@ class VdaError(RuntimeError):
 _lib = None
 _inited = set()
 
+# launch accounting for bench.py: LAUNCHES counts kernels of this library enqueued so far;
+# when PROFILE is a list, every tensor-core launch appends (kind, flops, start_event, end_event).
+LAUNCHES = 0
+PROFILE = None
+
+
+def _launched(n=1):
+    global LAUNCHES
+    LAUNCHES += n
+
+
+class _timed:
+    """Brackets one launch with CUDA events on the current stream when profiling is on."""
+
+    def __init__(self, kind, flops):
+        self.kind, self.flops = kind, flops
+
+    def __enter__(self):
+        if PROFILE is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e1 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+
+    def __exit__(self, *a):
+        if PROFILE is not None:
+            self.e1.record()
+            PROFILE.append((self.kind, self.flops, self.e0, self.e1))
+
 
 def load():
     """Load (building if the in-tree .so is absent) and return the ctypes library handle."""
@@ -132,16 +160,22 @@ def gemm(a, w, epi, M=None, N=None, K=None, lda=None, ldw=None):
     N = w.shape[0] if N is None else N
     lda = a.stride(0) if lda is None else lda
     ldw = w.stride(0) if ldw is None else ldw
-    check(load().vda_gemm_bf16(ptr(a), lda, ptr(w), ldw, M, N, K, C.byref(epi), stream_ptr()))
+    with _timed("gemm", 2.0 * M * N * K):
+        check(load().vda_gemm_bf16(ptr(a), lda, ptr(w), ldw, M, N, K, C.byref(epi), stream_ptr()))
+    _launched()
 
 
 def conv3x3(x, w, epi, n, H, W, Cin, Cout, ldx=None):
     ldx = Cin if ldx is None else ldx
-    check(load().vda_conv3x3_nhwc(ptr(x), ldx, ptr(w), n, H, W, Cin, Cout, C.byref(epi), stream_ptr()))
+    with _timed("conv3x3", 2.0 * n * H * W * Cout * 9 * Cin):
+        check(load().vda_conv3x3_nhwc(ptr(x), ldx, ptr(w), n, H, W, Cin, Cout, C.byref(epi), stream_ptr()))
+    _launched()
 
 
 def flash_attn(qk, vt, out, frames, S, heads, s_pad):
-    check(load().vda_flash_attn_fwd(ptr(qk), ptr(vt), ptr(out), frames, S, heads, s_pad, stream_ptr()))
+    with _timed("attn", 4.0 * frames * heads * S * S * 64):
+        check(load().vda_flash_attn_fwd(ptr(qk), ptr(vt), ptr(out), frames, S, heads, s_pad, stream_ptr()))
+    _launched()
 
 
 def layernorm(x, gamma, beta, out, eps, rows=None, C=None, tokens_per_frame=0, skip=0, pe=None, out_nope=None,
@@ -150,50 +184,62 @@ def layernorm(x, gamma, beta, out, eps, rows=None, C=None, tokens_per_frame=0, s
     C = x.shape[-1] if C is None else C
     check(load().vda_layernorm(ptr(x), int(x.dtype == torch.float32), ptr(gamma), ptr(beta), ptr(out), ptr(out_nope),
                                ptr(pe), rows, C, eps, tokens_per_frame, skip, pe_rows_per_t, pe_T, stream_ptr()))
+    _launched(1)
 
 
 def groupnorm_nhwc(x, gamma, beta, out, stats_ws, n, hw, C, eps, ldx=None):
     check(load().vda_groupnorm_nhwc(ptr(x), C if ldx is None else ldx, ptr(gamma), ptr(beta), ptr(out), ptr(stats_ws),
                                     n, hw, C, eps, stream_ptr()))
+    _launched(2)
 
 
 def patch_im2col(x, a, frames, H, W, ldk):
     check(load().vda_patch_im2col(ptr(x), ptr(a), frames, H, W, ldk, stream_ptr()))
+    _launched(1)
 
 
 def add_cls_pos(patch, cls, pos, tokens, frames, hw, D):
     check(load().vda_add_cls_pos(ptr(patch), ptr(cls), ptr(pos), ptr(tokens), frames, hw, D, stream_ptr()))
+    _launched(1)
 
 
 def bilinear_nhwc(x, out, n, h, w, H, W, C, ldx=None, ldo=None):
     check(load().vda_bilinear_nhwc(ptr(x), C if ldx is None else ldx, ptr(out), C if ldo is None else ldo,
                                    n, h, w, H, W, C, stream_ptr()))
+    _launched(1)
 
 
 def bilinear_f32(x, out, n, h, w, H, W, relu=False):
     check(load().vda_bilinear_f32(ptr(x), ptr(out), n, h, w, H, W, int(relu), stream_ptr()))
+    _launched(1)
 
 
 def im2col_s2(x, a, n, h, w, C):
     check(load().vda_im2col_s2(ptr(x), ptr(a), n, h, w, C, stream_ptr()))
+    _launched(1)
 
 
 def temporal_attn(q, ldq, k, ldk, v, ldv, out, ldo, hw, heads, head_dim, Tq, Tk):
     check(load().vda_temporal_attn(ptr(q), ldq, ptr(k), ldk, ptr(v), ldv, ptr(out), ldo, hw, heads, head_dim, Tq, Tk,
                                    stream_ptr()))
+    _launched(1)
 
 
 def lsq_accum(pred, target, n, sums5):
     check(load().vda_lsq_accum(ptr(pred), ptr(target), n, ptr(sums5), stream_ptr()))
+    _launched(1)
 
 
 def lsq_solve(sums5, scale_shift, metric=False):
     check(load().vda_lsq_solve(ptr(sums5), ptr(scale_shift), int(metric), stream_ptr()))
+    _launched(1)
 
 
 def affine_clamp(src, dst, n, scale_shift):
     check(load().vda_affine_clamp(ptr(src), ptr(dst), n, ptr(scale_shift), stream_ptr()))
+    _launched(1)
 
 
 def affine_clamp_blend(pre, post, per_frame, frames, scale_shift):
     check(load().vda_affine_clamp_blend(ptr(pre), ptr(post), per_frame, frames, ptr(scale_shift), stream_ptr()))
+    _launched(1)

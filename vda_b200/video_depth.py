@@ -23,6 +23,26 @@ OVERLAP = 10
 KEYFRAMES = [0, 12, 24, 25, 26, 27, 28, 29, 30, 31]
 INTERP_LEN = 8
 
+# ctor kwargs per encoder, as every caller of the reference spells them (run.py:45-49)
+MODEL_CONFIGS = {
+    "vits": {"encoder": "vits", "features": 64, "out_channels": [48, 96, 192, 384]},
+    "vitb": {"encoder": "vitb", "features": 128, "out_channels": [96, 192, 384, 768]},
+    "vitl": {"encoder": "vitl", "features": 256, "out_channels": [256, 512, 1024, 1024]},
+}
+
+
+def randomize_zero_init_(model, seed=0):
+    """Random-init benchmarking helper: the reference zero-initialises every motion module's
+    proj_out (motion_module.py:57-58), which would make the temporal branch a no-op on fresh weights;
+    give it small random values so a random-init model exercises the whole path."""
+    g = torch.Generator().manual_seed(seed)
+    for m in model.head.motion_modules:
+        po = m.temporal_transformer.proj_out
+        with torch.no_grad():
+            po.weight.copy_(torch.randn(po.weight.shape, generator=g) * po.weight.shape[1] ** -0.5)
+            po.bias.copy_(torch.randn(po.bias.shape, generator=g) * 0.02)
+    return model
+
 
 def window_frame_indices(n_frames):
     """Raw-frame indices of every window (closed form of video_depth.py:92-115: the keyframe slots
