@@ -106,6 +106,15 @@ int vda_im2col_s2(const void* x, void* a, int n, int h, int w, int C, void* stre
 int vda_temporal_attn(const void* q, int ldq, const void* k, int ldk, const void* v, int ldv, void* out, int ldo,
                       int hw, int heads, int head_dim, int Tq, int Tk, void* stream);
 
+/* Streaming temporal attention (video_depth_stream.py:134-153, motion_module.py:252-266): the new
+ * frame (Tq = 1) attends over Tk <= 32 list positions.  kcache/vcache: [cap, hw, C] bf16 PE-free
+ * projections of cached frames; slots: DEVICE int[Tk], cache slot of each list position, the last
+ * entry being the slot this call stores knew/vnew into; pe_q/pe_k/pe_v: f32 [32, C] positional
+ * table projected through W_q/W_k/W_v (K(n+pe) = Kn + K pe).  q/knew/vnew: [hw, ldn], out: [hw, ldo]. */
+int vda_temporal_attn_stream(const void* q, const void* knew, const void* vnew, int ldn, void* kcache, void* vcache,
+                             const int* slots, const float* pe_q, const float* pe_k, const float* pe_v, void* out,
+                             int ldo, int hw, int heads, int head_dim, int Tk, void* stream);
+
 /* Alignment (utils/util.py:40-74, video_depth.py:120-160).  sums5 = {sum p*p, sum p, n, sum p*t,
  * sum t} accumulated in FP64 (caller zeroes it); solve writes {scale, shift} (metric: {1,0}). */
 int vda_lsq_accum(const float* pred, const float* target, long long n, double* sums5, void* stream);

@@ -122,3 +122,24 @@ def test_alignment_scan_matches_oracle_exactly_on_same_raw_depth():
     want = np.stack(O.align_windows([raw[i].copy() for i in range(raw.shape[0])]))
     got = align_windows_device(torch.from_numpy(raw).cuda()).cpu().numpy()
     np.testing.assert_allclose(got, want, rtol=2e-4, atol=2e-4)
+
+
+def test_streaming_vs_reference_golden():
+    """Config 5: frame-by-frame with the temporal cache, past the steady state (frame 11+)."""
+    from video_depth_anything.video_depth_stream import VideoDepthAnything as Stream
+
+    v = G.VIDEO_CASE
+    frames = G.video_frames(v["n"], v["h"], v["w"])
+    gold = np.load(os.path.join(G.GOLDEN_DIR, "video_vits_46x44x60.npz"))["stream"]
+    cfg = O.ARCH[v["arch"]]
+    m = Stream(encoder=v["arch"], features=cfg["features"], out_channels=cfg["out_channels"])
+    m.load_state_dict(refload.seeded_state_dict(v["arch"], 0), strict=True)
+    m = m.to("cuda").eval()
+    got = np.stack([m.infer_video_depth_one(frames[i], input_size=v["input_size"], device="cuda")
+                    for i in range(v["n"])])
+    assert got.shape == gold.shape and got.dtype == np.float32
+    assert len(m.frame_cache_list) == 42 and len(m.frame_id_list) == 42 and m.frame_id_list[0] == 0
+    assert m.frame_id_list[-1] == v["n"] - 1
+    errs = [absrel(got[i], gold[i]) for i in range(v["n"])]
+    print(f"stream: absrel first {errs[0]:.2e} max {max(errs):.2e} last {errs[-1]:.2e}")
+    assert max(errs) <= ABSREL_TOL

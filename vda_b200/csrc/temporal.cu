@@ -124,9 +124,131 @@ __global__ void __launch_bounds__(kTWarps * 32) temporal_attn_kernel(const Tempo
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Streaming variant (video_depth_stream.py:134-153, motion_module.py:252-266): one new frame
+// attends over Tk <= 32 positions = (Tk-1) cached frames + itself.  The reference re-projects K and
+// V of all 32 cached hidden states every frame because the sinusoidal PE is added by *position in
+// the current list*, which shifts; projections are linear, so we cache the PE-free projections
+// k_c = n W_k^T, v_c = n W_v^T per frame and add the projected PE rows (pe_k[p] = PE[p] W_k^T, ...)
+// at read time.  `slots[p]` names the cache slot of list position p; slots[Tk-1] is where the new
+// frame's k_c / v_c are stored by this kernel.  One warp per (token, head); lane p owns position p.
+struct TemporalStreamParams {
+  const bf16* q;     // [hw, ldn] new frame, PE-free projection
+  const bf16* knew;  // [hw, ldn]
+  const bf16* vnew;
+  bf16* kcache;      // [cap, hw, C]
+  bf16* vcache;
+  const int* slots;  // device, Tk entries
+  const float* pe_q; // [32, C] projected PE tables (fp32)
+  const float* pe_k;
+  const float* pe_v;
+  bf16* out;         // [hw, ldo]
+  int ldn, ldo, hw, heads, hd, C, Tk;
+  float scale;
+};
+
+__global__ void __launch_bounds__(kTWarps * 32) temporal_attn_stream_kernel(const TemporalStreamParams p) {
+  extern __shared__ __align__(16) uint8_t tsm[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int unit = blockIdx.x * kTWarps + warp;
+  if (unit >= p.hw * p.heads) return;
+  const int d = unit / p.heads, head = unit - d * p.heads;
+  const int hd = p.hd, chunks = hd >> 3;
+  float* sW = reinterpret_cast<float*>(tsm) + warp * 32 * (hd + 1);  // [32][hd+1] weighted V rows
+  const int pos = lane;
+  const bool active = pos < p.Tk;
+  const bool is_new = pos == p.Tk - 1;
+  const int slot = active ? p.slots[pos] : 0;
+  const long long crow = (static_cast<long long>(slot) * p.hw + d) * p.C + head * hd;
+  const bf16* krow = is_new ? p.knew + static_cast<long long>(d) * p.ldn + head * hd : p.kcache + crow;
+  const bf16* vrow = is_new ? p.vnew + static_cast<long long>(d) * p.ldn + head * hd : p.vcache + crow;
+  const bf16* qrow = p.q + static_cast<long long>(d) * p.ldn + head * hd;
+  const float* peq = p.pe_q + static_cast<long long>(p.Tk - 1) * p.C + head * hd;
+  const float* pek = p.pe_k + static_cast<long long>(pos) * p.C + head * hd;
+  const float* pev = p.pe_v + static_cast<long long>(pos) * p.C + head * hd;
+  float s = 0.f;
+  if (active) {
+    for (int c = 0; c < chunks; ++c) {
+      const uint4 qq = __ldg(reinterpret_cast<const uint4*>(qrow + c * 8));
+      const uint4 kk = *reinterpret_cast<const uint4*>(krow + c * 8);
+      if (is_new) *reinterpret_cast<uint4*>(p.kcache + crow + c * 8) = kk;
+      const uint32_t qw[4] = {qq.x, qq.y, qq.z, qq.w}, kw[4] = {kk.x, kk.y, kk.z, kk.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 qf = bf2(qw[i]), kf = bf2(kw[i]);
+        const int cc = c * 8 + 2 * i;
+        s += (qf.x + peq[cc]) * (kf.x + pek[cc]) + (qf.y + peq[cc + 1]) * (kf.y + pek[cc + 1]);
+      }
+    }
+  }
+  s = active ? s * p.scale : -INFINITY;
+  float m = s;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  float e = active ? __expf(s - m) : 0.f;
+  float l = e;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
+  const float w = e / l;
+  float* mine = sW + lane * (hd + 1);
+  if (active) {
+    for (int c = 0; c < chunks; ++c) {
+      const uint4 vv = *reinterpret_cast<const uint4*>(vrow + c * 8);
+      if (is_new) *reinterpret_cast<uint4*>(p.vcache + crow + c * 8) = vv;
+      const uint32_t vw[4] = {vv.x, vv.y, vv.z, vv.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 vf = bf2(vw[i]);
+        const int cc = c * 8 + 2 * i;
+        mine[cc] = w * (vf.x + pev[cc]);
+        mine[cc + 1] = w * (vf.y + pev[cc + 1]);
+      }
+    }
+  } else {
+    for (int c = 0; c < hd; ++c) mine[c] = 0.f;
+  }
+  __syncwarp();
+  bf16* orow = p.out + static_cast<long long>(d) * p.ldo + head * hd;
+  for (int c = lane; c < hd; c += 32) {
+    float acc = 0.f;
+#pragma unroll 8
+    for (int j = 0; j < 32; ++j) acc += sW[j * (hd + 1) + c];
+    orow[c] = __float2bfloat16(acc);
+  }
+}
+
 }  // namespace vda
 
 using namespace vda;
+
+extern "C" int vda_temporal_attn_stream(const void* q, const void* knew, const void* vnew, int ldn, void* kcache,
+                                        void* vcache, const int* slots, const float* pe_q, const float* pe_k,
+                                        const float* pe_v, void* out, int ldo, int hw, int heads, int head_dim, int Tk,
+                                        void* stream) {
+  if (!q || !knew || !vnew || !kcache || !vcache || !slots || !pe_q || !pe_k || !pe_v || !out || hw <= 0 || heads <= 0 ||
+      head_dim % 8 || head_dim > 128 || Tk < 1 || Tk > 32 || ldn % 8 || ldo % 2)
+    return set_error(-1, "vda_temporal_attn_stream: bad arguments");
+  TemporalStreamParams p;
+  p.q = static_cast<const bf16*>(q), p.knew = static_cast<const bf16*>(knew), p.vnew = static_cast<const bf16*>(vnew);
+  p.kcache = static_cast<bf16*>(kcache), p.vcache = static_cast<bf16*>(vcache);
+  p.slots = slots, p.pe_q = pe_q, p.pe_k = pe_k, p.pe_v = pe_v;
+  p.out = static_cast<bf16*>(out);
+  p.ldn = ldn, p.ldo = ldo, p.hw = hw, p.heads = heads, p.hd = head_dim, p.C = heads * head_dim, p.Tk = Tk;
+  p.scale = 1.0f / sqrtf(static_cast<float>(head_dim));
+  const int smem = kTWarps * 32 * (head_dim + 1) * 4;
+  static bool configured = false;
+  if (!configured) {
+    int rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             kTWarps * 32 * 129 * 4),
+                        "temporal stream smem attribute");
+    if (rc) return rc;
+    configured = true;
+  }
+  const int units = hw * heads;
+  temporal_attn_stream_kernel<<<(units + kTWarps - 1) / kTWarps, kTWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  return check_cuda(cudaGetLastError(), "temporal_attn_stream launch");
+}
+
 
 extern "C" int vda_temporal_attn(const void* q, int ldq, const void* k, int ldk, const void* v, int ldv, void* out,
                                  int ldo, int hw, int heads, int head_dim, int Tq, int Tk, void* stream) {

@@ -50,8 +50,11 @@ class _Motion:
         for a, n in zip(blk.attention_blocks, blk.norms):
             wqkv, _ = P.linear(torch.cat([a.to_q.weight, a.to_k.weight, a.to_v.weight], 0), device=dev)
             wo, bo = P.linear(a.to_out[0].weight, a.to_out[0].bias, device=dev)
-            self.attn.append(dict(ln_w=P.vec(n.weight, dev), ln_b=P.vec(n.bias, dev), wqkv=wqkv, wo=wo, bo=bo,
-                                  pe=a.pos_encoder.pe.detach().float().reshape(-1, self.C).contiguous().to(dev)))
+            pe = a.pos_encoder.pe.detach().float().reshape(-1, self.C).contiguous().to(dev)
+            # streaming mode: K(n + pe) = K n + K pe, so the projected PE rows are added at read time
+            proj_pe = [(pe @ w_.detach().float().to(dev).T).contiguous() for w_ in (a.to_q.weight, a.to_k.weight, a.to_v.weight)]
+            self.attn.append(dict(ln_w=P.vec(n.weight, dev), ln_b=P.vec(n.bias, dev), wqkv=wqkv, wo=wo, bo=bo, pe=pe,
+                                  pe_q=proj_pe[0], pe_k=proj_pe[1], pe_v=proj_pe[2]))
         self.ffn_w, self.ffn_b = P.vec(blk.ff_norm.weight, dev), P.vec(blk.ff_norm.bias, dev)
         self.w_geglu, self.b_geglu = P.geglu(blk.ff.net[0].proj.weight, blk.ff.net[0].proj.bias, dev)
         self.w_ff2, self.b_ff2 = P.linear(blk.ff.net[2].weight, blk.ff.net[2].bias, device=dev)
@@ -297,8 +300,9 @@ class Engine:
         return depth
 
     # ------------------------------------------------------------------ whole window
-    def forward(self, x):
-        """x f32 [T,3,H,W] on this device -> depth f32 [T,H,W] (a workspace buffer: copy before reuse)."""
+    def forward(self, x, stream_ctx=None):
+        """x f32 [T,3,H,W] on this device -> depth f32 [T,H,W] (a workspace buffer: copy before reuse).
+        With `stream_ctx` (T == 1) the temporal attention reads the streaming K/V cache instead."""
         assert x.dim() == 4 and x.shape[1] == 3 and x.dtype == torch.float32 and x.is_cuda
         T, _, H, W = x.shape
         if H % PATCH or W % PATCH:
@@ -308,4 +312,40 @@ class Engine:
         ws = self._ws(("win", T, H, W))
         with torch.cuda.device(self.device):
             taps = self.encoder(x.contiguous(), ws)
-            return self.head(taps, H // PATCH, W // PATCH, T, ws)
+            return self.head(taps, H // PATCH, W // PATCH, T, ws, stream_ctx=stream_ctx)
+
+
+class StreamCache:
+    """Device-side temporal cache of the streaming mode (video_depth_stream.py:55-60,134-159).
+
+    The reference keeps, per frame, the 8 post-LayerNorm hidden states feeding the 8 temporal
+    attentions and re-projects K/V of all of them every frame.  Here each of the 8 attentions owns
+    a slot-addressed K/V cache [cap, hw, C] of PE-free projections; the reference's
+    `frame_cache_list` becomes a list of slot numbers with identical list semantics."""
+
+    CAP = 44  # the reference's list peaks at 43 entries (42 after the trim) + 1 slot in flight
+
+    def __init__(self, engine, gh, gw):
+        w = engine.w
+        dev = engine.device
+        gh4, gw4 = (gh - 1) // 2 + 1, (gw - 1) // 2 + 1
+        geo = [(gh * gw, w.oc[2]), (gh4 * gw4, w.oc[3]), (gh * gw, w.F), (4 * gh * gw, w.F)]
+        self.k = [[torch.zeros(self.CAP, hw, C, dtype=torch.bfloat16, device=dev) for _ in range(2)] for hw, C in geo]
+        self.v = [[torch.zeros(self.CAP, hw, C, dtype=torch.bfloat16, device=dev) for _ in range(2)] for hw, C in geo]
+        self.slots_dev = torch.zeros(32, dtype=torch.int32, device=dev)
+        self.slots_host = torch.zeros(32, dtype=torch.int32).pin_memory()
+        self.Tk = 1
+
+    def begin_frame(self, cached_slots, new_slot):
+        """cached_slots: slot numbers of the list positions the new frame attends to (<= 31)."""
+        lst = list(cached_slots) + [new_slot]
+        self.Tk = len(lst)
+        self.slots_host[: self.Tk] = torch.tensor(lst, dtype=torch.int32)
+        self.slots_dev.copy_(self.slots_host, non_blocking=True)
+
+    def attend(self, eng, idx, a_i, a, h, n, o, hw, C, ws):
+        qkv = ws.get(f"mm{idx}_qkv", (hw, 3 * C))
+        L.layernorm(h, a["ln_w"], a["ln_b"], n, 1e-5)
+        L.gemm(n, a["wqkv"], L.make_epilogue(out=qkv, ldo=3 * C))
+        L.temporal_attn_stream(qkv, qkv[:, C:], qkv[:, 2 * C:], 3 * C, self.k[idx][a_i], self.v[idx][a_i], self.slots_dev,
+                               a["pe_q"], a["pe_k"], a["pe_v"], o, C, hw, 8, C // 8, self.Tk)

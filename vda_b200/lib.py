@@ -95,6 +95,7 @@ def _declare(lib):
         "vda_bilinear_f32": [vp, vp, i, i, i, i, i, i, vp],
         "vda_im2col_s2": [vp, vp, i, i, i, i, vp],
         "vda_temporal_attn": [vp, i, vp, i, vp, i, vp, i, i, i, i, i, i, vp],
+        "vda_temporal_attn_stream": [vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, vp],
         "vda_lsq_accum": [vp, vp, C.c_longlong, vp, vp],
         "vda_lsq_solve": [vp, vp, i, vp],
         "vda_affine_clamp": [vp, vp, C.c_longlong, vp, vp],
@@ -222,6 +223,13 @@ def im2col_s2(x, a, n, h, w, C):
 def temporal_attn(q, ldq, k, ldk, v, ldv, out, ldo, hw, heads, head_dim, Tq, Tk):
     check(load().vda_temporal_attn(ptr(q), ldq, ptr(k), ldk, ptr(v), ldv, ptr(out), ldo, hw, heads, head_dim, Tq, Tk,
                                    stream_ptr()))
+    _launched(1)
+
+
+def temporal_attn_stream(q, knew, vnew, ldn, kcache, vcache, slots, pe_q, pe_k, pe_v, out, ldo, hw, heads, head_dim, Tk):
+    check(load().vda_temporal_attn_stream(ptr(q), ptr(knew), ptr(vnew), ldn, ptr(kcache), ptr(vcache), ptr(slots),
+                                          ptr(pe_q), ptr(pe_k), ptr(pe_v), ptr(out), ldo, hw, heads, head_dim, Tk,
+                                          stream_ptr()))
     _launched(1)
 
 

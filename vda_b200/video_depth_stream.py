@@ -1,0 +1,106 @@
+"""Drop-in streaming `VideoDepthAnything` (video_depth_anything/video_depth_stream.py:31-161):
+frame-by-frame inference with a temporal cache.  Same ctor (no `metric` kwarg, :33-42), same
+state_dict keys, same stateful attributes (`transform`, `frame_id_list`, `frame_cache_list`, `gap`,
+`id`, `frame_height`, `frame_width`) and the same list bookkeeping; the cache entries are slot
+numbers into a device-resident K/V cache (vda_b200.engine.StreamCache) instead of lists of tensors.
+"""
+import numpy as np
+import torch
+from torch import nn
+
+from . import lib as L
+from .engine import Engine, StreamCache
+from .modules import ARCH, DinoEncoder, DPTTemporalHead
+from .preprocess import net_input_size, preprocess_frames
+from .video_depth import INFER_LEN, INTERP_LEN, OVERLAP
+
+
+class VideoDepthAnything(nn.Module):
+    def __init__(self, encoder="vitl", features=256, out_channels=[256, 512, 1024, 1024], use_bn=False,
+                 use_clstoken=False, num_frames=32, pe="ape"):
+        super().__init__()
+        if use_bn or use_clstoken or pe != "ape":
+            raise NotImplementedError("use_bn / use_clstoken / pe='rope' are never selected by the reference's "
+                                      "callers and are out of scope (SURVEY.md section 2)")
+        if encoder not in ARCH:
+            raise KeyError(encoder)
+        self.intermediate_layer_idx = {k: list(v["taps"]) for k, v in ARCH.items()}
+        self.encoder = encoder
+        self.pretrained = DinoEncoder(encoder)
+        self.head = DPTTemporalHead(self.pretrained.embed_dim, features, out_channels, num_frames)
+        self.transform = None
+        self.frame_id_list = []
+        self.frame_cache_list = []
+        self.gap = (INFER_LEN - OVERLAP) * 2 - 1 - (OVERLAP - INTERP_LEN)
+        assert self.gap == 41
+        self.id = -1
+        self._engine = None
+        self._cache = None
+
+    def _apply(self, fn, *a, **k):
+        self._engine = None
+        return super()._apply(fn, *a, **k)
+
+    def load_state_dict(self, *a, **k):
+        self._engine = None
+        return super().load_state_dict(*a, **k)
+
+    def engine(self):
+        dev = self.pretrained.cls_token.device
+        if self._engine is None or self._engine.device != dev:
+            self._engine = Engine(self, dev)
+        return self._engine
+
+    def forward(self, x):
+        """Cache-free forward, x f32 [B,T,3,H,W] -> [B,T,H,W] (video_depth_stream.py:62-63)."""
+        eng = self.engine()
+        return torch.stack([eng.forward(x[b].float()).clone() for b in range(x.shape[0])], 0)
+
+    def _free_slot(self):
+        used = set(self.frame_cache_list)
+        for s in range(StreamCache.CAP):
+            if s not in used:
+                return s
+        raise RuntimeError("streaming cache exhausted")
+
+    @torch.no_grad()
+    def infer_video_depth_one(self, frame, input_size=518, device="cuda", fp32=False):
+        """frame uint8 [H0,W0,3] RGB -> float32 [H0,W0] depth of that frame (video_depth_stream.py:77-161)."""
+        self.id += 1
+        dev = self.pretrained.cls_token.device
+        frame = np.asarray(frame)
+        if self.transform is None:  # first frame
+            self.frame_height, self.frame_width = frame.shape[:2]
+            self.transform = net_input_size(self.frame_height, self.frame_width, input_size)
+        else:
+            assert frame.shape[0] == self.frame_height
+            assert frame.shape[1] == self.frame_width
+        nh, nw = self.transform
+        eng = self.engine()
+        with torch.cuda.device(dev):
+            if self._cache is None or self.id == 0:
+                self._cache = StreamCache(eng, nh // 14, nw // 14)
+            x = preprocess_frames(frame[None], [0], nh, nw, dev)
+            slot = self._free_slot()
+            if self.id == 0:
+                cur = []
+            else:
+                cur = self.frame_cache_list[0:2] + self.frame_cache_list[-INFER_LEN + 3:]
+                assert len(cur) == INFER_LEN - 1
+            self._cache.begin_frame(cur, slot)
+            d = eng.forward(x, stream_ctx=self._cache)
+            out = torch.empty(1, self.frame_height, self.frame_width, dtype=torch.float32, device=dev)
+            L.bilinear_f32(d, out, 1, nh, nw, self.frame_height, self.frame_width)
+            new_depth = out[0].cpu().numpy()
+        if self.id == 0:
+            # copy the cache to simulate a full window (video_depth_stream.py:117-119)
+            self.frame_cache_list = [slot] * INFER_LEN
+            self.frame_id_list.extend([0] * (INFER_LEN - 1))
+        else:
+            self.frame_cache_list.append(slot)
+        # adjust the sliding window (video_depth_stream.py:155-159)
+        self.frame_id_list.append(self.id)
+        if self.id + INFER_LEN > self.gap + 1:
+            del self.frame_id_list[1]
+            del self.frame_cache_list[1]
+        return new_depth
