@@ -13,6 +13,7 @@ import torch
 from torch import nn
 
 from . import lib as L
+from . import parallel
 from .engine import Engine
 from .modules import ARCH, DinoEncoder, DPTTemporalHead
 from .preprocess import net_input_size, preprocess_frames
@@ -113,6 +114,22 @@ class VideoDepthAnything(nn.Module):
     def infer_video_depth_device(self, frames, input_size=518, device="cuda", windows=None, return_raw=False):
         """Same as infer_video_depth but leaves the aligned depth [N,H0,W0] on the GPU.
         `windows` restricts the forward passes to a subset (multi-GPU sharding, vda_b200.parallel)."""
+        if windows is None and not return_raw and parallel.active():
+            # one process per GPU (torchrun): shard the windows, all-gather the per-window depth over NCCL
+            n = len(frames)
+            return parallel.distributed_infer(
+                n, window_frame_indices,
+                lambda ids: self.infer_video_depth_device(frames, input_size, device, windows=ids, return_raw=True),
+                lambda raw: align_windows_device(raw, self.metric))
+        prep = self.prepare_video(frames, input_size, device, windows)
+        raw = self.run_windows(prep)
+        if return_raw:
+            return raw
+        return align_windows_device(raw, self.metric)[:prep["n"]]
+
+    def prepare_video(self, frames, input_size=518, device="cuda", windows=None):
+        """Host side of the driver: window composition, one cv2 pre-process per needed source frame
+        (util/transform.py via vda_b200.preprocess), one async H2D copy.  Returns the state run_windows needs."""
         dev = torch.device(device if device != "cuda" else f"cuda:{torch.cuda.current_device()}")
         if self.pretrained.cls_token.device != dev:
             raise RuntimeError(f"model is on {self.pretrained.cls_token.device}, call .to('{dev}') first")
@@ -121,19 +138,23 @@ class VideoDepthAnything(nn.Module):
         nh, nw = net_input_size(h0, w0, input_size)
         wins = window_frame_indices(n)
         mine = list(range(len(wins))) if windows is None else list(windows)
-        eng = self.engine()
+        needed = sorted({i for k in mine for i in wins[k]})
+        slot = {f: j for j, f in enumerate(needed)}
         with torch.cuda.device(dev):
-            needed = sorted({i for k in mine for i in wins[k]})
-            slot = {f: j for j, f in enumerate(needed)}
             net_in = preprocess_frames(frames, needed, nh, nw, dev)            # [len(needed),3,nh,nw] f32 on GPU
-            raw = torch.empty(len(mine) * INFER_LEN, h0, w0, dtype=torch.float32, device=dev)
-            for j, k in enumerate(mine):
-                idx = torch.tensor([slot[f] for f in wins[k]], device=dev)
-                d = eng.forward(net_in.index_select(0, idx))
+            idx = [torch.tensor([slot[f] for f in wins[k]], device=dev) for k in mine]
+        return dict(n=n, h0=h0, w0=w0, nh=nh, nw=nw, mine=mine, net_in=net_in, idx=idx, dev=dev)
+
+    def run_windows(self, prep):
+        """Device side: one forward per owned window + bilinear to the source size -> raw [len*32,H0,W0]."""
+        eng = self.engine()
+        dev, h0, w0, nh, nw = prep["dev"], prep["h0"], prep["w0"], prep["nh"], prep["nw"]
+        with torch.cuda.device(dev):
+            raw = torch.empty(len(prep["mine"]) * INFER_LEN, h0, w0, dtype=torch.float32, device=dev)
+            for j, idx in enumerate(prep["idx"]):
+                d = eng.forward(prep["net_in"].index_select(0, idx))
                 L.bilinear_f32(d, raw[j * INFER_LEN:(j + 1) * INFER_LEN], INFER_LEN, nh, nw, h0, w0)
-            if return_raw:
-                return raw
-            return align_windows_device(raw, self.metric)[:n]
+        return raw
 
 
 def align_windows_device(raw, metric=False, out=None):
