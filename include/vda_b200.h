@@ -48,6 +48,7 @@ typedef struct vda_epilogue {
   /* VDA_ST_HEADDOT: out_f32[row] = relu(b2 + sum_c relu(acc+bias)[c]*w2[c])  (dpt.py:118-124) */
   const float* w2;
   float b2;
+  int cta_pair;         /* 0 = auto, 1 = force the single-CTA kernel, 2 = force the CTA-pair (cta_group::2) kernel */
 } vda_epilogue;
 
 /* C[M,N] = epi(A[M,K] * W[N,K]^T).  A bf16 with row pitch lda (elements, multiple of 8), W bf16

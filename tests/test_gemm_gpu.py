@@ -35,9 +35,37 @@ def test_gemm_plain_bias(L, M, N, K, bn):
     w = _rand(N, K, scale=K ** -0.5, seed=2).bfloat16()
     b = _rand(N, seed=3)
     out = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
-    L.gemm(a, w, L.make_epilogue(bias=b, out=out, ldo=N, block_n=bn))
+    L.gemm(a, w, L.make_epilogue(bias=b, out=out, ldo=N, block_n=bn, cta_pair=1))
     torch.cuda.synchronize()
     _close(out, a.float() @ w.float().T + b)
+
+
+@pytest.mark.parametrize("M,N,K,bn", [
+    (128, 256, 64, 256), (256, 256, 128, 256), (300, 384, 592, 128), (1000, 64, 1024, 64), (129, 64, 64, 64),
+    (1370, 1024, 1024, 128), (4096 + 128, 3072, 1024, 256), (777, 48, 256, 64), (43840, 1024, 1024, 0),
+])
+def test_gemm_cta_pair_kernel(L, M, N, K, bn):
+    """tcgen05.mma.cta_group::2 kernel forced (odd tile counts, ragged M/N, partial pair)."""
+    a = _rand(M, K, seed=1).bfloat16()
+    w = _rand(N, K, scale=K ** -0.5, seed=2).bfloat16()
+    b, g = _rand(N, seed=3), _rand(N, seed=4)
+    out = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
+    L.gemm(a, w, L.make_epilogue(bias=b, scale=g, out=out, ldo=N, block_n=bn, cta_pair=2))
+    torch.cuda.synchronize()
+    _close(out, (a.float() @ w.float().T + b) * g)
+
+
+@pytest.mark.parametrize("n,H,W,C,Cout", [(2, 19, 19, 64, 64), (3, 37, 37, 128, 256), (1, 5, 200, 192, 128)])
+def test_conv3x3_cta_pair_kernel(L, n, H, W, C, Cout):
+    x = _rand(n, C, H, W, seed=1).bfloat16()
+    wt = _rand(Cout, C, 3, 3, scale=(9 * C) ** -0.5, seed=2).bfloat16()
+    b = _rand(Cout, seed=3)
+    want = F.conv2d(x.float(), wt.float(), b, padding=1).permute(0, 2, 3, 1)
+    xn = x.permute(0, 2, 3, 1).contiguous()
+    wk = wt.permute(0, 2, 3, 1).reshape(Cout, 9 * C).contiguous()
+    out = torch.full((n, H, W, Cout), float("nan"), device="cuda", dtype=torch.bfloat16)
+    L.conv3x3(xn, wk, L.make_epilogue(bias=b, out=out, ldo=Cout, cta_pair=2), n, H, W, C, Cout)
+    _close(out, want)
 
 
 def test_gemm_gelu_scale_residual_inplace(L):

@@ -10,7 +10,7 @@
 #include "api_internal.h"
 
 namespace vda {
-cudaError_t launch_gemm(const GemmParams& p, int block_n, int num_sms, cudaStream_t stream);
+cudaError_t launch_gemm(const GemmParams& p, int block_n, bool two_cta, int num_sms, cudaStream_t stream);
 
 static thread_local char g_err[512] = "";
 static int g_num_sms = 0;
@@ -55,16 +55,44 @@ int encode_bf16_map(CUtensorMap* tm, const void* base, int rank, const uint64_t*
   return 0;
 }
 
-static int pick_block_n(int requested, int N, int m_tiles, int store_mode) {
-  if (store_mode == ST_HEADDOT) return 32;
-  if (requested) return requested;
+// Tile selection.  CTA pairs (256 x BN per pair, half of W per CTA) whenever some BN in {256,128,64}
+// wastes <= 12.5 % of the padded N and leaves at least one full wave of pair tiles for the 74 SM
+// pairs; otherwise the single-CTA kernel with the largest BN that still fills the SMs.
+static void pick_tile(const vda_epilogue* e, int N, int m_tiles, int* bn_out, bool* two_out) {
+  if (e->store_mode == ST_HEADDOT) {
+    *bn_out = 32, *two_out = false;
+    return;
+  }
+  const int n16 = ((N + 15) / 16) * 16;
+  if (e->cta_pair != 1) {
+    const int m2 = (m_tiles + 1) / 2;
+    const int cands2[3] = {256, 128, 64};
+    for (int i = 0; i < 3; ++i) {
+      const int bn = cands2[i];
+      if (e->block_n && e->block_n != bn) continue;
+      const int nt = (N + bn - 1) / bn;
+      const bool forced = e->cta_pair == 2;
+      if (!forced && (nt * bn - n16) * 8 > nt * bn) continue;
+      if (!forced && static_cast<long long>(m2) * nt < g_num_sms / 2) continue;
+      *bn_out = bn, *two_out = true;
+      return;
+    }
+  }
+  *two_out = false;
+  if (e->block_n) {
+    *bn_out = e->block_n;
+    return;
+  }
   const int cands[4] = {256, 128, 64, 32};
   for (int i = 0; i < 4; ++i) {
     const int bn = cands[i];
     if (bn > 32 && bn > ((N + 31) / 32) * 32) continue;
-    if (static_cast<long long>(m_tiles) * ((N + bn - 1) / bn) >= g_num_sms) return bn;
+    if (static_cast<long long>(m_tiles) * ((N + bn - 1) / bn) >= g_num_sms) {
+      *bn_out = bn;
+      return;
+    }
   }
-  return N >= 64 ? 64 : 32;
+  *bn_out = N >= 64 ? 64 : 32;
 }
 
 static int fill_epilogue(GemmParams& p, const vda_epilogue* e) {
@@ -145,7 +173,9 @@ int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, 
   p.m_tiles = (M + 127) / 128;
   int rc = fill_epilogue(p, epi);
   if (rc) return rc;
-  const int bn = pick_block_n(epi->block_n, N, p.m_tiles, epi->store_mode);
+  int bn;
+  bool two;
+  pick_tile(epi, N, p.m_tiles, &bn, &two);
   p.n_tiles = (N + bn - 1) / bn;
   {
     const uint64_t dims[2] = {(uint64_t)K, (uint64_t)M};
@@ -156,10 +186,10 @@ int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, 
   {
     const uint64_t dims[2] = {(uint64_t)K, (uint64_t)N};
     const uint64_t str[1] = {(uint64_t)ldw * 2};
-    const uint32_t box[2] = {64, (uint32_t)bn};
+    const uint32_t box[2] = {64, (uint32_t)(two ? bn / 2 : bn)};
     if ((rc = encode_bf16_map(&p.tmB, W, 2, dims, str, box))) return rc;
   }
-  return check_cuda(launch_gemm(p, bn, g_num_sms, static_cast<cudaStream_t>(stream)), "gemm launch");
+  return check_cuda(launch_gemm(p, bn, two, g_num_sms, static_cast<cudaStream_t>(stream)), "gemm launch");
 }
 
 int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W, int C, int Cout,
@@ -185,7 +215,9 @@ int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W,
   int rc = fill_epilogue(p, epi);
   if (rc) return rc;
   if (epi->store_mode != ST_PLAIN && epi->store_mode != ST_HEADDOT) return set_error(-1, "conv3x3: unsupported store mode");
-  const int bn = pick_block_n(epi->block_n, Cout, p.m_tiles, epi->store_mode);
+  int bn;
+  bool two;
+  pick_tile(epi, Cout, p.m_tiles, &bn, &two);
   p.n_tiles = (Cout + bn - 1) / bn;
   {
     const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)n};
@@ -196,10 +228,10 @@ int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W,
   {
     const uint64_t dims[2] = {(uint64_t)(9 * C), (uint64_t)Cout};
     const uint64_t str[1] = {(uint64_t)(9 * C) * 2};
-    const uint32_t box[2] = {64, (uint32_t)bn};
+    const uint32_t box[2] = {64, (uint32_t)(two ? bn / 2 : bn)};
     if ((rc = encode_bf16_map(&p.tmB, w, 2, dims, str, box))) return rc;
   }
-  return check_cuda(launch_gemm(p, bn, g_num_sms, static_cast<cudaStream_t>(stream)), "conv3x3 launch");
+  return check_cuda(launch_gemm(p, bn, two, g_num_sms, static_cast<cudaStream_t>(stream)), "conv3x3 launch");
 }
 
 }  // extern "C"

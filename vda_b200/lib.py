@@ -23,7 +23,7 @@ class Epilogue(C.Structure):
         ("ct_s", C.c_int), ("ct_cout", C.c_int), ("ct_h", C.c_int), ("ct_w", C.c_int),
         ("vt", C.c_void_p),
         ("qkv_d", C.c_int), ("qkv_heads", C.c_int), ("qkv_s", C.c_int), ("qkv_spad", C.c_int),
-        ("w2", C.c_void_p), ("b2", C.c_float),
+        ("w2", C.c_void_p), ("b2", C.c_float), ("cta_pair", C.c_int),
     ]
 
 
@@ -139,7 +139,7 @@ def ptr(t):
 
 def make_epilogue(bias=None, scale=None, res_f32=None, res1=None, res2=None, out=None, out_relu=None,
                   out_f32=None, ldo=0, act=ACT_NONE, store_mode=ST_PLAIN, block_n=0, ct=None, qkv=None,
-                  w2=None, b2=0.0):
+                  w2=None, b2=0.0, cta_pair=0):
     e = Epilogue()
     e.bias, e.scale, e.res_f32 = ptr(bias), ptr(scale), ptr(res_f32)
     e.res1, e.res2 = ptr(res1), ptr(res2)
@@ -150,7 +150,7 @@ def make_epilogue(bias=None, scale=None, res_f32=None, res1=None, res2=None, out
     if qkv is not None:
         vt, d, heads, s, spad = qkv
         e.vt, e.qkv_d, e.qkv_heads, e.qkv_s, e.qkv_spad = ptr(vt), d, heads, s, spad
-    e.w2, e.b2 = ptr(w2), b2
+    e.w2, e.b2, e.cta_pair = ptr(w2), b2, cta_pair
     return e
 
 
