@@ -84,42 +84,50 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_kernel(const __grid_c
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tmem_S = tmem_base, tmem_O = tmem_base + 128;
 
+  // producer / MMA loops run warp-convergent with single-lane issue (see gemm.cu for why)
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_expect_tx(q_full, kQBytes);
       tma_load_3d(sQ, &p.tmQK, q_full, head * 64, qt * 128, frame);
-      for (int j = 0; j < p.kv_tiles; ++j) {
-        const int st = j & 1;
-        mbar_wait(&kv_empty[st], ((j >> 1) & 1) ^ 1);
-        uint8_t* sk = sKV + st * kKVStage;
+    }
+    __syncwarp();
+    for (int j = 0; j < p.kv_tiles; ++j) {
+      const int st = j & 1;
+      mbar_wait(&kv_empty[st], ((j >> 1) & 1) ^ 1);
+      uint8_t* sk = sKV + st * kKVStage;
+      if (elect_one()) {
         mbar_expect_tx(&kv_full[st], kKVStage);
         tma_load_3d(sk, &p.tmQK, &kv_full[st], p.D + head * 64, j * 128, frame);
         tma_load_3d(sk + kKBytes, &p.tmV, &kv_full[st], j * 128, 0, frame * p.heads + head);
         tma_load_3d(sk + kKBytes + kVBytes / 2, &p.tmV, &kv_full[st], j * 128 + 64, 0, frame * p.heads + head);
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc_s = umma_idesc_f16(128, 128, true);
-      constexpr uint32_t idesc_o = umma_idesc_f16(128, 64, true);
-      const uint64_t qdesc = umma_desc_k_sw128(smem_u32(sQ));
-      const uint32_t p_addr = smem_u32(sP);
-      auto issue_s = [&](int j) {
-        const int st = j & 1;
-        mbar_wait(&kv_full[st], (j >> 1) & 1);
-        tc_fence_after();
-        const uint64_t kdesc = umma_desc_k_sw128(smem_u32(sKV + st * kKVStage));
+    constexpr uint32_t idesc_s = umma_idesc_f16(128, 128, true);
+    constexpr uint32_t idesc_o = umma_idesc_f16(128, 64, true);
+    const uint64_t qdesc = umma_desc_k_sw128(smem_u32(sQ));
+    const uint32_t p_addr = smem_u32(sP);
+    auto issue_s = [&](int j) {
+      const int st = j & 1;
+      mbar_wait(&kv_full[st], (j >> 1) & 1);
+      tc_fence_after();
+      const uint64_t kdesc = umma_desc_k_sw128(smem_u32(sKV + st * kKVStage));
+      if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_f16_ss(tmem_S, qdesc + 2 * k, kdesc + 2 * k, idesc_s, k != 0);
         umma_commit(s_full);
-      };
-      mbar_wait(q_full, 0);
-      issue_s(0);
-      for (int j = 0; j < p.kv_tiles; ++j) {
-        const int st = j & 1;
-        mbar_wait(p_full, j & 1);
-        tc_fence_after();
-        const uint32_t v_addr = smem_u32(sKV + st * kKVStage + kKBytes);
+      }
+      __syncwarp();
+    };
+    mbar_wait(q_full, 0);
+    issue_s(0);
+    for (int j = 0; j < p.kv_tiles; ++j) {
+      const int st = j & 1;
+      mbar_wait(p_full, j & 1);
+      tc_fence_after();
+      const uint32_t v_addr = smem_u32(sKV + st * kKVStage + kKBytes);
+      if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const uint64_t pdesc = umma_desc_k_sw128(p_addr + (k >> 2) * (128 * 128)) + 2 * (k & 3);
@@ -128,8 +136,9 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_kernel(const __grid_c
         }
         umma_commit(o_full);
         umma_commit(&kv_empty[st]);
-        if (j + 1 < p.kv_tiles) issue_s(j + 1);
       }
+      __syncwarp();
+      if (j + 1 < p.kv_tiles) issue_s(j + 1);
     }
   } else {
     // ------------------------------------------------------------- softmax warps

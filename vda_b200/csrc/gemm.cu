@@ -101,19 +101,23 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // The producer and MMA loops are executed by their WHOLE warp (all addresses and descriptors stay
+  // warp-uniform, i.e. in uniform registers) and only the issuing instructions are predicated on one
+  // elected lane.  Running the loops under `if (lane == 0)` made ptxas wrap every tcgen05.mma in an
+  // elect / R2UR.BROADCAST sequence and the single issuing thread, not the tensor pipe, set the pace.
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      const int cblocks = (p.a_mode == A_CONV3X3) ? (p.C / kBlockK) : 1;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m_t = tile / p.n_tiles, n_t = tile - m_t * p.n_tiles;
-        TileCoord tc = {0, 0, 0};
-        if (p.a_mode == A_CONV3X3) tc = conv_tile_coord(p, m_t);
-        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          uint8_t* sa = smem + stage * Cfg::kStageBytes;
-          uint8_t* sb = sa + Cfg::kABytes;
+    int stage = 0;
+    uint32_t phase = 0;
+    const int cblocks = (p.a_mode == A_CONV3X3) ? (p.C / kBlockK) : 1;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m_t = tile / p.n_tiles, n_t = tile - m_t * p.n_tiles;
+      TileCoord tc = {0, 0, 0};
+      if (p.a_mode == A_CONV3X3) tc = conv_tile_coord(p, m_t);
+      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sa = smem + stage * Cfg::kStageBytes;
+        uint8_t* sb = sa + Cfg::kABytes;
+        if (elect_one()) {
           mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
           if (p.a_mode == A_CONV3X3) {
             const int tap = kb / cblocks, cb = kb - tap * cblocks;
@@ -123,37 +127,39 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
             tma_load_2d(sa, &p.tmA, &full_bar[stage], kb * kBlockK, m_t * kBlockM);
           }
           tma_load_2d(sb, &p.tmB, &full_bar[stage], kb * kBlockK, n_t * BN);
-          if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
         }
+        __syncwarp();
+        if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_f16(kBlockM, BN, true);
-      int stage = 0;
-      uint32_t phase = 0;
-      int it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-        const int as = it & 1;
-        const uint32_t aphase = (it >> 1) & 1;
-        mbar_wait(&tempty_bar[as], aphase ^ 1);
+    constexpr uint32_t idesc = umma_idesc_f16(kBlockM, BN, true);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      mbar_wait(&tempty_bar[as], aphase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BN;
+      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
-          tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
-          const uint64_t adesc = umma_desc_k_sw128(sa);
-          const uint64_t bdesc = umma_desc_k_sw128(sa + Cfg::kABytes);
+        const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+        const uint64_t adesc = umma_desc_k_sw128(sa);
+        const uint64_t bdesc = umma_desc_k_sw128(sa + Cfg::kABytes);
+        if (elect_one()) {
 #pragma unroll
           for (int k = 0; k < kBlockK / 16; ++k) {
             // +32 B per K=16 step inside the 128 B swizzle row (start-address field is >>4)
             umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
           }
           umma_commit(&empty_bar[stage]);
-          if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
+          if (kb == p.num_k_blocks - 1) umma_commit(&tfull_bar[as]);
         }
-        umma_commit(&tfull_bar[as]);
+        __syncwarp();
+        if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
       }
     }
   } else if (warp >= 4) {
@@ -242,19 +248,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      const int cblocks = (p.a_mode == A_CONV3X3) ? (p.C / kBlockK) : 1;
-      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-        const int m2 = tile / p.n_tiles, n_t = tile - m2 * p.n_tiles;
-        const int m_t = 2 * m2 + static_cast<int>(rank);
-        TileCoord tc = {0, 0, 0};
-        if (p.a_mode == A_CONV3X3) tc = conv_tile_coord(p, m_t);
-        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          uint8_t* sa = smem + stage * Cfg::kStageBytes;
-          uint8_t* sb = sa + Cfg::kABytes;
+    int stage = 0;
+    uint32_t phase = 0;
+    const int cblocks = (p.a_mode == A_CONV3X3) ? (p.C / kBlockK) : 1;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      const int m2 = tile / p.n_tiles, n_t = tile - m2 * p.n_tiles;
+      const int m_t = 2 * m2 + static_cast<int>(rank);
+      TileCoord tc = {0, 0, 0};
+      if (p.a_mode == A_CONV3X3) tc = conv_tile_coord(p, m_t);
+      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* sa = smem + stage * Cfg::kStageBytes;
+        uint8_t* sb = sa + Cfg::kABytes;
+        if (elect_one()) {
           if (leader) mbar_expect_tx(&full_bar[stage], 2 * Cfg::kStageBytes);
           if (p.a_mode == A_CONV3X3) {
             const int tap = kb / cblocks, cb = kb - tap * cblocks;
@@ -264,12 +270,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
             tma_load_2d_2sm(sa, &p.tmA, &full_bar[stage], kb * kBlockK, m_t * kBlockM);
           }
           tma_load_2d_2sm(sb, &p.tmB, &full_bar[stage], kb * kBlockK, n_t * BN + static_cast<int>(rank) * (BN / 2));
-          if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
         }
+        __syncwarp();
+        if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
       }
     }
   } else if (warp == 1) {
-    if (leader && lane == 0) {
+    if (leader) {
       constexpr uint32_t idesc = umma_idesc_f16(2 * kBlockM, BN, true);
       int stage = 0;
       uint32_t phase = 0;
@@ -286,13 +293,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
           const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
           const uint64_t adesc = umma_desc_k_sw128(sa);
           const uint64_t bdesc = umma_desc_k_sw128(sa + Cfg::kABytes);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < kBlockK / 16; ++k)
-            umma_f16_ss_2cta(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
-          umma_commit_2cta(&empty_bar[stage]);
+            for (int k = 0; k < kBlockK / 16; ++k)
+              umma_f16_ss_2cta(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+            umma_commit_2cta(&empty_bar[stage]);
+            if (kb == p.num_k_blocks - 1) umma_commit_2cta(&tfull_bar[as]);
+          }
+          __syncwarp();
           if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
         }
-        umma_commit_2cta(&tfull_bar[as]);
       }
     }
   } else if (warp >= 4) {

@@ -220,45 +220,42 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, int m_tile, i
     return;
   }
 
-  uint32_t raw[2][32];
-  tmem_ld32(t_acc + cbeg, raw[0]);
+  // One 16-column group per iteration, deliberately NOT unrolled: the generic epilogue body is a
+  // few hundred instructions and an unrolled tile loop overflowed the instruction cache (ncu:
+  // "no_instruction" stalls, 134 KB of SASS), which made the epilogue, not the MMA, set the pace.
   const bool pre = p.res_f32 != nullptr && p.store_mode == ST_PLAIN && rm.valid;
+  constexpr int kStep = 16;
+  const int step = (p.act == ACT_GEGLU) ? 32 : kStep;
+#pragma unroll 1
+  for (int c0 = cbeg; c0 < cbeg + kPer && c0 < BN; c0 += step) {
+    const int col = n_t * BN + c0;
+    uint32_t raw[16], gate[16];
+    __syncwarp();
+    tmem_ld16(t_acc + c0, raw);
+    if (p.act == ACT_GEGLU) tmem_ld16(t_acc + c0 + 16, gate);
+    float4 rpre[4];
+    if (pre && col < p.N) {
+      const float4* src = reinterpret_cast<const float4*>(p.res_f32 + rm.row * p.ldo + col);
 #pragma unroll
-  for (int ci = 0; ci < kChunks; ++ci) {
-    const int c0 = cbeg + ci * 32;
-    const int colc = n_t * BN + c0;
-    float4 rpre[8];
-    if (pre) {
-      const float4* src = reinterpret_cast<const float4*>(p.res_f32 + rm.row * p.ldo + colc);
-#pragma unroll
-      for (int i = 0; i < 8; ++i)
-        if (colc + 4 * i < p.N) rpre[i] = __ldcs(src + i);
+      for (int i = 0; i < 4; ++i) rpre[i] = __ldcs(src + i);
     }
     tmem_ld_wait();
-    if (ci + 1 < kChunks) tmem_ld32(t_acc + c0 + 32, raw[(ci + 1) & 1]);
-    if (!rm.valid) continue;
-    const uint32_t(&acc)[32] = raw[ci & 1];
+    if (!rm.valid || col >= p.N) continue;
+    float v[16], b[16];
+    lds_f32x16(s_bias + c0, b);
     if (p.act == ACT_GEGLU) {
       // physical columns [32j, 32j+16) = value, [32j+16, 32j+32) = gate -> output columns [16j, 16j+16)
-      if (colc < p.N) {
-        float v[16];
+      float bg[16];
+      lds_f32x16(s_bias + c0 + 16, bg);
 #pragma unroll
-        for (int i = 0; i < 16; ++i)
-          v[i] = (__uint_as_float(acc[i]) + s_bias[c0 + i]) * gelu_fast(__uint_as_float(acc[16 + i]) + s_bias[c0 + 16 + i]);
-        store_bf16x16(p.out + rm.row * p.ldo + (colc >> 1), v);
-      }
+      for (int i = 0; i < 16; ++i)
+        v[i] = (__uint_as_float(raw[i]) + b[i]) * gelu_fast(__uint_as_float(gate[i]) + bg[i]);
+      store_bf16x16(p.out + rm.row * p.ldo + (col >> 1), v);
       continue;
     }
 #pragma unroll
-    for (int g = 0; g < 2; ++g) {
-      const int col = colc + 16 * g;
-      if (col >= p.N) continue;
-      float v[16], b[16];
-      lds_f32x16(s_bias + c0 + 16 * g, b);
-#pragma unroll
-      for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(acc[16 * g + i]) + b[i];
-      finish_group16(p, rm, col, v, s_scale + c0 + 16 * g, pre ? &rpre[4 * g] : nullptr);
-    }
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(raw[i]) + b[i];
+    finish_group16(p, rm, col, v, s_scale + c0, pre ? rpre : nullptr);
   }
 }
 
