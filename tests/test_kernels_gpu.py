@@ -45,6 +45,26 @@ def test_flash_attention(L, frames, S, heads):
     _close(out.view(frames, S, heads, 64), want.transpose(1, 2), 2e-2)
 
 
+def test_flash_attention_growing_maxima(L):
+    """Key magnitudes grow along the sequence, so the running row maximum jumps by far more than the
+    lazy-rescale threshold (2^8) at several KV tiles: exercises the in-TMEM rescale of O."""
+    frames, S, heads = 2, 1000, 2
+    D = heads * 64
+    spad = (S + 7) // 8 * 8
+    q = _rand(frames, S, heads, 64, scale=2.0, seed=1).bfloat16()
+    ramp = torch.linspace(0.2, 6.0, S, device="cuda").view(1, S, 1, 1)
+    k = (_rand(frames, S, heads, 64, seed=2) * ramp).bfloat16()
+    v = _rand(frames, S, heads, 64, seed=3).bfloat16()
+    qk = torch.cat([q.reshape(frames * S, D), k.reshape(frames * S, D)], dim=1).contiguous()
+    vt = torch.zeros(frames * heads, 64, spad, device="cuda", dtype=torch.bfloat16)
+    vt[:, :, :S] = v.permute(0, 2, 3, 1).reshape(frames * heads, 64, S)
+    out = torch.full((frames * S, D), float("nan"), device="cuda", dtype=torch.bfloat16)
+    L.flash_attn(qk, vt, out, frames, S, heads, spad)
+    torch.cuda.synchronize()
+    want = F.scaled_dot_product_attention(q.float().transpose(1, 2), k.float().transpose(1, 2), v.float().transpose(1, 2))
+    _close(out.view(frames, S, heads, 64), want.transpose(1, 2), 2e-2)
+
+
 @pytest.mark.parametrize("rows,C,f32", [(100, 384, True), (2740, 1024, True), (77, 256, False), (50, 64, False), (33, 768, True), (10, 192, False)])
 def test_layernorm(L, rows, C, f32):
     x = _rand(rows, C, scale=2.0, seed=1) + 0.5

@@ -14,6 +14,7 @@
 //   warp 2-5  softmax: one thread per query row (tcgen05.ld 32x32b): running max/sum in registers,
 //             P written to shared memory as bf16 in the UMMA K-major 128B-swizzled layout,
 //             O accumulated in fp32 registers with the online-softmax rescale.
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -239,6 +240,254 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_kernel(const __grid_c
   }
 }
 
+// =============================================================================================
+// v2: S row in registers, P and O in TMEM.
+//   * the softmax thread pulls its whole 128-column S row into registers with one burst of
+//     tcgen05.ld and immediately frees the S buffer, so S_{j+1} = Q K_{j+1}^T runs on the tensor pipe
+//     while the exponentials of tile j are still being computed;
+//   * P_j is written back to TMEM as packed bf16 (tcgen05.st) and the PV MMA takes it as its A operand
+//     straight from TMEM (no 32 KB/tile shared-memory round trip, no proxy fence);
+//   * O accumulates in TMEM across KV tiles; it is rescaled (tcgen05.ld / st) only when a row
+//     maximum grows by more than 2^8 ("lazy rescale": p <= 256, harmless in fp32 / bf16);
+//   * K and V have separate 2-stage rings: K_j is released as soon as S_j has been computed.
+// TMEM per CTA: S cols [0,128), P cols [128,192), O cols [192,256); two CTAs per SM.
+constexpr int kA2Smem = kQBytes + 2 * kKBytes + 2 * kVBytes + 256;
+constexpr float kRescaleThreshold = 8.0f;
+
+__global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __grid_constant__ AttnParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  if ((smem_u32(smem) & 1023u) != 0) __trap();
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + kQBytes;          // [2][16 KB]
+  uint8_t* sV = sK + 2 * kKBytes;        // [2][16 KB]  (two 64x64 sub-tiles each)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sV + 2 * kVBytes);
+  uint64_t* q_full = bars;
+  uint64_t* k_full = bars + 1;    // [2]
+  uint64_t* k_empty = bars + 3;   // [2]
+  uint64_t* v_full = bars + 5;    // [2]
+  uint64_t* v_empty = bars + 7;   // [2]
+  uint64_t* s_full = bars + 9;
+  uint64_t* s_free = bars + 10;
+  uint64_t* p_full = bars + 11;
+  uint64_t* o_done = bars + 12;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qt = blockIdx.x, head = blockIdx.y, frame = blockIdx.z;
+  const int n_tiles = p.kv_tiles;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tmQK);
+    tma_prefetch_desc(&p.tmV);
+    mbar_init(q_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&k_full[s], 1), mbar_init(&k_empty[s], 1);
+      mbar_init(&v_full[s], 1), mbar_init(&v_empty[s], 1);
+    }
+    mbar_init(s_full, 1);
+    mbar_init(s_free, 4);
+    mbar_init(p_full, 4);
+    mbar_init(o_done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, kAttTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_S = tmem_base, tmem_P = tmem_base + 128, tmem_O = tmem_base + 192;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (elect_one()) {
+      mbar_expect_tx(q_full, kQBytes);
+      tma_load_3d(sQ, &p.tmQK, q_full, head * 64, qt * 128, frame);
+    }
+    __syncwarp();
+    for (int j = 0; j < n_tiles; ++j) {
+      const int st = j & 1;
+      const uint32_t ph = ((j >> 1) & 1) ^ 1;
+      mbar_wait(&k_empty[st], ph);
+      if (elect_one()) {
+        mbar_expect_tx(&k_full[st], kKBytes);
+        tma_load_3d(sK + st * kKBytes, &p.tmQK, &k_full[st], p.D + head * 64, j * 128, frame);
+      }
+      __syncwarp();
+      mbar_wait(&v_empty[st], ph);
+      if (elect_one()) {
+        mbar_expect_tx(&v_full[st], kVBytes);
+        tma_load_3d(sV + st * kVBytes, &p.tmV, &v_full[st], j * 128, 0, frame * p.heads + head);
+        tma_load_3d(sV + st * kVBytes + kVBytes / 2, &p.tmV, &v_full[st], j * 128 + 64, 0, frame * p.heads + head);
+      }
+      __syncwarp();
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
+    constexpr uint32_t idesc_s = umma_idesc_f16(128, 128, true);
+    constexpr uint32_t idesc_o = umma_idesc_f16(128, 64, true);
+    const uint64_t qdesc = umma_desc_k_sw128(smem_u32(sQ));
+    auto issue_s = [&](int j) {
+      const int st = j & 1;
+      mbar_wait(&k_full[st], (j >> 1) & 1);
+      if (j > 0) mbar_wait(s_free, (j - 1) & 1);  // softmax has drained S_{j-1} from TMEM
+      tc_fence_after();
+      const uint64_t kdesc = umma_desc_k_sw128(smem_u32(sK + st * kKBytes));
+      if (elect_one()) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_f16_ss(tmem_S, qdesc + 2 * k, kdesc + 2 * k, idesc_s, k != 0);
+        umma_commit(s_full);
+        umma_commit(&k_empty[st]);
+      }
+      __syncwarp();
+    };
+    mbar_wait(q_full, 0);
+    issue_s(0);
+    for (int j = 0; j < n_tiles; ++j) {
+      const int st = j & 1;
+      if (j + 1 < n_tiles) issue_s(j + 1);
+      mbar_wait(&v_full[st], (j >> 1) & 1);
+      mbar_wait(p_full, j & 1);
+      tc_fence_after();
+      const uint32_t v_addr = smem_u32(sV + st * kVBytes);
+      if (elect_one()) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          // K = 16 kv positions per MMA: 8 packed-bf16 TMEM columns of P, 32 B of each V^T row
+          const uint64_t vdesc = umma_desc_k_sw128(v_addr + (k >> 2) * (64 * 128)) + 2 * (k & 3);
+          umma_f16_ts(tmem_O, tmem_P + 8 * k, vdesc, idesc_o, (j | k) != 0);
+        }
+        umma_commit(o_done);
+        umma_commit(&v_empty[st]);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ------------------------------------------------------------------ softmax warps (thread = query row)
+    const int quad = warp & 3;
+    const int r = quad * 32 + lane;
+    const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;
+    const int q_idx = qt * 128 + r;
+    const float sc = p.scale_log2;
+    float m_run = -INFINITY, l_run = 0.f;
+
+    for (int j = 0; j < n_tiles; ++j) {
+      mbar_wait(s_full, j & 1);
+      tc_fence_after();
+      uint32_t s[128];
+      {
+        uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
+        uint32_t(&s1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
+        uint32_t(&s2)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[64]);
+        uint32_t(&s3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[96]);
+        tmem_ld32(tmem_S + lane_off + 0, s0);
+        tmem_ld32(tmem_S + lane_off + 32, s1);
+        tmem_ld32(tmem_S + lane_off + 64, s2);
+        tmem_ld32(tmem_S + lane_off + 96, s3);
+        tmem_ld_wait();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(s_free);
+      const int kv_left = p.S - j * 128;
+      if (kv_left < 128) {
+#pragma unroll
+        for (int c = 0; c < 128; ++c)
+          if (c >= kv_left) s[c] = 0xff800000u;  // -inf
+      }
+      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+      for (int c = 0; c < 128; c += 4) {
+        mx0 = fmaxf(mx0, __uint_as_float(s[c]));
+        mx1 = fmaxf(mx1, __uint_as_float(s[c + 1]));
+        mx2 = fmaxf(mx2, __uint_as_float(s[c + 2]));
+        mx3 = fmaxf(mx3, __uint_as_float(s[c + 3]));
+      }
+      const float m_tile = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * sc;
+      bool need = false;
+      float alpha = 1.f;
+      if (j == 0) {
+        m_run = m_tile;
+      } else {
+        need = m_tile > m_run + kRescaleThreshold;
+        if (need) {
+          alpha = fast_exp2(m_run - m_tile);
+          m_run = m_tile;
+          l_run *= alpha;
+        }
+        // PV_{j-1} must be complete before P is overwritten (and before O is rescaled)
+        mbar_wait(o_done, (j - 1) & 1);
+        tc_fence_after();
+        if (__any_sync(0xffffffffu, need)) {
+#pragma unroll
+          for (int c0 = 0; c0 < 64; c0 += 32) {
+            uint32_t o[32];
+            tmem_ld32(tmem_O + lane_off + c0, o);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st32(tmem_O + lane_off + c0, o);
+          }
+        }
+      }
+      const float neg_m = -m_run;
+      float l0 = 0.f, l1 = 0.f;
+#pragma unroll
+      for (int c0 = 0; c0 < 128; c0 += 32) {
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          const float p0 = fast_exp2(fmaf(__uint_as_float(s[c0 + i]), sc, neg_m));
+          const float p1 = fast_exp2(fmaf(__uint_as_float(s[c0 + i + 1]), sc, neg_m));
+          l0 += p0;
+          l1 += p1;
+          __nv_bfloat162 h = __floats2bfloat162_rn(p0, p1);
+          pk[i >> 1] = *reinterpret_cast<uint32_t*>(&h);
+        }
+        tmem_st16(tmem_P + lane_off + (c0 >> 1), pk);
+      }
+      l_run += l0 + l1;
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(p_full);
+    }
+    // ---- epilogue: O / l -> bf16
+    mbar_wait(o_done, (n_tiles - 1) & 1);
+    tc_fence_after();
+    const float inv = 1.0f / l_run;
+    bf16* dst = p.out + (static_cast<long long>(frame) * p.S + q_idx) * p.D + head * 64;
+#pragma unroll
+    for (int c0 = 0; c0 < 64; c0 += 32) {
+      uint32_t o[32];
+      tmem_ld32(tmem_O + lane_off + c0, o);
+      tmem_ld_wait();
+      if (q_idx < p.S) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t w[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(o[8 * c + 2 * i]) * inv,
+                                                     __uint_as_float(o[8 * c + 2 * i + 1]) * inv);
+            w[i] = *reinterpret_cast<uint32_t*>(&h);
+          }
+          reinterpret_cast<uint4*>(dst + c0)[c] = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kAttTmemCols);
+  }
+}
+
 }  // namespace vda
 
 using namespace vda;
@@ -270,13 +519,22 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
   p.kv_tiles = (S + 127) / 128;
   p.scale_log2 = 0.125f * 1.4426950408889634f;
   static bool configured = false;
+  static int variant = 2;
   if (!configured) {
+    const char* v = getenv("VDA_ATTN_VARIANT");  // 1 = first-generation kernel (P via smem), kept for A/B runs
+    if (v && v[0] == '1') variant = 1;
     int rc = check_cuda(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmem),
                         "attn smem attribute");
+    if (rc) return rc;
+    rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem),
+                    "attn v2 smem attribute");
     if (rc) return rc;
     configured = true;
   }
   dim3 grid(p.q_tiles, heads, frames);
-  attn_fwd_kernel<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(stream)>>>(p);
+  if (variant == 1)
+    attn_fwd_kernel<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(stream)>>>(p);
+  else
+    attn_fwd_v2_kernel<<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
   return check_cuda(cudaGetLastError(), "attn launch");
 }
