@@ -26,7 +26,15 @@ ao = torch.empty(M, D, device=dev, dtype=torch.bfloat16)
 h1 = torch.empty(M, 4 * D, device=dev, dtype=torch.bfloat16)
 lnw, lnb = r(D), r(D)
 
+# DPT-head 3x3 convolutions (refinenet level: 32 frames, 256 ch, 148x148 and 296x296 / 128->32 tail)
+cx = r(T, 148, 148, 256).to(torch.bfloat16)
+cw = r(256, 9 * 256).to(torch.bfloat16)
+cb = r(256)
+cy = torch.empty(T, 148, 148, 256, device=dev, dtype=torch.bfloat16)
+
 ops = {
+    "conv148": (lambda: L.conv3x3(cx, cw, L.make_epilogue(bias=cb, out=cy, ldo=256, act=L.ACT_RELU), T, 148, 148, 256, 256),
+                2 * T * 148 * 148 * 256 * 9 * 256),
     "ln": (lambda: L.layernorm(tok, lnw, lnb, xn, 1e-6), 0),
     "qkv": (lambda: L.gemm(xn, wqkv, L.make_epilogue(bias=bqkv, out=qk, ldo=2 * D, store_mode=L.ST_QKV,
                                                      qkv=(vt, D, heads, S, spad))), 2 * M * 3 * D * D),
@@ -38,22 +46,50 @@ ops = {
             2 * M * 4 * D * D),
     "fc1_bias": (lambda: L.gemm(xn, w1, L.make_epilogue(bias=b1, out=h1, ldo=4 * D)), 2 * M * 4 * D * D),
     "fc1_relu": (lambda: L.gemm(xn, w1, L.make_epilogue(bias=b1, out=h1, ldo=4 * D, act=L.ACT_RELU)), 2 * M * 4 * D * D),
+    "proj_wf32": (lambda: L.gemm(ao, wproj, L.make_epilogue(bias=bproj, scale=g1, out_f32=tok, ldo=D)), 2 * M * D * D),
+    "proj_rres": (lambda: L.gemm(ao, wproj, L.make_epilogue(bias=bproj, scale=g1, res_f32=tok, out=xn, ldo=D)), 2 * M * D * D),
+    "proj_bias": (lambda: L.gemm(ao, wproj, L.make_epilogue(bias=bproj, scale=g1, out=xn, ldo=D)), 2 * M * D * D),
     "fc1_plain": (lambda: L.gemm(xn, w1, L.make_epilogue(out=h1, ldo=4 * D)), 2 * M * 4 * D * D),
     "proj_plain": (lambda: L.gemm(ao, wproj, L.make_epilogue(out=xn, ldo=D)), 2 * M * D * D),
 }
-only = sys.argv[1:] or list(ops)
-tot = 0.0
-for name in only:
-    fn, flops = ops[name]
-    for _ in range(3):
-        fn()
+# usage: bench_ops.py [op ...] [--env NAME=v1,v2,...]  -> every op is timed under each value of the
+# environment knob, interleaved round-robin over 5 rounds; the best round of each is reported.
+args = sys.argv[1:]
+env_name, env_vals = None, [None]
+if "--env" in args:
+    i = args.index("--env")
+    env_name, vals = args[i + 1].split("=")
+    env_vals = vals.split(",")
+    del args[i:i + 2]
+only = args or list(ops)
+
+
+def timed(fn, iters=15):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(20):
+    for _ in range(iters):
         fn()
     e1.record()
     torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / 20
-    tot += ms if "plain" not in name else 0
-    print(f"{name:10s} {ms * 1e3:8.1f} us  {flops / ms / 1e9:7.0f} TFLOP/s")
-print(f"sum of non-plain ops {tot:.3f} ms")
+    return e0.elapsed_time(e1) / iters
+
+
+best = {}
+for rnd in range(5):
+    for name in only:
+        for val in env_vals:
+            if env_name:
+                os.environ[env_name] = val
+            fn = ops[name][0]
+            fn()
+            ms = timed(fn)
+            best[(name, val)] = min(best.get((name, val), 1e9), ms)
+tot = {v: 0.0 for v in env_vals}
+for name in only:
+    for val in env_vals:
+        ms, flops = best[(name, val)], ops[name][1]
+        tot[val] += ms if "plain" not in name and "bias" not in name and "relu" not in name else 0
+        tag = f" [{env_name}={val}]" if env_name else ""
+        print(f"{name:10s} {ms * 1e3:8.1f} us  {flops / ms / 1e9:7.0f} TFLOP/s{tag}")
+for val in env_vals:
+    print(f"sum of block ops {tot[val]:.3f} ms" + (f" [{env_name}={val}]" if env_name else ""))

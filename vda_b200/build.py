@@ -6,12 +6,12 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "libvda_b200.so")
-STAMP = os.path.join(HERE, ".libvda_b200.stamp")
+LIB = os.path.join(HERE, os.environ.get("VDA_LIB_NAME", "libvda_b200.so"))  # VDA_LIB_NAME: A/B builds for tuning
+STAMP = LIB[:-3] + ".stamp" if os.environ.get("VDA_LIB_NAME") else os.path.join(HERE, ".libvda_b200.stamp")
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-shared",
-]
+] + os.environ.get("VDA_NVCC_EXTRA", "").split()
 
 
 def _sources():

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "../../include/vda_b200.h"
@@ -32,9 +33,17 @@ int check_cuda(cudaError_t e, const char* what) {
 }
 int num_sms() { return g_num_sms; }
 
+static int encode_map(CUtensorMap* tm, CUtensorMapDataType dt, CUtensorMapSwizzle sw, const void* base, int rank,
+                      const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box);
+
 // bf16 tensor map, 128B swizzle, inner box = 64 elements (128 B); rank 2..4.
 int encode_bf16_map(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                     const uint32_t* box) {
+  return encode_map(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, CU_TENSOR_MAP_SWIZZLE_128B, base, rank, dims, strides_bytes, box);
+}
+
+static int encode_map(CUtensorMap* tm, CUtensorMapDataType dt, CUtensorMapSwizzle sw, const void* base, int rank,
+                      const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box) {
   if (!g_encode) return set_error(-2, "vda_init() has not been called");
   cuuint64_t gdim[5], gstr[5];
   cuuint32_t bdim[5], estr[5];
@@ -48,9 +57,8 @@ int encode_bf16_map(CUtensorMap* tm, const void* base, int rank, const uint64_t*
     }
   }
   if (reinterpret_cast<uintptr_t>(base) % 16) return set_error(-3, "tensor map base not 16 B aligned");
-  CUresult r = g_encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), gdim, gstr, bdim, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = g_encode(tm, dt, rank, const_cast<void*>(base), gdim, gstr, bdim, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return set_error(-4, "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
   return 0;
 }
@@ -95,7 +103,37 @@ static void pick_tile(const vda_epilogue* e, int N, int m_tiles, int* bn_out, bo
   *bn_out = N >= 64 ? 64 : 32;
 }
 
+// Epilogue flavour (gemm_epilogue.cuh): 1 = in-place fp32 residual update as TMA reduce-add,
+// 2 = bf16 output through TMA box stores, 0 = generic element-wise path.
+static int pick_epi_tma(const vda_epilogue* e, bool conv) {
+  const char* ev = getenv("VDA_GEMM_NO_TMA_EPI");  // A/B knob: 1 disables all, 2 disables the bf16 store flavour
+  const int off_lvl = ev ? atoi(ev) : 0;
+  const bool off = off_lvl == 1;
+  if (off || e->act == ACT_GEGLU || e->out_relu || e->res1 || e->res2) return 0;
+  const auto aligned = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  if (!conv && e->store_mode == ST_PLAIN && e->res_f32 && e->out_f32 == e->res_f32 && !e->out && e->ldo % 4 == 0 &&
+      aligned(e->out_f32))
+    return 1;
+  if ((e->store_mode == ST_PLAIN || (!conv && e->store_mode == ST_QKV)) && e->out && !e->out_f32 && !e->res_f32 &&
+      e->ldo % 8 == 0 && aligned(e->out) && off_lvl != 2)
+    return 2;
+  return 0;
+}
+
+// smem ring depth of a launch: the compiled maximum of the kernel variant, minus the stages whose
+// shared memory the epilogue takes over (48 KB: TMA boxes or the fp32-residual staging ring).
+static int pick_stages(int bn, bool two, const vda_epilogue* e, int epi_tma) {
+  const int max_stages = two ? (bn >= 256 ? 6 : 8) : (bn >= 256 ? 4 : (bn >= 128 ? 6 : 8));
+  const bool staged = epi_tma || (e->res_f32 && e->store_mode == ST_PLAIN && e->act != ACT_GEGLU);
+  if (!staged) return max_stages;
+  const int stage_bytes = 128 * 64 * 2 + (two ? bn / 2 : bn) * 64 * 2;
+  const int freed = (48 * 1024 + stage_bytes - 1) / stage_bytes;
+  return max_stages - freed;
+}
+
 static int fill_epilogue(GemmParams& p, const vda_epilogue* e) {
+  const char* sv = getenv("VDA_GEMM_SCHED");  // tuning knob: 1 = round-robin tiles, 2 = contiguous runs
+  p.sched = sv ? atoi(sv) : 0;
   p.act = e->act;
   p.store_mode = e->store_mode;
   p.bias = e->bias;
@@ -177,6 +215,22 @@ int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, 
   bool two;
   pick_tile(epi, N, p.m_tiles, &bn, &two);
   p.n_tiles = (N + bn - 1) / bn;
+  p.epi_tma = pick_epi_tma(epi, false);
+  p.stages = pick_stages(bn, two, epi, p.epi_tma);
+  if (p.epi_tma == 1) {
+    const uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
+    const uint64_t str[1] = {(uint64_t)epi->ldo * 4};
+    const uint32_t box[2] = {16, 128};
+    if ((rc = encode_map(&p.tmD, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, CU_TENSOR_MAP_SWIZZLE_64B, epi->out_f32, 2, dims, str, box)))
+      return rc;
+  } else if (p.epi_tma == 2) {
+    // QKV: only the Q|K columns [0, 2D) are stored through the map
+    const uint64_t dims[2] = {(uint64_t)(epi->store_mode == ST_QKV ? 2 * epi->qkv_d : N), (uint64_t)M};
+    const uint64_t str[1] = {(uint64_t)epi->ldo * 2};
+    const uint32_t box[2] = {32, 128};
+    if ((rc = encode_map(&p.tmD, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, CU_TENSOR_MAP_SWIZZLE_64B, epi->out, 2, dims, str, box)))
+      return rc;
+  }
   {
     const uint64_t dims[2] = {(uint64_t)K, (uint64_t)M};
     const uint64_t str[1] = {(uint64_t)lda * 2};
@@ -219,6 +273,15 @@ int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W,
   bool two;
   pick_tile(epi, Cout, p.m_tiles, &bn, &two);
   p.n_tiles = (Cout + bn - 1) / bn;
+  p.epi_tma = pick_epi_tma(epi, true);
+  p.stages = pick_stages(bn, two, epi, p.epi_tma);
+  if (p.epi_tma == 2) {
+    const uint64_t dims[4] = {(uint64_t)Cout, (uint64_t)W, (uint64_t)H, (uint64_t)n};
+    const uint64_t str[3] = {(uint64_t)epi->ldo * 2, (uint64_t)W * epi->ldo * 2, (uint64_t)H * W * epi->ldo * 2};
+    const uint32_t box[4] = {32, 1u << p.tw_log2, 128u >> p.tw_log2, 1};
+    if ((rc = encode_map(&p.tmD, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, CU_TENSOR_MAP_SWIZZLE_64B, epi->out, 4, dims, str, box)))
+      return rc;
+  }
   {
     const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)n};
     const uint64_t str[3] = {(uint64_t)ldx * 2, (uint64_t)W * ldx * 2, (uint64_t)H * W * ldx * 2};

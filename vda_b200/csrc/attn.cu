@@ -29,6 +29,19 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
+// 2^x on the FMA pipe (Cody-Waite split + degree-3 polynomial, rel. error 1.1e-4, invisible after the
+// bf16 rounding of P): the MUFU unit does 16 ex2/clk/SM and bounds head_dim-64 attention, so a fixed
+// fraction of the exponentials is evaluated here instead to balance the XU and FMA pipes.
+__device__ __forceinline__ float poly_exp2(float x) {
+  x = fmaxf(x, -126.0f);
+  const float fl = x + 12582912.0f;           // 1.5 * 2^23: integer part lands in the low mantissa bits
+  const float f = x - (fl - 12582912.0f);     // f in [-0.5, 0.5]
+  float r = fmaf(0.05459282f, f, 0.24221784f);
+  r = fmaf(r, f, 0.6933686f);
+  r = fmaf(r, f, 1.0f);
+  return __int_as_float(__float_as_int(r) + (__float_as_int(fl) << 23));
+}
+
 constexpr int kAttThreads = 192;
 constexpr int kQBytes = 128 * 64 * 2;        // 16 KB
 constexpr int kKBytes = 128 * 64 * 2;        // 16 KB
@@ -254,6 +267,8 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_kernel(const __grid_c
 constexpr int kA2Smem = kQBytes + 2 * kKBytes + 2 * kVBytes + 256;
 constexpr float kRescaleThreshold = 8.0f;
 
+// POLY: one in POLY exponentials (0 = none, 2/4/8) is evaluated with poly_exp2 on the FMA pipe.
+template <int POLY>
 __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __grid_constant__ AttnParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
@@ -439,8 +454,10 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          const float p0 = fast_exp2(fmaf(__uint_as_float(s[c0 + i]), sc, neg_m));
-          const float p1 = fast_exp2(fmaf(__uint_as_float(s[c0 + i + 1]), sc, neg_m));
+          const float x0 = fmaf(__uint_as_float(s[c0 + i]), sc, neg_m);
+          const float x1 = fmaf(__uint_as_float(s[c0 + i + 1]), sc, neg_m);
+          const float p0 = fast_exp2(x0);
+          const float p1 = (POLY > 0 && ((i >> 1) % (POLY / 2 > 0 ? POLY / 2 : 1)) == 0) ? poly_exp2(x1) : fast_exp2(x1);
           l0 += p0;
           l1 += p1;
           __nv_bfloat162 h = __floats2bfloat162_rn(p0, p1);
@@ -519,22 +536,32 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
   p.kv_tiles = (S + 127) / 128;
   p.scale_log2 = 0.125f * 1.4426950408889634f;
   static bool configured = false;
-  static int variant = 2;
+  static int variant = 2, poly = 0;
   if (!configured) {
     const char* v = getenv("VDA_ATTN_VARIANT");  // 1 = first-generation kernel (P via smem), kept for A/B runs
     if (v && v[0] == '1') variant = 1;
+    const char* pe = getenv("VDA_ATTN_POLY");    // 0 / 2 / 4 / 8: share of exponentials on the FMA pipe (tuning)
+    if (pe) poly = atoi(pe);
     int rc = check_cuda(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmem),
                         "attn smem attribute");
     if (rc) return rc;
-    rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem),
-                    "attn v2 smem attribute");
+    rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
     if (rc) return rc;
     configured = true;
   }
   dim3 grid(p.q_tiles, heads, frames);
   if (variant == 1)
     attn_fwd_kernel<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(stream)>>>(p);
+  else if (poly == 0)
+    attn_fwd_v2_kernel<0><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+  else if (poly == 2)
+    attn_fwd_v2_kernel<2><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+  else if (poly == 8)
+    attn_fwd_v2_kernel<8><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
   else
-    attn_fwd_v2_kernel<<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+    attn_fwd_v2_kernel<4><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
   return check_cuda(cudaGetLastError(), "attn launch");
 }

@@ -10,7 +10,8 @@
 //   warp 0    TMA producer    (128B-swizzled K-major tiles, mbarrier ring)
 //   warp 1    MMA issuer      (one thread)
 //   warp 2    TMEM allocator  (2 accumulator stages of BN fp32 columns)
-//   warp 4-11 epilogue        (tcgen05.ld 32x32b -> registers -> fused epilogue -> global)
+//   warp 4+   epilogue        (16 warps: 4 lane quadrants x 4 column slices; tcgen05.ld 32x32b ->
+//                              registers -> fused epilogue -> global)
 //
 //   gemm_tc2_kernel<BN>  CTA pairs (cluster of 2, tcgen05.mma.cta_group::2, M=256 x N=BN per pair):
 //                        each CTA loads its 128 rows of A and HALF of the W tile, so the operand
@@ -22,7 +23,7 @@
 
 namespace vda {
 
-constexpr int kGemmThreads = 384;
+constexpr int kGemmThreads = 128 + kEpiThreads;  // 4 control warps + epilogue warps
 
 template <int BN>
 struct GemmCfg {
@@ -76,6 +77,16 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_tiles = p.m_tiles * p.n_tiles;
+  // Tile order (tile = m_tile * n_tiles + n_tile).  If the A row-blocks of all CTAs fit in L2 together
+  // (K <= ~1k), each CTA takes a CONTIGUOUS run of tiles: its A rows come from HBM once, every later
+  // n_tile hits L2, and the next row-block is prefetched into L2 a tile ahead, so first-touch HBM
+  // latency never reaches the smem ring.  Otherwise tiles are dealt round-robin: the tiles in flight
+  // then form a narrow band of the (m, n) grid (few A row-blocks x all W tiles) that stays L2-resident.
+  const bool chunked = p.sched == 2;  // measured: round-robin wins on every encoder shape, contiguous runs kept as a knob
+  const int chunk = (num_tiles + gridDim.x - 1) / gridDim.x;
+  const int tile_begin = chunked ? blockIdx.x * chunk : blockIdx.x;
+  const int tile_end = chunked ? min(num_tiles, tile_begin + chunk) : num_tiles;
+  const int tile_step = chunked ? 1 : gridDim.x;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmA);
@@ -109,10 +120,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     int stage = 0;
     uint32_t phase = 0;
     const int cblocks = (p.a_mode == A_CONV3X3) ? (p.C / kBlockK) : 1;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = tile_begin; tile < tile_end; tile += tile_step) {
       const int m_t = tile / p.n_tiles, n_t = tile - m_t * p.n_tiles;
       TileCoord tc = {0, 0, 0};
       if (p.a_mode == A_CONV3X3) tc = conv_tile_coord(p, m_t);
+      if (chunked && n_t == p.n_tiles - 1 && tile + 1 < tile_end && elect_one()) {
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) tma_prefetch_2d(&p.tmA, kb * kBlockK, (m_t + 1) * kBlockM);
+      }
+      __syncwarp();
       for (int kb = 0; kb < p.num_k_blocks; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* sa = smem + stage * Cfg::kStageBytes;
@@ -129,7 +144,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
           tma_load_2d(sb, &p.tmB, &full_bar[stage], kb * kBlockK, n_t * BN);
         }
         __syncwarp();
-        if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
+        if (++stage == p.stages) stage = 0, phase ^= 1;
       }
     }
   } else if (warp == 1) {
@@ -137,7 +152,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       mbar_wait(&tempty_bar[as], aphase ^ 1);
@@ -159,32 +174,48 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
           if (kb == p.num_k_blocks - 1) umma_commit(&tfull_bar[as]);
         }
         __syncwarp();
-        if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
+        if (++stage == p.stages) stage = 0, phase ^= 1;
       }
     }
   } else if (warp >= 4) {
     const int ew = warp - 4;
     const int quad = warp & 3;  // TMEM lane quadrant this warp may access
-    const int half = ew >> 2;
+    const int half = ew >> 2;  // column slice of this warp (0..kEpiParts-1)
     const int r = quad * 32 + lane;
     const int et = threadIdx.x - 128;
+    const TileSched ts = {tile_begin, tile_step, tile_end, 1, 0};
+    ResRing rr = make_res_ring<BN>(p, ts, smem + p.stages * Cfg::kStageBytes, (Cfg::kStages - p.stages) * Cfg::kStageBytes, et,
+                                   r, half);
+    // TMA reduce-add epilogue: 3 boxes per column slice in the freed stages; thread 0 of each slice issues
+    const uint32_t red_base = smem_u32(smem + p.stages * Cfg::kStageBytes) + static_cast<uint32_t>(half) * kRedBoxes * kRedBoxBytes;
+    const bool red_issuer = (et & 127) == 0;
+    int box_ctr = 0;
     int it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
       const int m_t = tile / p.n_tiles, n_t = tile - m_t * p.n_tiles;
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       float* s_bias = s_epi + as * 2 * BN;
       float* s_scale = s_bias + BN;
       stage_bias_scale<BN>(p, n_t, et, s_bias, s_scale);
-      epilogue_prefetch<BN>(p, m_t, n_t, r, half);
+      if (tile + tile_step < tile_end)  // residual rows of the NEXT tile into L2: a whole tile of lead time
+        epilogue_prefetch<BN>(p, (tile + tile_step) / p.n_tiles, (tile + tile_step) % p.n_tiles, r, half);
       mbar_wait(&tfull_bar[as], aphase);
       tc_fence_after();
       const uint32_t t_acc = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN;
-      epilogue_tile<BN>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale);
+      // QKV tiles that hold V columns keep the transposing element-wise store
+      const bool v_tile = p.store_mode == ST_QKV && (n_t + 1) * BN > 2 * p.qkv_d;
+      if (p.epi_tma == 1)
+        epilogue_tile_box<BN, 1>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer);
+      else if (p.epi_tma == 2 && !v_tile)
+        epilogue_tile_box<BN, 2>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer);
+      else
+        epilogue_tile<BN>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, ts, rr, it);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[as]);
     }
+    if (p.epi_tma && red_issuer) bulk_wait_all();
   }
 
   tc_fence_before();
@@ -222,6 +253,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
   const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
   const int m2_tiles = (p.m_tiles + 1) >> 1;
   const int num_tiles = m2_tiles * p.n_tiles;
+  // tile order: see gemm_tc_kernel
+  const bool chunked = p.sched == 2;  // measured: round-robin wins on every encoder shape, contiguous runs kept as a knob
+  const int chunk = (num_tiles + num_clusters - 1) / num_clusters;
+  const int tile_begin = chunked ? cluster_id * chunk : cluster_id;
+  const int tile_end = chunked ? min(num_tiles, tile_begin + chunk) : num_tiles;
+  const int tile_step = chunked ? 1 : num_clusters;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmA);
@@ -251,11 +288,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
     int stage = 0;
     uint32_t phase = 0;
     const int cblocks = (p.a_mode == A_CONV3X3) ? (p.C / kBlockK) : 1;
-    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+    for (int tile = tile_begin; tile < tile_end; tile += tile_step) {
       const int m2 = tile / p.n_tiles, n_t = tile - m2 * p.n_tiles;
       const int m_t = 2 * m2 + static_cast<int>(rank);
       TileCoord tc = {0, 0, 0};
       if (p.a_mode == A_CONV3X3) tc = conv_tile_coord(p, m_t);
+      if (chunked && n_t == p.n_tiles - 1 && tile + 1 < tile_end && elect_one()) {
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) tma_prefetch_2d(&p.tmA, kb * kBlockK, (m_t + 2) * kBlockM);
+      }
+      __syncwarp();
       for (int kb = 0; kb < p.num_k_blocks; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* sa = smem + stage * Cfg::kStageBytes;
@@ -272,7 +313,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
           tma_load_2d_2sm(sb, &p.tmB, &full_bar[stage], kb * kBlockK, n_t * BN + static_cast<int>(rank) * (BN / 2));
         }
         __syncwarp();
-        if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
+        if (++stage == p.stages) stage = 0, phase ^= 1;
       }
     }
   } else if (warp == 1) {
@@ -281,7 +322,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
+      for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
         mbar_wait(&tempty_bar[as], aphase ^ 1);
@@ -301,18 +342,25 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
             if (kb == p.num_k_blocks - 1) umma_commit_2cta(&tfull_bar[as]);
           }
           __syncwarp();
-          if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
+          if (++stage == p.stages) stage = 0, phase ^= 1;
         }
       }
     }
   } else if (warp >= 4) {
     const int ew = warp - 4;
     const int quad = warp & 3;
-    const int half = ew >> 2;
+    const int half = ew >> 2;  // column slice of this warp (0..kEpiParts-1)
     const int r = quad * 32 + lane;
     const int et = threadIdx.x - 128;
+    const TileSched ts = {tile_begin, tile_step, tile_end, 2, static_cast<int>(rank)};
+    ResRing rr = make_res_ring<BN>(p, ts, smem + p.stages * Cfg::kStageBytes, (Cfg::kStages - p.stages) * Cfg::kStageBytes, et,
+                                   r, half);
+    // TMA reduce-add epilogue: 3 boxes per column slice in the freed stages; thread 0 of each slice issues
+    const uint32_t red_base = smem_u32(smem + p.stages * Cfg::kStageBytes) + static_cast<uint32_t>(half) * kRedBoxes * kRedBoxBytes;
+    const bool red_issuer = (et & 127) == 0;
+    int box_ctr = 0;
     int it = 0;
-    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
+    for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
       const int m2 = tile / p.n_tiles, n_t = tile - m2 * p.n_tiles;
       const int m_t = 2 * m2 + static_cast<int>(rank);
       const int as = it & 1;
@@ -320,15 +368,25 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
       float* s_bias = s_epi + as * 2 * BN;
       float* s_scale = s_bias + BN;
       stage_bias_scale<BN>(p, n_t, et, s_bias, s_scale);
-      epilogue_prefetch<BN>(p, m_t, n_t, r, half);
+      if (tile + tile_step < tile_end)
+        epilogue_prefetch<BN>(p, 2 * ((tile + tile_step) / p.n_tiles) + static_cast<int>(rank),
+                              (tile + tile_step) % p.n_tiles, r, half);
       mbar_wait(&tfull_bar[as], aphase);
       tc_fence_after();
       const uint32_t t_acc = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + as * BN;
-      epilogue_tile<BN>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale);
+      // QKV tiles that hold V columns keep the transposing element-wise store
+      const bool v_tile = p.store_mode == ST_QKV && (n_t + 1) * BN > 2 * p.qkv_d;
+      if (p.epi_tma == 1)
+        epilogue_tile_box<BN, 1>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer);
+      else if (p.epi_tma == 2 && !v_tile)
+        epilogue_tile_box<BN, 2>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer);
+      else
+        epilogue_tile<BN>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, ts, rr, it);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(&tempty_bar[as], 0);
     }
+    if (p.epi_tma && red_issuer) bulk_wait_all();
   }
 
   // nobody may exit (or free TMEM) while the peer can still touch this CTA's smem, barriers or TMEM

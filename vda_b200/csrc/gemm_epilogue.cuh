@@ -16,7 +16,11 @@ namespace vda {
 
 constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;
-constexpr int kEpiWarps = 8;
+#ifndef VDA_EPI_WARPS
+#define VDA_EPI_WARPS 8  // measured: 16 warps (96 regs) is not faster than 8 (126 regs)
+#endif
+constexpr int kEpiWarps = VDA_EPI_WARPS;  // 4 TMEM lane quadrants x kEpiParts column slices
+constexpr int kEpiParts = kEpiWarps / 4;
 constexpr int kEpiThreads = kEpiWarps * 32;
 
 struct RowMap {
@@ -174,11 +178,17 @@ __device__ __forceinline__ void finish_group16(const GemmParams& p, const RowMap
   }
 }
 
+// Columns [cbeg, cbeg + kPer) of the tile belong to column slice `part` (0..kEpiParts-1).
+template <int BN>
+struct EpiSlice {
+  static constexpr int kPer = (BN / kEpiParts >= 32) ? BN / kEpiParts : 32;
+};
+
 // Requests the fp32 residual lines this thread will read for the tile into L2 (no registers held).
 template <int BN>
 __device__ __forceinline__ void epilogue_prefetch(const GemmParams& p, int m_tile, int n_t, int r, int half) {
   if (p.res_f32 == nullptr || p.store_mode != ST_PLAIN) return;
-  constexpr int kPer = (BN / 2 >= 32) ? BN / 2 : 32;
+  constexpr int kPer = EpiSlice<BN>::kPer;
   const int cbeg = half * kPer;
   if (cbeg >= BN) return;
   const RowMap rm = map_row(p, m_tile, r);
@@ -190,14 +200,193 @@ __device__ __forceinline__ void epilogue_prefetch(const GemmParams& p, int m_til
     if (col + i < p.N) prefetch_l2(src + i);
 }
 
+// ---------------------------------------------------------------------------------------------
+// fp32 residual staging (proj / fc2 / motion-module epilogues: x += gamma * (acc + b), in place).
+// Reading the residual with plain loads put a full L2/HBM round trip on every 16-column group of
+// every thread (proj: 184 us against 82 us without the read).  Instead each epilogue thread streams
+// its residual segments through a private ring of shared-memory slots with cp.async, kRing-1 groups
+// (and across tile boundaries) ahead of their use; slots are thread-private, so no barrier is needed.
+// The ring lives in the smem of GEMM stages that this launch leaves unused (GemmParams::stages).
+struct TileSched {
+  int begin, step, end;  // this CTA's tile sequence
+  int m_mul, m_add;      // m_tile = m_mul * (tile / n_tiles) + m_add  (2, rank for CTA pairs)
+};
+
+struct ResRing {
+  uint32_t base;  // shared-space address of slot 0 of this thread (slot pitch = kEpiThreads * 64 B)
+  int nbuf;       // slots in the ring; 0 = staging off
+  int issued;     // groups issued so far (global group counter of this thread)
+};
+constexpr uint32_t kResSlotPitch = kEpiThreads * 64;
+
+template <int BN>
+__device__ __forceinline__ void res_ring_issue(const GemmParams& p, const TileSched& ts, ResRing& rr, int r, int half) {
+  constexpr int kPer = EpiSlice<BN>::kPer;
+  constexpr int kGroups = kPer / 16;
+  const int k = rr.issued++;
+  const int ti = k / kGroups, g = k - ti * kGroups;
+  const int tile = ts.begin + ti * ts.step;
+  if (tile < ts.end) {
+    const int mq = tile / p.n_tiles, n_t = tile - mq * p.n_tiles;
+    const RowMap rm = map_row(p, ts.m_mul * mq + ts.m_add, r);
+    const int col = n_t * BN + half * kPer + 16 * g;
+    if (rm.valid && col < p.N) {
+      const float* src = p.res_f32 + rm.row * p.ldo + col;
+      const uint32_t dst = rr.base + static_cast<uint32_t>(k % rr.nbuf) * kResSlotPitch;
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16 * i), "l"(src + 4 * i) : "memory");
+    }
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+// Builds the ring in `bytes` of free smem at `area` and issues the first nbuf-1 groups.
+template <int BN>
+__device__ __forceinline__ ResRing make_res_ring(const GemmParams& p, const TileSched& ts, uint8_t* area, int bytes, int et,
+                                                 int r, int half) {
+  ResRing rr;
+  rr.base = smem_u32(area) + static_cast<uint32_t>(et) * 64;
+  rr.nbuf = 0;
+  rr.issued = 0;
+  constexpr int kPer = EpiSlice<BN>::kPer;
+  if (!p.epi_tma && p.res_f32 != nullptr && p.store_mode == ST_PLAIN && p.act != ACT_GEGLU && half * kPer < BN) {
+    const int n = bytes / static_cast<int>(kResSlotPitch);
+    rr.nbuf = n >= 4 ? 4 : (n >= 3 ? 3 : (n >= 2 ? 2 : 0));
+    for (int i = 0; i + 1 < rr.nbuf; ++i) res_ring_issue<BN>(p, ts, rr, r, half);
+  }
+  return rr;
+}
+
+// ---------------------------------------------------------------------------------------------
+// In-place fp32 residual update  x += scale * act(acc + bias)  as a TMA reduce-add.
+// With one thread per accumulator row, every warp-level global access of the epilogue touches 32
+// different 128-byte lines, and L1TEX serialises those (about 16 B/clk/SM): reading and writing the
+// fp32 residual cost more than the MMAs (ncu / A-B runs: proj 184 us vs 82 us without them).  Here
+// the threads only write their delta rows into a swizzled shared-memory box (16 fp32 columns x 128
+// rows); one elected thread per column slice hands the box to the TMA unit, which adds it onto the
+// residual in L2 (cp.reduce.async.bulk.tensor .add).  The SM never reads the residual at all.
+// Three boxes per column slice rotate; one named barrier per box (see the ordering argument inline).
+constexpr int kRedBoxBytes = 16 * 4 * kBlockM;  // 8 KB
+constexpr int kRedBoxes = 3;
+
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, uint32_t src_smem, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(src_smem), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read_1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, uint32_t src_smem, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(src_smem), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, uint32_t src_smem, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(src_smem), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+
+// Box epilogues.  MODE 1: fp32 reduce-add, 16 columns per box.  MODE 2: bf16 store, 32 columns per
+// box (same 64-byte rows, SWIZZLE_64B; conv tiles use a 4-D map whose box is the tile's pixel patch).
+// `box_base`: shared address of this column slice's 3 boxes; `box_ctr`: running box counter of the slice.
+template <int BN, int MODE>
+__device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_tile, int n_t, uint32_t t_acc, int r, int half,
+                                                  const float* s_bias, const float* s_scale, uint32_t box_base, int& box_ctr,
+                                                  bool issuer) {
+  constexpr int kPer = EpiSlice<BN>::kPer;
+  constexpr int kCols = MODE == 1 ? 16 : 32;
+  const int cbeg = half * kPer;
+  if (cbeg >= BN) return;
+#pragma unroll 1
+  for (int c0 = cbeg; c0 < cbeg + kPer; c0 += kCols) {
+    const int col = n_t * BN + c0;
+    uint32_t raw[kCols];
+    __syncwarp();
+    if constexpr (MODE == 1) {
+      tmem_ld16(t_acc + c0, raw);
+    } else {
+      tmem_ld32(t_acc + c0, raw);
+    }
+    tmem_ld_wait();
+    uint32_t pk[16];  // 64 bytes of this row: 16 fp32 or 32 bf16
+#pragma unroll
+    for (int g = 0; g < kCols / 16; ++g) {
+      float b[16], v[16];
+      lds_f32x16(s_bias + c0 + 16 * g, b);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(raw[16 * g + i]) + b[i];
+      if (p.act == ACT_GELU) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = gelu_fast(v[i]);
+      } else if (p.act == ACT_RELU) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);
+      }
+      if (p.scale) {
+        float sc[16];
+        lds_f32x16(s_scale + c0 + 16 * g, sc);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] *= sc[i];
+      }
+      if constexpr (MODE == 1) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) pk[i] = __float_as_uint(v[i]);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          __nv_bfloat162 h2 = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+          pk[8 * g + i] = *reinterpret_cast<uint32_t*>(&h2);
+        }
+      }
+    }
+    // box (box_ctr % 3) is free: its previous store (3 boxes ago) was confirmed read by the issuer
+    // before the issuer joined the barrier of the previous box, which every thread has passed.
+    const uint32_t box = box_base + static_cast<uint32_t>(box_ctr % kRedBoxes) * kRedBoxBytes;
+    const uint32_t rowaddr = box + static_cast<uint32_t>(r) * 64;
+    const uint32_t sw = (static_cast<uint32_t>(r) >> 1) & 3;
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + ((static_cast<uint32_t>(c) ^ sw) << 4)),
+                   "r"(pk[4 * c]), "r"(pk[4 * c + 1]), "r"(pk[4 * c + 2]), "r"(pk[4 * c + 3])
+                   : "memory");
+    fence_proxy_async_smem();
+    named_bar_sync(2 + half, 128);
+    if (issuer) {
+      if (col < p.N) {  // rows >= M / cols >= N / pixels outside the map are clipped by TMA
+        if constexpr (MODE == 1) {
+          tma_reduce_add_2d(&p.tmD, box, col, m_tile * kBlockM);
+        } else if (p.a_mode == A_CONV3X3) {
+          const int tpi = p.tiles_w * p.tiles_h;
+          const int img = m_tile / tpi;
+          const int t = m_tile - img * tpi;
+          const int ty = t / p.tiles_w, tx = t - ty * p.tiles_w;
+          tma_store_4d(&p.tmD, box, col, tx << p.tw_log2, ty * (kBlockM >> p.tw_log2), img);
+        } else {
+          tma_store_2d(&p.tmD, box, col, m_tile * kBlockM);
+        }
+      }
+      bulk_commit();
+      bulk_wait_read_1();  // the previous box of this slice has been read out of shared memory
+    }
+    ++box_ctr;
+  }
+}
+
 // t_acc: TMEM address (lane quadrant of this warp, accumulator stage, column 0 of the tile).
 // s_bias / s_scale: staged bias / scale of the tile's BN columns (see stage_bias_scale).
 template <int BN>
 __device__ __forceinline__ void epilogue_tile(const GemmParams& p, int m_tile, int n_t, uint32_t t_acc, int r, int half,
-                                              const float* s_bias, const float* s_scale) {
+                                              const float* s_bias, const float* s_scale, const TileSched& ts, ResRing& rr,
+                                              int tile_iter) {
   const RowMap rm = map_row(p, m_tile, r);
-  constexpr int kPer = (BN / 2 >= 32) ? BN / 2 : 32;
-  constexpr int kChunks = kPer / 32;
+  constexpr int kPer = EpiSlice<BN>::kPer;
   const int cbeg = half * kPer;
   if (cbeg >= BN) return;
 
@@ -223,8 +412,10 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, int m_tile, i
   // One 16-column group per iteration, deliberately NOT unrolled: the generic epilogue body is a
   // few hundred instructions and an unrolled tile loop overflowed the instruction cache (ncu:
   // "no_instruction" stalls, 134 KB of SASS), which made the epilogue, not the MMA, set the pace.
-  const bool pre = p.res_f32 != nullptr && p.store_mode == ST_PLAIN && rm.valid;
+  const bool staged = rr.nbuf > 0;
+  const bool pre = staged && rm.valid;
   constexpr int kStep = 16;
+  constexpr int kGroups = kPer / 16;
   const int step = (p.act == ACT_GEGLU) ? 32 : kStep;
 #pragma unroll 1
   for (int c0 = cbeg; c0 < cbeg + kPer && c0 < BN; c0 += step) {
@@ -234,10 +425,22 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, int m_tile, i
     tmem_ld16(t_acc + c0, raw);
     if (p.act == ACT_GEGLU) tmem_ld16(t_acc + c0 + 16, gate);
     float4 rpre[4];
-    if (pre && col < p.N) {
-      const float4* src = reinterpret_cast<const float4*>(p.res_f32 + rm.row * p.ldo + col);
+    if (staged) {
+      // request group k + nbuf - 1 (possibly of the next tile), then wait until group k has landed
+      res_ring_issue<BN>(p, ts, rr, r, half);
+      if (rr.nbuf == 4)
+        asm volatile("cp.async.wait_group 3;" ::: "memory");
+      else if (rr.nbuf == 3)
+        asm volatile("cp.async.wait_group 2;" ::: "memory");
+      else
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+      const int k = tile_iter * kGroups + ((c0 - cbeg) >> 4);
+      const uint32_t slot = rr.base + static_cast<uint32_t>(k % rr.nbuf) * kResSlotPitch;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) rpre[i] = __ldcs(src + i);
+      for (int i = 0; i < 4; ++i)
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(rpre[i].x), "=f"(rpre[i].y), "=f"(rpre[i].z), "=f"(rpre[i].w)
+                     : "r"(slot + 16 * i));
     }
     tmem_ld_wait();
     if (!rm.valid || col >= p.N) continue;
@@ -255,7 +458,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, int m_tile, i
     }
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(raw[i]) + b[i];
-    finish_group16(p, rm, col, v, s_scale + c0, pre ? rpre : nullptr);
+    finish_group16(p, rm, col, v, s_scale + c0, pre ? rpre : nullptr);  // unstaged residuals are loaded inside
   }
 }
 

@@ -20,10 +20,14 @@ enum : int { ACT_NONE = 0, ACT_GELU = 1, ACT_RELU = 2, ACT_GEGLU = 3 };
 struct alignas(64) GemmParams {
   CUtensorMap tmA;  // 2D [M,K] or 4D [N,H,W,C] bf16, box 64 x 128 rows, SWIZZLE_128B
   CUtensorMap tmB;  // 2D [N,K] bf16, box 64 x BLOCK_N
+  CUtensorMap tmD;  // epi_tma: 2D [N,M] f32 view of out_f32, box 16 x 128 rows, SWIZZLE_64B
+  int epi_tma;      // 1 = in-place fp32 residual update done as TMA reduce-add (gemm_epilogue.cuh)
   int M, N, K;      // GEMM extents (conv: M = images*H*W, K = 9*C)
   int num_k_blocks;
   int m_tiles, n_tiles;
   int a_mode;
+  int stages;  // smem ring depth used by this launch (<= compiled maximum); freed stages hold the residual ring
+  int sched;  // tile order: 0 = auto, 1 = round-robin, 2 = contiguous run per CTA (see gemm.cu)
   // conv geometry (a_mode == A_CONV3X3): stride 1, pad 1, output map = input map
   int H, W, C;
   int tw_log2;           // spatial tile is TH x TW pixels with TW = 1<<tw_log2, TH = 128/TW
