@@ -32,7 +32,23 @@ cw = r(256, 9 * 256).to(torch.bfloat16)
 cb = r(256)
 cy = torch.empty(T, 148, 148, 256, device=dev, dtype=torch.bfloat16)
 
+# motion-module temporal attention (mm0: 37x37 tokens, C=1024; mm3: 74x74, C=256) and head upsamples
+tq0 = r(T * 1369, 3 * 1024).to(torch.bfloat16)
+to0 = torch.empty(T * 1369, 1024, device=dev, dtype=torch.bfloat16)
+tq3 = r(T * 5476, 3 * 256).to(torch.bfloat16)
+to3 = torch.empty(T * 5476, 256, device=dev, dtype=torch.bfloat16)
+up_in = r(T, 148, 148, 256).to(torch.bfloat16)
+up_out = torch.empty(T, 296, 296, 256, device=dev, dtype=torch.bfloat16)
+up2_in = r(T, 296, 296, 128).to(torch.bfloat16)
+up2_out = torch.empty(T, 518, 518, 128, device=dev, dtype=torch.bfloat16)
+
 ops = {
+    "tattn0": (lambda: L.temporal_attn(tq0, 3072, tq0[:, 1024:], 3072, tq0[:, 2048:], 3072, to0, 1024, 1369, 8, 128, 32, 32),
+               4 * 1369 * 8 * 32 * 32 * 128),
+    "tattn3": (lambda: L.temporal_attn(tq3, 768, tq3[:, 256:], 768, tq3[:, 512:], 768, to3, 256, 5476, 8, 32, 32, 32),
+               4 * 5476 * 8 * 32 * 32 * 32),
+    "up296": (lambda: L.bilinear_nhwc(up_in, up_out, T, 148, 148, 296, 296, 256), 0),
+    "up518": (lambda: L.bilinear_nhwc(up2_in, up2_out, T, 296, 296, 518, 518, 128), 0),
     "conv148": (lambda: L.conv3x3(cx, cw, L.make_epilogue(bias=cb, out=cy, ldo=256, act=L.ACT_RELU), T, 148, 148, 256, 256),
                 2 * T * 148 * 148 * 256 * 9 * 256),
     "ln": (lambda: L.layernorm(tok, lnw, lnb, xn, 1e-6), 0),

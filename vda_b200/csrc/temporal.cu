@@ -7,6 +7,7 @@
 // One warp per (token, head): K and V rows staged in shared memory (broadcast reads), lane t owns
 // query frame t, the 32 scores and the softmax live in that lane's registers (no shuffles), the
 // output row is staged back through shared memory for coalesced 16-byte stores.
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -122,6 +123,201 @@ __global__ void __launch_bounds__(kTWarps * 32) temporal_attn_kernel(const Tempo
     const long long row = static_cast<long long>(tt) * p.hw + d;
     *reinterpret_cast<uint4*>(p.out + row * p.ldo + head * hd + c * 8) = make_uint4(src[0], src[1], src[2], src[3]);
   }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Warp-MMA version of the same op (the default).  The SIMT kernel above spends ~12k FMA/convert
+// instructions per (token, head) and stages K/V/Q through registers one 16-byte load at a time
+// (0.75 ms for the 1369x8x(32x128) module of vitl against ~60 us of HBM time).  Here each warp
+//   1. copies its Q, K, V slices (32 rows x head_dim) global -> shared with cp.async, all requests in
+//      flight at once, rows padded by 16 bytes so ldmatrix is bank-conflict free,
+//   2. S = Q K^T with mma.sync.m16n8k16 (bf16 in, fp32 accumulate): 2 m-tiles x 4 n-tiles,
+//   3. softmax over the 32 keys in the accumulator registers (quad shuffles),
+//   4. O = P V with P re-used from the accumulators as A fragments and V read with ldmatrix.trans,
+//   5. O staged through the (dead) Q rows for 16-byte coalesced stores.
+// The temporal axis is only 32 long, so these are warp-level tensor-core tiles, not tcgen05 ones:
+// the op is HBM-bound (4 x rows x C x 2 bytes) and the MMA work is negligible.
+__device__ __forceinline__ void cp_async16_zfill(uint32_t dst, const void* src, int bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+template <int HDP>  // head_dim rounded up to a multiple of 16
+__global__ void __launch_bounds__(kTWarps * 32) temporal_attn_mma_kernel(const TemporalParams p) {
+  constexpr int kStride = HDP * 2 + 16;  // bytes per staged row
+  constexpr int kMat = 32 * kStride;
+  constexpr int kChunks = HDP / 8;       // 16-byte chunks per staged row
+  constexpr int kNC = HDP % 32 == 0 ? 32 : 16;  // output columns per PV pass (divides HDP)
+  extern __shared__ __align__(16) uint8_t tsm[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int unit = blockIdx.x * kTWarps + warp;
+  if (unit >= p.hw * p.heads) return;
+  const int d = unit / p.heads, head = unit - d * p.heads;
+  const uint32_t sQ = smem_u32(tsm) + warp * 3 * kMat, sK = sQ + kMat, sV = sK + kMat;
+
+#pragma unroll
+  for (int i = 0; i < kChunks; ++i) {
+    const int idx = i * 32 + lane;
+    const int t = idx / kChunks, c = idx % kChunks;
+    const bool col_ok = c * 8 < p.hd;
+    const long long row = static_cast<long long>(t) * p.hw + d;
+    const uint32_t off = t * kStride + c * 16;
+    const bool qok = col_ok && t < p.Tq, kok = col_ok && t < p.Tk;
+    cp_async16_zfill(sQ + off, qok ? p.q + row * p.ldq + head * p.hd + c * 8 : p.q, qok ? 16 : 0);
+    cp_async16_zfill(sK + off, kok ? p.k + row * p.ldk + head * p.hd + c * 8 : p.k, kok ? 16 : 0);
+    cp_async16_zfill(sV + off, kok ? p.v + row * p.ldv + head * p.hd + c * 8 : p.v, kok ? 16 : 0);
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncwarp();
+
+  // ---- S = Q K^T
+  float s[2][4][4];
+#pragma unroll
+  for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) s[mt][nt][i] = 0.f;
+#pragma unroll
+  for (int ks = 0; ks < HDP / 16; ++ks) {
+    uint32_t a[2][4], b[2][4];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+      ldsm_x4(sQ + (mt * 16 + (lane & 15)) * kStride + (ks * 2 + (lane >> 4)) * 16, a[mt]);
+#pragma unroll
+    for (int np = 0; np < 2; ++np)  // keys np*16 .. +16: {n-tile 2np: k lo, k hi; n-tile 2np+1: k lo, k hi}
+      ldsm_x4(sK + (np * 16 + (lane & 7) + ((lane >> 4) << 3)) * kStride + (ks * 2 + ((lane >> 3) & 1)) * 16, b[np]);
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) mma_bf16_16816(s[mt][nt], a[mt], b[nt >> 1][(nt & 1) * 2], b[nt >> 1][(nt & 1) * 2 + 1]);
+  }
+  __syncwarp();  // Q rows are dead from here on: they receive the output
+
+  // ---- softmax over keys; this lane holds, per m-tile, rows g = lane/4 (i = 0,1) and g+8 (i = 2,3),
+  // key columns nt*8 + (lane%4)*2 + (i&1)
+  const float sl2 = p.scale * 1.4426950408889634f;
+  uint32_t pa[2][2][4];  // P as A fragments: [m-tile][k-step of 16 keys]
+  float inv[2][2];
+#pragma unroll
+  for (int mt = 0; mt < 2; ++mt) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      float m = -INFINITY;
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int col = nt * 8 + (lane & 3) * 2 + i;
+          if (col >= p.Tk) s[mt][nt][2 * h + i] = -INFINITY;
+          m = fmaxf(m, s[mt][nt][2 * h + i]);
+        }
+      m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+      m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+      float l = 0.f;
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const float e = exp2f((s[mt][nt][2 * h + i] - m) * sl2);
+          s[mt][nt][2 * h + i] = e;
+          l += e;
+        }
+      l += __shfl_xor_sync(0xffffffffu, l, 1);
+      l += __shfl_xor_sync(0xffffffffu, l, 2);
+      inv[mt][h] = 1.f / l;
+    }
+#pragma unroll
+    for (int kk = 0; kk < 2; ++kk) {
+      pa[mt][kk][0] = pack_bf16(s[mt][2 * kk][0], s[mt][2 * kk][1]);
+      pa[mt][kk][1] = pack_bf16(s[mt][2 * kk][2], s[mt][2 * kk][3]);
+      pa[mt][kk][2] = pack_bf16(s[mt][2 * kk + 1][0], s[mt][2 * kk + 1][1]);
+      pa[mt][kk][3] = pack_bf16(s[mt][2 * kk + 1][2], s[mt][2 * kk + 1][3]);
+    }
+  }
+
+  // ---- O = P V, kNC output columns per pass
+#pragma unroll 1
+  for (int n0 = 0; n0 < HDP; n0 += kNC) {
+    float o[2][kNC / 8][4];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < kNC / 8; ++nt)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) o[mt][nt][i] = 0.f;
+#pragma unroll
+    for (int kk = 0; kk < 2; ++kk) {
+#pragma unroll
+      for (int np = 0; np < kNC / 16; ++np) {
+        // matrices: (t lo, n-tile 2np), (t hi, n-tile 2np), (t lo, n-tile 2np+1), (t hi, n-tile 2np+1)
+        uint32_t b[4];
+        const int mi = lane >> 3;
+        ldsm_x4_t(sV + (kk * 16 + (mi & 1) * 8 + (lane & 7)) * kStride + (n0 + np * 16 + (mi >> 1) * 8) * 2, b);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+          mma_bf16_16816(o[mt][2 * np], pa[mt][kk], b[0], b[1]);
+          mma_bf16_16816(o[mt][2 * np + 1], pa[mt][kk], b[2], b[3]);
+        }
+      }
+    }
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < kNC / 8; ++nt)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int row = mt * 16 + (lane >> 2) + 8 * h;
+          const uint32_t w = pack_bf16(o[mt][nt][2 * h] * inv[mt][h], o[mt][nt][2 * h + 1] * inv[mt][h]);
+          asm volatile("st.shared.b32 [%0], %1;" ::"r"(sQ + row * kStride + (n0 + nt * 8 + (lane & 3) * 2) * 2), "r"(w) : "memory");
+        }
+  }
+  __syncwarp();
+#pragma unroll
+  for (int i = 0; i < kChunks; ++i) {
+    const int idx = i * 32 + lane;
+    const int t = idx / kChunks, c = idx % kChunks;
+    if (t < p.Tq && c * 8 < p.hd) {
+      uint4 w;
+      asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w.x), "=r"(w.y), "=r"(w.z), "=r"(w.w) : "r"(sQ + t * kStride + c * 16));
+      const long long row = static_cast<long long>(t) * p.hw + d;
+      *reinterpret_cast<uint4*>(p.out + row * p.ldo + head * p.hd + c * 8) = w;
+    }
+  }
+}
+
+template <int HDP>
+static int launch_temporal_mma(const TemporalParams& p, cudaStream_t stream) {
+  constexpr int smem = kTWarps * 3 * 32 * (HDP * 2 + 16);
+  static bool configured = false;
+  if (!configured) {
+    int rc = check_cuda(cudaFuncSetAttribute(temporal_attn_mma_kernel<HDP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
+                        "temporal mma smem attribute");
+    if (rc) return rc;
+    configured = true;
+  }
+  const int units = p.hw * p.heads;
+  temporal_attn_mma_kernel<HDP><<<(units + kTWarps - 1) / kTWarps, kTWarps * 32, smem, stream>>>(p);
+  return check_cuda(cudaGetLastError(), "temporal_attn launch");
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -261,6 +457,19 @@ extern "C" int vda_temporal_attn(const void* q, int ldq, const void* k, int ldk,
   p.ldq = ldq, p.ldk = ldk, p.ldv = ldv, p.ldo = ldo;
   p.hw = hw, p.heads = heads, p.hd = head_dim, p.Tq = Tq, p.Tk = Tk;
   p.scale = 1.0f / sqrtf(static_cast<float>(head_dim));
+  const char* ev = getenv("VDA_TEMPORAL_SIMT");  // A/B knob: the SIMT kernel
+  if (!(ev && atoi(ev))) {
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    switch ((head_dim + 15) / 16) {
+      case 1: return launch_temporal_mma<16>(p, st);
+      case 2: return launch_temporal_mma<32>(p, st);
+      case 3: return launch_temporal_mma<48>(p, st);
+      case 4: return launch_temporal_mma<64>(p, st);
+      case 6: return launch_temporal_mma<96>(p, st);
+      case 8: return launch_temporal_mma<128>(p, st);
+      default: break;  // other head sizes: SIMT kernel below
+    }
+  }
   const int per_warp = 32 * (head_dim + 2) * 2 + 2 * 32 * head_dim * 2;
   const int smem = per_warp * kTWarps;
   static int configured = 0;
