@@ -49,6 +49,12 @@ typedef struct vda_epilogue {
   const float* w2;
   float b2;
   int cta_pair;         /* 0 = auto, 1 = force the single-CTA kernel, 2 = force the CTA-pair (cta_group::2) kernel */
+  /* FP32-accuracy mode (infer_video_depth(..., fp32=True), video_depth.py:108): if > 0, out / out_relu /
+   * res1 / res2 are "split" tensors: value x is stored as bf16 hi at [col], bf16(x - hi) at [col + split]
+   * and hi again at [col + 2*split], i.e. ready to be the A operand of the next GEMM whose weights are
+   * packed [Wh | Wh | Wl] along K.  `split` is the distance between the parts in elements. */
+  int split;
+  int ld32;             /* row pitch of out_f32 / res_f32 if different from ldo (0 = ldo); plain stores only */
 } vda_epilogue;
 
 /* C[M,N] = epi(A[M,K] * W[N,K]^T).  A bf16 with row pitch lda (elements, multiple of 8), W bf16
@@ -78,16 +84,19 @@ int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int frames, in
  * out_nope (optional) receives the value before the add (the streaming cache, motion_module.py:251). */
 int vda_layernorm(const void* x, int x_is_f32, const float* gamma, const float* beta, void* out, void* out_nope,
                   const float* pe, int rows, int C, float eps, int tokens_per_frame, int skip, int pe_rows_per_t,
-                  int pe_T, void* stream);
+                  int pe_T, int split, void* stream);
+/* split != 0 (FP32-accuracy mode): out / out_nope rows are 3*C wide, [hi | lo | hi] (see vda_epilogue::split). */
 
 /* GroupNorm(32 groups) on an NHWC bf16 map [n, hw, ldx>=C] -> [n, hw, C] bf16 (motion_module.py:112).
  * stats_ws: 64*n doubles of scratch. */
 int vda_groupnorm_nhwc(const void* x, int ldx, const float* gamma, const float* beta, void* out, double* stats_ws,
-                       int n, int hw, int C, float eps, void* stream);
+                       int n, int hw, int C, float eps, int split, void* stream);
+/* split > 0: x is a split tensor whose parts are `split` elements apart; out is [n, hw, 3*C] split, parts C apart. */
 
 /* 14x14/stride-14 patch gather: x f32 NCHW [frames,3,H,W] -> A bf16 [frames*(H/14)*(W/14), ldk],
  * k = (c,kh,kw), zero padded to ldk (dinov2_layers/patch_embed.py:66,76-78). */
-int vda_patch_im2col(const float* x, void* a, int frames, int H, int W, int ldk, void* stream);
+int vda_patch_im2col(const float* x, void* a, int frames, int H, int W, int ldk, int split, void* stream);
+/* split != 0: A rows are 3*ldk wide, [hi | lo | hi] of the fp32 pixels. */
 
 /* tokens[f,0]=cls+pos[0]; tokens[f,1+i]=patch[f*hw+i]+pos[1+i], all f32 (dinov2.py:218-219). */
 int vda_add_cls_pos(const float* patch, const float* cls, const float* pos, float* tokens, int frames, int hw, int D,
@@ -96,7 +105,8 @@ int vda_add_cls_pos(const float* patch, const float* cls, const float* pos, floa
 /* Bilinear resampling with align_corners=True: NHWC bf16 (util/blocks.py:156-158,
  * dpt_temporal.py:116-118) and single-channel f32 with optional ReLU (video_depth.py:66-67,111-112). */
 int vda_bilinear_nhwc(const void* x, int ldx, void* out, int ldo, int n, int h, int w, int H, int W, int C,
-                      void* stream);
+                      int split_in, int split_out, void* stream);
+/* split_in / split_out > 0: split tensors (parts that many elements apart), interpolated in fp32. */
 int vda_bilinear_f32(const float* x, float* out, int n, int h, int w, int H, int W, int relu, void* stream);
 
 /* 3x3 stride-2 pad-1 patch gather for dpt.py:85-90: x NHWC bf16 [n,h,w,C] -> [n*ho*wo, 9*C]. */
@@ -115,6 +125,14 @@ int vda_temporal_attn(const void* q, int ldq, const void* k, int ldk, const void
 int vda_temporal_attn_stream(const void* q, const void* knew, const void* vnew, int ldn, void* kcache, void* vcache,
                              const int* slots, const float* pe_q, const float* pe_k, const float* pe_v, void* out,
                              int ldo, int hw, int heads, int head_dim, int Tk, void* stream);
+
+/* FP32-accuracy mode attention (fp32=True of infer_video_depth, video_depth.py:108).  Inputs are the
+ * fp32 q/k/v written by the projection GEMM, outputs are split tensors (vda_epilogue::split).
+ * vda_attn_f32: qkv f32 [frames*S, ld >= 3*heads*64] laid out q | k | v (dinov2_layers/attention.py:51-59);
+ * out [frames*S, ldo] with parts `split` apart.  vda_temporal_attn_f32: as vda_temporal_attn. */
+int vda_attn_f32(const float* qkv, int ld, void* out, int ldo, int split, int frames, int S, int heads, void* stream);
+int vda_temporal_attn_f32(const float* q, const float* k, const float* v, int ld, void* out, int ldo, int split, int hw,
+                          int heads, int head_dim, int Tq, int Tk, void* stream);
 
 /* Alignment (utils/util.py:40-74, video_depth.py:120-160).  sums5 = {sum p*p, sum p, n, sum p*t,
  * sum t} accumulated in FP64 (caller zeroes it); solve writes {scale, shift} (metric: {1,0}). */

@@ -18,6 +18,7 @@ for s in $STAGES; do
   case $s in
     gemm)    run gemm 420 python -m pytest tests/test_gemm_gpu.py -q -m gpu -x -s ;;
     kernels) run kernels 420 python -m pytest tests/test_kernels_gpu.py -q -m gpu -x -s ;;
+    fp32)    run fp32 900 python -m pytest tests/test_fp32_gpu.py -q -m gpu -x -s ;;
     model)   run model 900 python -m pytest tests/test_model_gpu.py -q -m gpu -s ;;
     all)     run all 1500 python -m pytest tests -q -m gpu -s ;;
     smoke)   run smoke 300 python __graft_entry__.py --smoke ;;

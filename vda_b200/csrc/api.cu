@@ -109,7 +109,7 @@ static int pick_epi_tma(const vda_epilogue* e, bool conv) {
   const char* ev = getenv("VDA_GEMM_NO_TMA_EPI");  // A/B knob: 1 disables all, 2 disables the bf16 store flavour
   const int off_lvl = ev ? atoi(ev) : 0;
   const bool off = off_lvl == 1;
-  if (off || e->act == ACT_GEGLU || e->out_relu || e->res1 || e->res2) return 0;
+  if (off || e->act == ACT_GEGLU || e->out_relu || e->res1 || e->res2 || e->split) return 0;
   const auto aligned = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
   if (!conv && e->store_mode == ST_PLAIN && e->res_f32 && e->out_f32 == e->res_f32 && !e->out && e->ldo % 4 == 0 &&
       aligned(e->out_f32))
@@ -151,6 +151,10 @@ static int fill_epilogue(GemmParams& p, const vda_epilogue* e) {
   p.qkv_d = e->qkv_d, p.qkv_heads = e->qkv_heads, p.qkv_s = e->qkv_s, p.qkv_spad = e->qkv_spad;
   p.w2 = e->w2;
   p.b2 = e->b2;
+  p.split = e->split;
+  p.ld32 = e->ld32;
+  if (e->ld32 % 4) return set_error(-1, "ld32 must be a multiple of 4");
+  if (e->split && (e->split % 8 || e->store_mode == ST_QKV)) return set_error(-1, "split must be a multiple of 8; not with the QKV store");
   if (p.N % 16) return set_error(-1, "N=%d must be a multiple of 16", p.N);
   if (e->act == ACT_GEGLU) {
     if (p.N % 32 || !e->bias || !e->out) return set_error(-1, "GEGLU needs N%%32==0, bias and out");
@@ -219,7 +223,7 @@ int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, 
   p.stages = pick_stages(bn, two, epi, p.epi_tma);
   if (p.epi_tma == 1) {
     const uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
-    const uint64_t str[1] = {(uint64_t)epi->ldo * 4};
+    const uint64_t str[1] = {(uint64_t)(epi->ld32 ? epi->ld32 : epi->ldo) * 4};
     const uint32_t box[2] = {16, 128};
     if ((rc = encode_map(&p.tmD, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, CU_TENSOR_MAP_SWIZZLE_64B, epi->out_f32, 2, dims, str, box)))
       return rc;

@@ -15,6 +15,27 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// ------------------------------------------------------------------ split tensors (FP32-accuracy mode)
+// value = hi + lo, stored [hi | lo | hi] with `split` elements between the parts (include/vda_b200.h,
+// vda_epilogue::split).  split == 0: ordinary bf16 tensor.
+__device__ __forceinline__ float2 ld_pair(const bf16* p, int split) {
+  float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
+  if (split) {
+    const float2 l = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p + split));
+    t.x += l.x, t.y += l.y;
+  }
+  return t;
+}
+__device__ __forceinline__ void st_pair(bf16* p, float a, float b, int split) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  *reinterpret_cast<__nv_bfloat162*>(p) = h;
+  if (split) {
+    const float2 f = __bfloat1622float2(h);
+    *reinterpret_cast<__nv_bfloat162*>(p + split) = __floats2bfloat162_rn(a - f.x, b - f.y);
+    *reinterpret_cast<__nv_bfloat162*>(p + 2 * split) = h;
+  }
+}
+
 // ------------------------------------------------------------------ LayerNorm
 // One warp per row; the row lives in registers (C <= 64*MAXV).  Two-pass (mean, then centred variance) like torch's CPU/GPU kernels.
 // Output row remap: input rows are [frames, S] tokens; the first `skip` tokens of every frame are
@@ -24,7 +45,7 @@ template <typename TIn, int MAXV>
 __global__ void layernorm_kernel(const TIn* __restrict__ x, const float* __restrict__ gamma,
                                  const float* __restrict__ beta, bf16* __restrict__ out, bf16* __restrict__ out_nope,
                                  const float* __restrict__ pe, int rows, int C, float eps, int S, int skip,
-                                 int pe_rows_per_t, int pe_T) {
+                                 int pe_rows_per_t, int pe_T, int split) {
   const int warps_per_block = blockDim.x >> 5;
   const int row = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
@@ -62,8 +83,9 @@ __global__ void layernorm_kernel(const TIn* __restrict__ x, const float* __restr
   }
   const float rstd = rsqrtf(warp_sum(sq) / C + eps);
   const float* per = pe ? pe + static_cast<long long>((row / pe_rows_per_t) % pe_T) * C : nullptr;
-  bf16* o = out + orow * C;
-  bf16* o2 = out_nope ? out_nope + orow * C : nullptr;
+  const int ldo = split ? 3 * C : C;  // split outputs: [hi | lo | hi], parts C apart
+  bf16* o = out + orow * ldo;
+  bf16* o2 = out_nope ? out_nope + orow * ldo : nullptr;
 #pragma unroll
   for (int i = 0; i < MAXV; ++i) {
     const int c = (i * 32 + lane) * 2;
@@ -72,12 +94,12 @@ __global__ void layernorm_kernel(const TIn* __restrict__ x, const float* __restr
       const float2 bb = *reinterpret_cast<const float2*>(beta + c);
       float a = (v[i] - mean) * rstd * g.x + bb.x;
       float b = (w[i] - mean) * rstd * g.y + bb.y;
-      if (o2) *reinterpret_cast<__nv_bfloat162*>(o2 + c) = __floats2bfloat162_rn(a, b);
+      if (o2) st_pair(o2 + c, a, b, split);
       if (per) {
         const float2 pp = *reinterpret_cast<const float2*>(per + c);
         a += pp.x, b += pp.y;
       }
-      *reinterpret_cast<__nv_bfloat162*>(o + c) = __floats2bfloat162_rn(a, b);
+      st_pair(o + c, a, b, split);
     }
   }
 }
@@ -86,7 +108,7 @@ __global__ void layernorm_kernel(const TIn* __restrict__ x, const float* __restr
 // stats: one block per (image, row-chunk); thread t owns channel pair 2t; per-group partial sums
 // go through shared memory then one double atomicAdd per (group, block).
 __global__ void groupnorm_stats_kernel(const bf16* __restrict__ x, double* __restrict__ stats, int hw, int C, int ldx,
-                                       int rows_per_block) {
+                                       int rows_per_block, int split) {
   __shared__ float sh[64];
   const int img = blockIdx.y;
   const int r0 = blockIdx.x * rows_per_block;
@@ -97,8 +119,7 @@ __global__ void groupnorm_stats_kernel(const bf16* __restrict__ x, double* __res
   for (int c = threadIdx.x * 2; c < C; c += blockDim.x * 2) {
     float s = 0.f, ss = 0.f;
     for (int r = r0; r < r1; ++r) {
-      const float2 t = __bfloat1622float2(
-          *reinterpret_cast<const __nv_bfloat162*>(x + (static_cast<long long>(img) * hw + r) * ldx + c));
+      const float2 t = ld_pair(x + (static_cast<long long>(img) * hw + r) * ldx + c, split);
       s += t.x + t.y;
       ss += t.x * t.x + t.y * t.y;
     }
@@ -113,7 +134,8 @@ __global__ void groupnorm_stats_kernel(const bf16* __restrict__ x, double* __res
 
 __global__ void groupnorm_apply_kernel(const bf16* __restrict__ x, const double* __restrict__ stats,
                                        const float* __restrict__ gamma, const float* __restrict__ beta,
-                                       bf16* __restrict__ out, int hw, int C, int ldx, float eps, long long total_pairs) {
+                                       bf16* __restrict__ out, int hw, int C, int ldx, float eps, long long total_pairs,
+                                       int split) {
   const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= total_pairs) return;
   const int half_c = C / 2;
@@ -126,16 +148,16 @@ __global__ void groupnorm_apply_kernel(const bf16* __restrict__ x, const double*
   const double var = stats[img * 64 + 2 * g + 1] / n - mean * mean;
   const float rstd = rsqrtf(static_cast<float>(var > 0 ? var : 0) + eps);
   const float m = static_cast<float>(mean);
-  const float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(x + pix * ldx + c));
+  const float2 t = ld_pair(x + pix * ldx + c, split);
   const float a = (t.x - m) * rstd * gamma[c] + beta[c];
   const float b = (t.y - m) * rstd * gamma[c + 1] + beta[c + 1];
-  *reinterpret_cast<__nv_bfloat162*>(out + pix * C + c) = __floats2bfloat162_rn(a, b);
+  st_pair(out + pix * (split ? 3 * C : C) + c, a, b, split ? C : 0);  // split in -> split out, parts C apart
 }
 
 // ------------------------------------------------------------------ patch im2col (14x14, stride 14)
 // x fp32 NCHW [frames,3,H,W] -> A bf16 [frames*gh*gw, ldk] with k = (c, kh, kw) (patch_embed.py:66).
 __global__ void patch_im2col_kernel(const float* __restrict__ x, bf16* __restrict__ a, int H, int W, int gh, int gw,
-                                    int ldk) {
+                                    int ldk, int split) {
   const long long row = blockIdx.x;
   const int f = static_cast<int>(row / (gh * gw));
   const int p = static_cast<int>(row - static_cast<long long>(f) * gh * gw);
@@ -147,7 +169,13 @@ __global__ void patch_im2col_kernel(const float* __restrict__ x, bf16* __restric
       const int kh = r / 14, kw = r - kh * 14;
       v = x[((static_cast<long long>(f) * 3 + c) * H + ph * 14 + kh) * W + pw * 14 + kw];
     }
-    a[row * ldk + k] = __float2bfloat16(v);
+    if (split) {  // row = [hi | lo | hi], parts ldk apart
+      const bf16 hi = __float2bfloat16(v);
+      bf16* o = a + row * 3 * ldk + k;
+      o[0] = hi, o[ldk] = __float2bfloat16(v - __bfloat162float(hi)), o[2 * ldk] = hi;
+    } else {
+      a[row * ldk + k] = __float2bfloat16(v);
+    }
   }
 }
 
@@ -246,6 +274,50 @@ __global__ void __launch_bounds__(256) bilinear_nhwc_kernel(const bf16* __restri
   }
 }
 
+// Split-tensor version (FP32-accuracy mode): taps are hi + lo, the interpolation runs in fp32 and
+// the result is written back as [hi | lo | hi].  One thread per (output pixel, 8 channels).
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+  const uint32_t* w = &u.x;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(w + i));
+    f[2 * i] = t.x, f[2 * i + 1] = t.y;
+  }
+}
+__global__ void __launch_bounds__(256) bilinear_split_kernel(const bf16* __restrict__ x, bf16* __restrict__ out, int h, int w,
+                                                             int H, int W, int C, int ldx, int ldo, int sin, int sout,
+                                                             float sy, float sx) {
+  const int c8 = C >> 3;
+  const int px = threadIdx.x / c8;
+  const int c = (threadIdx.x - px * c8) << 3;
+  const int ppb = 256 / c8;
+  const int X = blockIdx.x * ppb + px;
+  if (X >= W || px >= ppb) return;
+  const int Y = blockIdx.y, n = blockIdx.z;
+  const float fy = sy * Y, fx = sx * X;
+  const int y0 = min(static_cast<int>(fy), h - 1), x0 = min(static_cast<int>(fx), w - 1);
+  const int y1 = min(y0 + 1, h - 1), x1 = min(x0 + 1, w - 1);
+  const float ly = fy - y0, lx = fx - x0;
+  const float wt[4] = {(1.f - ly) * (1.f - lx), (1.f - ly) * lx, ly * (1.f - lx), ly * lx};
+  const int ys[4] = {y0, y0, y1, y1}, xs[4] = {x0, x1, x0, x1};
+  const bf16* base = x + static_cast<long long>(n) * h * w * ldx + c;
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    const bf16* src = base + (static_cast<long long>(ys[t]) * w + xs[t]) * ldx;
+    float hi[8], lo[8];
+    unpack8(__ldg(reinterpret_cast<const uint4*>(src)), hi);
+    unpack8(__ldg(reinterpret_cast<const uint4*>(src + sin)), lo);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] += wt[t] * (hi[i] + lo[i]);
+  }
+  bf16* o = out + ((static_cast<long long>(n) * H + Y) * W + X) * ldo + c;
+#pragma unroll
+  for (int i = 0; i < 8; i += 2) st_pair(o + i, acc[i], acc[i + 1], sout);
+}
+
 // fp32 single-channel bilinear (video_depth.py:66,111-112), optional ReLU.
 __global__ void bilinear_f32_kernel(const float* __restrict__ x, float* __restrict__ out, int h, int w, int H, int W,
                                     float sy, float sx, int relu, long long total) {
@@ -295,13 +367,13 @@ using namespace vda;
 
 template <typename TIn>
 static int launch_ln(const void* x, const float* gamma, const float* beta, void* out, void* out_nope, const float* pe,
-                     int rows, int C, float eps, int S, int skip, int pe_rows_per_t, int pe_T, cudaStream_t st) {
+                     int rows, int C, float eps, int S, int skip, int pe_rows_per_t, int pe_T, int split, cudaStream_t st) {
   const int warps = 8;
   dim3 grid((rows + warps - 1) / warps), block(warps * 32);
 #define VDA_LN(MAXV)                                                                                              \
   layernorm_kernel<TIn, MAXV><<<grid, block, 0, st>>>(static_cast<const TIn*>(x), gamma, beta, static_cast<bf16*>(out), \
                                                       static_cast<bf16*>(out_nope), pe, rows, C, eps, S, skip,  \
-                                                      pe_rows_per_t, pe_T)
+                                                      pe_rows_per_t, pe_T, split ? C : 0)
   if (C <= 256) VDA_LN(4);
   else if (C <= 512) VDA_LN(8);
   else if (C <= 1024) VDA_LN(16);
@@ -314,19 +386,19 @@ extern "C" {
 
 int vda_layernorm(const void* x, int x_is_f32, const float* gamma, const float* beta, void* out, void* out_nope,
                   const float* pe, int rows, int C, float eps, int tokens_per_frame, int skip, int pe_rows_per_t,
-                  int pe_T, void* stream) {
+                  int pe_T, int split, void* stream) {
   if (!x || !gamma || !beta || !out || rows <= 0 || C % 2) return set_error(-1, "vda_layernorm: bad arguments");
   if (tokens_per_frame <= 0) tokens_per_frame = rows, skip = 0;
   if (pe && (pe_rows_per_t <= 0 || pe_T <= 0)) return set_error(-1, "vda_layernorm: pe needs rows_per_t and T");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   return x_is_f32 ? launch_ln<float>(x, gamma, beta, out, out_nope, pe, rows, C, eps, tokens_per_frame, skip,
-                                     pe_rows_per_t, pe_T, st)
+                                     pe_rows_per_t, pe_T, split, st)
                   : launch_ln<bf16>(x, gamma, beta, out, out_nope, pe, rows, C, eps, tokens_per_frame, skip,
-                                    pe_rows_per_t, pe_T, st);
+                                    pe_rows_per_t, pe_T, split, st);
 }
 
 int vda_groupnorm_nhwc(const void* x, int ldx, const float* gamma, const float* beta, void* out, double* stats_ws,
-                       int n, int hw, int C, float eps, void* stream) {
+                       int n, int hw, int C, float eps, int split, void* stream) {
   if (!x || !out || !stats_ws || C % 64 || n <= 0 || hw <= 0) return set_error(-1, "vda_groupnorm_nhwc: bad arguments (C%%64)");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc = check_cuda(cudaMemsetAsync(stats_ws, 0, sizeof(double) * 64 * n, st), "groupnorm memset");
@@ -334,18 +406,18 @@ int vda_groupnorm_nhwc(const void* x, int ldx, const float* gamma, const float* 
   const int rows_per_block = 32;
   dim3 grid((hw + rows_per_block - 1) / rows_per_block, n);
   const int threads = C / 2 < 512 ? C / 2 : 512;
-  groupnorm_stats_kernel<<<grid, threads, 0, st>>>(static_cast<const bf16*>(x), stats_ws, hw, C, ldx, rows_per_block);
+  groupnorm_stats_kernel<<<grid, threads, 0, st>>>(static_cast<const bf16*>(x), stats_ws, hw, C, ldx, rows_per_block, split);
   const long long total = static_cast<long long>(n) * hw * (C / 2);
   groupnorm_apply_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(
-      static_cast<const bf16*>(x), stats_ws, gamma, beta, static_cast<bf16*>(out), hw, C, ldx, eps, total);
+      static_cast<const bf16*>(x), stats_ws, gamma, beta, static_cast<bf16*>(out), hw, C, ldx, eps, total, split);
   return check_cuda(cudaGetLastError(), "groupnorm launch");
 }
 
-int vda_patch_im2col(const float* x, void* a, int frames, int H, int W, int ldk, void* stream) {
+int vda_patch_im2col(const float* x, void* a, int frames, int H, int W, int ldk, int split, void* stream) {
   if (!x || !a || H % 14 || W % 14 || ldk < 588 || ldk % 8) return set_error(-1, "vda_patch_im2col: bad arguments");
   const int gh = H / 14, gw = W / 14;
   patch_im2col_kernel<<<frames * gh * gw, 160, 0, static_cast<cudaStream_t>(stream)>>>(x, static_cast<bf16*>(a), H, W,
-                                                                                       gh, gw, ldk);
+                                                                                       gh, gw, ldk, split);
   return check_cuda(cudaGetLastError(), "patch_im2col launch");
 }
 
@@ -359,12 +431,20 @@ int vda_add_cls_pos(const float* patch, const float* cls, const float* pos, floa
 }
 
 int vda_bilinear_nhwc(const void* x, int ldx, void* out, int ldo, int n, int h, int w, int H, int W, int C,
-                      void* stream) {
+                      int split_in, int split_out, void* stream) {
   if (!x || !out || C % 8 || ldx % 8 || ldo % 8) return set_error(-1, "vda_bilinear_nhwc: bad arguments");
+  if ((split_in == 0) != (split_out == 0) || split_in % 8 || split_out % 8)
+    return set_error(-1, "vda_bilinear_nhwc: split_in / split_out must both be set (multiples of 8) or both 0");
   const float sy = H > 1 ? static_cast<float>(h - 1) / (H - 1) : 0.f;
   const float sx = W > 1 ? static_cast<float>(w - 1) / (W - 1) : 0.f;
   if (C > 2048 || H > 65535 || n > 65535) return set_error(-1, "vda_bilinear_nhwc: C <= 2048, H, n <= 65535");
   const int ppb = 256 / (C / 8);
+  if (split_in) {
+    const dim3 grid((W + ppb - 1) / ppb, H, n);
+    bilinear_split_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const bf16*>(x), static_cast<bf16*>(out), h, w, H, W, C, ldx, ldo, split_in, split_out, sy, sx);
+    return check_cuda(cudaGetLastError(), "bilinear_split launch");
+  }
   const dim3 grid((W + ppb - 1) / ppb, (H + kBilRows - 1) / kBilRows, n);
   bilinear_nhwc_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const bf16*>(x), static_cast<bf16*>(out), h, w, H, W, C, ldx, ldo, sy, sx);

@@ -72,6 +72,29 @@ __device__ __forceinline__ void add_bf16x16(const bf16* src, float (&v)[16]) {
   }
 }
 
+// FP32-accuracy mode ("split" activations): an fp32 value x is carried as two bf16 numbers
+// hi = bf16(x), lo = bf16(x - hi) (|x - hi - lo| <= 2^-17 |x|), laid out [hi | lo | hi] with
+// `stride` elements between the parts so that the tensor is directly the A operand of a GEMM whose
+// weights are packed [Wh | Wh | Wl] along K:  A.W = hi.Wh + lo.Wh + hi.Wl  (the lo.Wl term is 2^-16).
+__device__ __forceinline__ void store_split16(bf16* dst, const float (&v)[16], int stride) {
+  float lo[16];
+  uint32_t w[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    w[i] = *reinterpret_cast<uint32_t*>(&h);
+    const float2 f = __bfloat1622float2(h);
+    lo[2 * i] = v[2 * i] - f.x, lo[2 * i + 1] = v[2 * i + 1] - f.y;
+  }
+  uint4* d = reinterpret_cast<uint4*>(dst);
+  d[0] = make_uint4(w[0], w[1], w[2], w[3]);
+  d[1] = make_uint4(w[4], w[5], w[6], w[7]);
+  d = reinterpret_cast<uint4*>(dst + 2 * stride);
+  d[0] = make_uint4(w[0], w[1], w[2], w[3]);
+  d[1] = make_uint4(w[4], w[5], w[6], w[7]);
+  store_bf16x16(dst + stride, lo);
+}
+
 __device__ __forceinline__ void load_f32x16(const float* src, float (&o)[16]) {
   const float4* s = reinterpret_cast<const float4*>(src);
 #pragma unroll
@@ -141,6 +164,8 @@ __device__ __forceinline__ void finish_group16(const GemmParams& p, const RowMap
   } else {
     off = rm.row * p.ldo + col;
   }
+  // fp32 operands may have their own row pitch (split mode: the bf16 tensors are three parts wide)
+  const long long off32 = (p.ld32 && p.store_mode == ST_PLAIN) ? rm.row * p.ld32 + col : off;
   if (p.store_mode == ST_QKV && col >= 2 * p.qkv_d) {
     const int m = static_cast<int>(rm.row);
     const int b = m / p.qkv_s, sidx = m - b * p.qkv_s;
@@ -159,16 +184,29 @@ __device__ __forceinline__ void finish_group16(const GemmParams& p, const RowMap
     }
   } else if (p.res_f32) {
     float t[16];
-    load_f32x16(p.res_f32 + off, t);
+    load_f32x16(p.res_f32 + off32, t);
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] += t[i];
   }
   if (p.res1) add_bf16x16(p.res1 + off, v);
   if (p.res2) add_bf16x16(p.res2 + off, v);
+  if (p.split) {  // residuals are split tensors too: add their lo parts
+    if (p.res1) add_bf16x16(p.res1 + off + p.split, v);
+    if (p.res2) add_bf16x16(p.res2 + off + p.split, v);
+  }
   if (p.out_f32) {
-    float4* d = reinterpret_cast<float4*>(p.out_f32 + off);
+    float4* d = reinterpret_cast<float4*>(p.out_f32 + off32);
 #pragma unroll
     for (int i = 0; i < 4; ++i) d[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+  }
+  if (p.split) {
+    if (p.out) store_split16(p.out + off, v, p.split);
+    if (p.out_relu) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);
+      store_split16(p.out_relu + off, v, p.split);
+    }
+    return;
   }
   if (p.out) store_bf16x16(p.out + off, v);
   if (p.out_relu) {
@@ -194,7 +232,7 @@ __device__ __forceinline__ void epilogue_prefetch(const GemmParams& p, int m_til
   const RowMap rm = map_row(p, m_tile, r);
   if (!rm.valid) return;
   const int col = n_t * BN + cbeg;
-  const float* src = p.res_f32 + rm.row * p.ldo + col;
+  const float* src = p.res_f32 + rm.row * (p.ld32 ? p.ld32 : p.ldo) + col;
 #pragma unroll
   for (int i = 0; i < kPer; i += 32)
     if (col + i < p.N) prefetch_l2(src + i);
@@ -231,7 +269,7 @@ __device__ __forceinline__ void res_ring_issue(const GemmParams& p, const TileSc
     const RowMap rm = map_row(p, ts.m_mul * mq + ts.m_add, r);
     const int col = n_t * BN + half * kPer + 16 * g;
     if (rm.valid && col < p.N) {
-      const float* src = p.res_f32 + rm.row * p.ldo + col;
+      const float* src = p.res_f32 + rm.row * (p.ld32 ? p.ld32 : p.ldo) + col;
       const uint32_t dst = rr.base + static_cast<uint32_t>(k % rr.nbuf) * kResSlotPitch;
 #pragma unroll
       for (int i = 0; i < 4; ++i)
@@ -453,7 +491,10 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, int m_tile, i
 #pragma unroll
       for (int i = 0; i < 16; ++i)
         v[i] = (__uint_as_float(raw[i]) + b[i]) * gelu_fast(__uint_as_float(gate[i]) + bg[i]);
-      store_bf16x16(p.out + rm.row * p.ldo + (col >> 1), v);
+      if (p.split)
+        store_split16(p.out + rm.row * p.ldo + (col >> 1), v, p.split);
+      else
+        store_bf16x16(p.out + rm.row * p.ldo + (col >> 1), v);
       continue;
     }
 #pragma unroll

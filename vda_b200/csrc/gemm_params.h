@@ -26,6 +26,8 @@ struct alignas(64) GemmParams {
   int num_k_blocks;
   int m_tiles, n_tiles;
   int a_mode;
+  int ld32;    // row pitch of out_f32 / res_f32 when it differs from ldo (0 = ldo)
+  int split;   // > 0: bf16 outputs / residuals are split tensors [hi | lo | hi], parts `split` elements apart
   int stages;  // smem ring depth used by this launch (<= compiled maximum); freed stages hold the residual ring
   int sched;  // tile order: 0 = auto, 1 = round-robin, 2 = contiguous run per CTA (see gemm.cu)
   // conv geometry (a_mode == A_CONV3X3): stride 1, pad 1, output map = input map

@@ -73,15 +73,19 @@ class _Fusion:
 class Packed:
     """All kernel-layout weights of one VideoDepthAnything module."""
 
-    def __init__(self, model, dev):
+    def __init__(self, model, dev, split=False):
+        with P.split_mode(split):
+            self._pack(model, dev)
+
+    def _pack(self, model, dev):
         enc, head = model.pretrained, model.head
         self.arch = model.encoder
         cfg = ARCH[self.arch]
         self.D, self.heads, self.taps = cfg["dim"], cfg["heads"], cfg["taps"]
         D = self.D
-        wp = torch.zeros(D, 592, dtype=torch.bfloat16, device=dev)
-        wp[:, :588] = enc.patch_embed.proj.weight.detach().reshape(D, 588).to(dev).bfloat16()
-        self.w_patch, self.b_patch = wp, P.vec(enc.patch_embed.proj.bias, dev)
+        wp = torch.zeros(D, 592, dtype=torch.float32, device=dev)
+        wp[:, :588] = enc.patch_embed.proj.weight.detach().reshape(D, 588).to(dev).float()
+        self.w_patch, self.b_patch = P.to_kernel(wp), P.vec(enc.patch_embed.proj.bias, dev)
         self.cls = P.vec(enc.cls_token, dev)
         self.pos_embed = enc.pos_embed.detach().float().to(dev)
         self.pos_cache = {}
@@ -137,17 +141,31 @@ class Packed:
 class Engine:
     """Executes the window forward for one model on one device."""
 
-    def __init__(self, model, device):
+    def __init__(self, model, device, fp32=False):
+        """fp32=True builds the FP32-accuracy executor (video_depth.py:108, `fp32` of infer_video_depth):
+        the same launch sequence on split activations [hi | lo | hi] (3 bf16 parts per value) against
+        weights packed [Wh | Wh | Wl], i.e. 3-term bf16 products with fp32 accumulation on the same
+        tensor-core kernels, fp32 SIMT attention, and fp32 everywhere else (csrc/fp32path.cu)."""
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise L.VdaError("vda_b200 runs on sm_100a GPUs only; there is no CPU path")
         L.init(self.device)
+        self.fp32 = bool(fp32)
+        self.W = 3 if self.fp32 else 1  # bf16 parts per activation value
         with torch.cuda.device(self.device):
-            self.w = Packed(model, self.device)
+            self.w = Packed(model, self.device, split=self.fp32)
         self.ws = {}
         self.graphs = {}
         self.launches_per_run = {}
         self.use_graph = True
+
+    def _ep(self, width, **kw):
+        """Epilogue of a launch whose bf16 outputs / residuals are `width` channels wide (x3 parts in
+        FP32-accuracy mode); fp32 operands of the same launch keep pitch kw['ld32'] if given."""
+        if self.fp32:
+            return L.make_epilogue(ldo=width * 3, split=width, **kw)
+        kw.pop("ld32", None)
+        return L.make_epilogue(ldo=width, **kw)
 
     def _ws(self, key):
         if key not in self.ws:
@@ -163,30 +181,38 @@ class Engine:
         hw, D, heads = gh * gw, w.D, w.heads
         S, M = hw + 1, T * (hw + 1)
         spad = _pad(S, 8)
-        a = ws.get("patch_a", (T * hw, 592))
-        L.patch_im2col(x, a, T, H, W, 592)
+        sp, Wd = self.fp32, self.W
+        a = ws.get("patch_a", (T * hw, 592 * Wd))
+        L.patch_im2col(x, a, T, H, W, 592, split=int(sp))
         patch = ws.get("patch_f32", (T * hw, D), torch.float32)
-        L.gemm(a, w.w_patch, L.make_epilogue(bias=w.b_patch, out_f32=patch, ldo=D), K=588)
+        L.gemm(a, w.w_patch, L.make_epilogue(bias=w.b_patch, out_f32=patch, ldo=D), K=None if sp else 588)
         tok = ws.get("tokens", (M, D), torch.float32)
         L.add_cls_pos(patch, w.cls, w.pos_for(gh, gw), tok, T, hw, D)
-        xn = ws.get("xn", (M, D))
-        qk = ws.get("qk", (M, 2 * D))
-        vt = ws.get("vt", (T * heads, 64, spad), zero=True)
-        ao = ws.get("attn_out", (M, D))
-        h1 = ws.get("mlp_h", (M, 4 * D))
+        xn = ws.get("xn", (M, D * Wd))
+        ao = ws.get("attn_out", (M, D * Wd))
+        h1 = ws.get("mlp_h", (M, 4 * D * Wd))
+        if sp:
+            qkv32 = ws.get("qkv_f32", (M, 3 * D), torch.float32)
+        else:
+            qk = ws.get("qk", (M, 2 * D))
+            vt = ws.get("vt", (T * heads, 64, spad), zero=True)
         taps = []
         for i, b in enumerate(w.blocks):
-            L.layernorm(tok, b["n1w"], b["n1b"], xn, 1e-6)
-            L.gemm(xn, b["wqkv"], L.make_epilogue(bias=b["bqkv"], out=qk, ldo=2 * D, store_mode=L.ST_QKV,
-                                                  qkv=(vt, D, heads, S, spad)))
-            L.flash_attn(qk, vt, ao, T, S, heads, spad)
+            L.layernorm(tok, b["n1w"], b["n1b"], xn, 1e-6, C=D, split=int(sp))
+            if sp:
+                L.gemm(xn, b["wqkv"], L.make_epilogue(bias=b["bqkv"], out_f32=qkv32, ldo=3 * D))
+                L.attn_f32(qkv32, ao, D, T, S, heads)
+            else:
+                L.gemm(xn, b["wqkv"], L.make_epilogue(bias=b["bqkv"], out=qk, ldo=2 * D, store_mode=L.ST_QKV,
+                                                      qkv=(vt, D, heads, S, spad)))
+                L.flash_attn(qk, vt, ao, T, S, heads, spad)
             L.gemm(ao, b["wproj"], L.make_epilogue(bias=b["bproj"], scale=b["g1"], res_f32=tok, out_f32=tok, ldo=D))
-            L.layernorm(tok, b["n2w"], b["n2b"], xn, 1e-6)
-            L.gemm(xn, b["w1"], L.make_epilogue(bias=b["b1"], out=h1, ldo=4 * D, act=L.ACT_GELU))
+            L.layernorm(tok, b["n2w"], b["n2b"], xn, 1e-6, C=D, split=int(sp))
+            L.gemm(xn, b["w1"], self._ep(4 * D, bias=b["b1"], out=h1, act=L.ACT_GELU))
             L.gemm(h1, b["w2"], L.make_epilogue(bias=b["b2"], scale=b["g2"], res_f32=tok, out_f32=tok, ldo=D))
             if i in w.taps:
-                t = ws.get(f"tap{len(taps)}", (T * hw, D))
-                L.layernorm(tok, w.norm_w, w.norm_b, t, 1e-6, tokens_per_frame=S, skip=1)
+                t = ws.get(f"tap{len(taps)}", (T * hw, D * Wd))
+                L.layernorm(tok, w.norm_w, w.norm_b, t, 1e-6, C=D, tokens_per_frame=S, skip=1, split=int(sp))
                 taps.append(t)
         return taps
 
@@ -195,16 +221,24 @@ class Engine:
         """x, out: NHWC bf16 [T*hw, C].  motion_module.py:102-134 / :172-189 / :242-321."""
         m = self.w.motion[idx]
         C, rows = m.C, T * hw
+        sp, Wd = self.fp32, self.W
+        if sp and stream_ctx is not None:
+            raise L.VdaError("the streaming cache runs in BF16 only")
         tag = f"mm{idx}_"
-        gn = ws.get(tag + "gn", (rows, C))
+        gn = ws.get(tag + "gn", (rows, C * Wd))
         stats = ws.get(tag + "gnstats", (64 * T,), torch.float64)
-        L.groupnorm_nhwc(x, m.gn_w, m.gn_b, gn, stats, T, hw, C, 1e-6)
+        L.groupnorm_nhwc(x, m.gn_w, m.gn_b, gn, stats, T, hw, C, 1e-6, ldx=C * Wd, split=C if sp else 0)
         h = ws.get(tag + "h", (rows, C), torch.float32)
         L.gemm(gn, m.w_in, L.make_epilogue(bias=m.b_in, out_f32=h, ldo=C))
-        n = ws.get(tag + "n", (rows, C))
-        o = ws.get(tag + "o", (rows, C))
+        n = ws.get(tag + "n", (rows, C * Wd))
+        o = ws.get(tag + "o", (rows, C * Wd))
         for a_i, a in enumerate(m.attn):
-            if stream_ctx is None:
+            if sp:
+                qkv32 = ws.get(tag + "qkv_f32", (rows, 3 * C), torch.float32)
+                L.layernorm(h, a["ln_w"], a["ln_b"], n, 1e-5, C=C, pe=a["pe"], pe_rows_per_t=hw, pe_T=32, split=1)
+                L.gemm(n, a["wqkv"], L.make_epilogue(out_f32=qkv32, ldo=3 * C))
+                L.temporal_attn_f32(qkv32, C, o, C, hw, 8, T, T)
+            elif stream_ctx is None:
                 qkv = ws.get(tag + "qkv", (rows, 3 * C))
                 L.layernorm(h, a["ln_w"], a["ln_b"], n, 1e-5, pe=a["pe"], pe_rows_per_t=hw, pe_T=32)
                 L.gemm(n, a["wqkv"], L.make_epilogue(out=qkv, ldo=3 * C))
@@ -212,12 +246,12 @@ class Engine:
             else:
                 stream_ctx.attend(self, idx, a_i, a, h, n, o, hw, C, ws)
             L.gemm(o, a["wo"], L.make_epilogue(bias=a["bo"], res_f32=h, out_f32=h, ldo=C))
-        L.layernorm(h, m.ffn_w, m.ffn_b, n, 1e-5)
-        g = ws.get(tag + "geglu", (rows, 4 * C))
-        L.gemm(n, m.w_geglu, L.make_epilogue(bias=m.b_geglu, out=g, ldo=4 * C, act=L.ACT_GEGLU))
-        hb = ws.get(tag + "hb", (rows, C))
-        L.gemm(g, m.w_ff2, L.make_epilogue(bias=m.b_ff2, res_f32=h, out=hb, ldo=C))
-        L.gemm(hb, m.w_out, L.make_epilogue(bias=m.b_out, res1=x, out=out, out_relu=out_relu, ldo=C))
+        L.layernorm(h, m.ffn_w, m.ffn_b, n, 1e-5, C=C, split=int(sp))
+        g = ws.get(tag + "geglu", (rows, 4 * C * Wd))
+        L.gemm(n, m.w_geglu, self._ep(4 * C, bias=m.b_geglu, out=g, act=L.ACT_GEGLU))
+        hb = ws.get(tag + "hb", (rows, C * Wd))
+        L.gemm(g, m.w_ff2, self._ep(C, bias=m.b_ff2, res_f32=h, out=hb, ld32=C))
+        L.gemm(hb, m.w_out, self._ep(C, bias=m.b_out, res1=x, out=out, out_relu=out_relu))
         return out
 
     # ------------------------------------------------------------------ DPT head
@@ -228,58 +262,62 @@ class Engine:
         the bilinear upsample (both linear, interpolation weights sum to 1 => same result, 1/4 FLOPs)."""
         f = self.w.fusion[idx]
         Fc = self.w.F
+        Wd, Fw = self.W, self.w.F * self.W
         rows = T * h * w_
         tag = f"rf{idx}_"
-        t = ws.get(tag + "t", (rows, Fc))
+        t = ws.get(tag + "t", (rows, Fw))
         if x0 is not None:
             w1, b1, w2, b2 = f.rcu[0]
-            L.conv3x3(skip_relu, w1, L.make_epilogue(bias=b1, out=t, ldo=Fc, act=L.ACT_RELU), T, h, w_, Fc, Fc)
-            s = ws.get(tag + "s", (rows, Fc))
-            sr = ws.get(tag + "sr", (rows, Fc))
-            L.conv3x3(t, w2, L.make_epilogue(bias=b2, res1=skip, res2=x0, out=s, out_relu=sr, ldo=Fc), T, h, w_, Fc, Fc)
+            L.conv3x3(skip_relu, w1, self._ep(Fc, bias=b1, out=t, act=L.ACT_RELU), T, h, w_, Fw, Fc)
+            s = ws.get(tag + "s", (rows, Fw))
+            sr = ws.get(tag + "sr", (rows, Fw))
+            L.conv3x3(t, w2, self._ep(Fc, bias=b2, res1=skip, res2=x0, out=s, out_relu=sr), T, h, w_, Fw, Fc)
         else:
             s, sr = skip, skip_relu
         w1, b1, w2, b2 = f.rcu[1]
-        L.conv3x3(sr, w1, L.make_epilogue(bias=b1, out=t, ldo=Fc, act=L.ACT_RELU), T, h, w_, Fc, Fc)
-        u = ws.get(tag + "u", (rows, Fc))
-        L.conv3x3(t, w2, L.make_epilogue(bias=b2, res1=s, out=u, ldo=Fc), T, h, w_, Fc, Fc)
-        v = ws.get(tag + "v", (rows, Fc))
-        L.gemm(u, f.w_out, L.make_epilogue(bias=f.b_out, out=v, ldo=Fc))
+        L.conv3x3(sr, w1, self._ep(Fc, bias=b1, out=t, act=L.ACT_RELU), T, h, w_, Fw, Fc)
+        u = ws.get(tag + "u", (rows, Fw))
+        L.conv3x3(t, w2, self._ep(Fc, bias=b2, res1=s, out=u), T, h, w_, Fw, Fc)
+        v = ws.get(tag + "v", (rows, Fw))
+        L.gemm(u, f.w_out, self._ep(Fc, bias=f.b_out, out=v))
         H2, W2 = size
-        up = ws.get(tag + "up", (T * H2 * W2, Fc))
-        L.bilinear_nhwc(v, up, T, h, w_, H2, W2, Fc)
+        up = ws.get(tag + "up", (T * H2 * W2, Fw))
+        sp_stride = Fc if self.fp32 else 0
+        L.bilinear_nhwc(v, up, T, h, w_, H2, W2, Fc, ldx=Fw, ldo=Fw, split_in=sp_stride, split_out=sp_stride)
         return up
 
     def head(self, taps, gh, gw, T, ws, stream_ctx=None):
         """DPTHeadTemporal.forward (dpt_temporal.py:53-125) -> depth f32 [T, 14gh, 14gw]."""
         w = self.w
         Fc, oc, ocp, hw = w.F, w.oc, w.ocp, gh * gw
+        sp, Wd = self.fp32, self.W
         rows = T * hw
         pr = []
         for i in range(4):
             wk, bk = w.proj[i]
-            p = ws.get(f"proj{i}", (rows, wk.shape[0]))
-            L.gemm(taps[i], wk, L.make_epilogue(bias=bk, out=p, ldo=wk.shape[0]))
+            n_i = wk.shape[0]
+            p = ws.get(f"proj{i}", (rows, n_i * Wd))
+            L.gemm(taps[i], wk, self._ep(n_i, bias=bk, out=p))
             pr.append(p)
         wk, bk, s, cop = w.ct0
-        l1 = ws.get("layer1", (T * 16 * hw, cop))
-        L.gemm(pr[0], wk, L.make_epilogue(bias=bk, out=l1, ldo=cop, store_mode=L.ST_CONVT, ct=(s, cop, gh, gw)), K=oc[0])
+        l1 = ws.get("layer1", (T * 16 * hw, cop * Wd))
+        L.gemm(pr[0], wk, self._ep(cop, bias=bk, out=l1, store_mode=L.ST_CONVT, ct=(s, cop, gh, gw)), K=None if sp else oc[0])
         wk, bk, s, cop = w.ct1
-        l2 = ws.get("layer2", (T * 4 * hw, cop))
-        L.gemm(pr[1], wk, L.make_epilogue(bias=bk, out=l2, ldo=cop, store_mode=L.ST_CONVT, ct=(s, cop, gh, gw)), K=oc[1])
+        l2 = ws.get("layer2", (T * 4 * hw, cop * Wd))
+        L.gemm(pr[1], wk, self._ep(cop, bias=bk, out=l2, store_mode=L.ST_CONVT, ct=(s, cop, gh, gw)), K=None if sp else oc[1])
         gh4, gw4 = (gh - 1) // 2 + 1, (gw - 1) // 2 + 1
         hw4 = gh4 * gw4
-        col = ws.get("rs3_col", (T * hw4, 9 * oc[3]))
-        L.im2col_s2(pr[3], col, T, gh, gw, oc[3])
-        l4 = ws.get("layer4", (T * hw4, oc[3]))
-        L.gemm(col, w.w_rs3, L.make_epilogue(bias=w.b_rs3, out=l4, ldo=oc[3]))
-        l3m = self.motion(0, pr[2], T, hw, ws, ws.get("layer3m", (rows, oc[2])), stream_ctx=stream_ctx)
-        l4m = self.motion(1, l4, T, hw4, ws, ws.get("layer4m", (T * hw4, oc[3])), stream_ctx=stream_ctx)
+        col = ws.get("rs3_col", (T * hw4, 9 * oc[3] * Wd))
+        L.im2col_s2(pr[3], col, T, gh, gw, oc[3] * Wd)
+        l4 = ws.get("layer4", (T * hw4, oc[3] * Wd))
+        L.gemm(col, w.w_rs3, self._ep(oc[3], bias=w.b_rs3, out=l4))
+        l3m = self.motion(0, pr[2], T, hw, ws, ws.get("layer3m", (rows, oc[2] * Wd)), stream_ctx=stream_ctx)
+        l4m = self.motion(1, l4, T, hw4, ws, ws.get("layer4m", (T * hw4, oc[3] * Wd)), stream_ctx=stream_ctx)
 
         def rn(i, src, n_h, n_w, cin):
-            r = ws.get(f"rn{i}", (T * n_h * n_w, Fc))
-            rr = ws.get(f"rn{i}r", (T * n_h * n_w, Fc))
-            L.conv3x3(src, w.rn[i], L.make_epilogue(out=r, out_relu=rr, ldo=Fc), T, n_h, n_w, cin, Fc)
+            r = ws.get(f"rn{i}", (T * n_h * n_w, Fc * Wd))
+            rr = ws.get(f"rn{i}r", (T * n_h * n_w, Fc * Wd))
+            L.conv3x3(src, w.rn[i], self._ep(Fc, out=r, out_relu=rr), T, n_h, n_w, cin * Wd, Fc)
             return r, rr
 
         r1, r1r = rn(0, l1, 4 * gh, 4 * gw, ocp[0])
@@ -287,19 +325,22 @@ class Engine:
         r3, r3r = rn(2, l3m, gh, gw, ocp[2])
         r4, r4r = rn(3, l4m, gh4, gw4, ocp[3])
         p4 = self._fusion(4, ws, T, gh4, gw4, None, r4, r4r, (gh, gw))
-        p4m = self.motion(2, p4, T, hw, ws, ws.get("path4m", (rows, Fc)), stream_ctx=stream_ctx)
+        p4m = self.motion(2, p4, T, hw, ws, ws.get("path4m", (rows, Fc * Wd)), stream_ctx=stream_ctx)
         p3 = self._fusion(3, ws, T, gh, gw, p4m, r3, r3r, (2 * gh, 2 * gw))
-        p3m = self.motion(3, p3, T, 4 * hw, ws, ws.get("path3m", (T * 4 * hw, Fc)), stream_ctx=stream_ctx)
+        p3m = self.motion(3, p3, T, 4 * hw, ws, ws.get("path3m", (T * 4 * hw, Fc * Wd)), stream_ctx=stream_ctx)
         p2 = self._fusion(2, ws, T, 2 * gh, 2 * gw, p3m, r2, r2r, (4 * gh, 4 * gw))
         p1 = self._fusion(1, ws, T, 4 * gh, 4 * gw, p2, r1, r1r, (8 * gh, 8 * gw))
-        o1 = ws.get("out1", (T * 64 * hw, w.F2p))
-        L.conv3x3(p1, w.w_oc1, L.make_epilogue(bias=w.b_oc1, out=o1, ldo=w.F2p), T, 8 * gh, 8 * gw, Fc, w.F2p)
+        F2p = w.F2p
+        o1 = ws.get("out1", (T * 64 * hw, F2p * Wd))
+        L.conv3x3(p1, w.w_oc1, self._ep(F2p, bias=w.b_oc1, out=o1), T, 8 * gh, 8 * gw, Fc * Wd, F2p)
         Ho, Wo = gh * PATCH, gw * PATCH
-        up = ws.get("out1_up", (T * Ho * Wo, w.F2p))
-        L.bilinear_nhwc(o1, up, T, 8 * gh, 8 * gw, Ho, Wo, w.F2p)
+        up = ws.get("out1_up", (T * Ho * Wo, F2p * Wd))
+        sp_stride = F2p if sp else 0
+        L.bilinear_nhwc(o1, up, T, 8 * gh, 8 * gw, Ho, Wo, F2p, ldx=F2p * Wd, ldo=F2p * Wd, split_in=sp_stride,
+                        split_out=sp_stride)
         depth = ws.get("depth", (T, Ho, Wo), torch.float32)
         L.conv3x3(up, w.w_oc2, L.make_epilogue(bias=w.b_oc2, out_f32=depth, w2=w.w_last, b2=w.b_last,
-                                               store_mode=L.ST_HEADDOT), T, Ho, Wo, w.F2p, 32)
+                                               store_mode=L.ST_HEADDOT), T, Ho, Wo, F2p * Wd, 32)
         return depth
 
     # ------------------------------------------------------------------ whole window

@@ -23,7 +23,7 @@ class Epilogue(C.Structure):
         ("ct_s", C.c_int), ("ct_cout", C.c_int), ("ct_h", C.c_int), ("ct_w", C.c_int),
         ("vt", C.c_void_p),
         ("qkv_d", C.c_int), ("qkv_heads", C.c_int), ("qkv_s", C.c_int), ("qkv_spad", C.c_int),
-        ("w2", C.c_void_p), ("b2", C.c_float), ("cta_pair", C.c_int),
+        ("w2", C.c_void_p), ("b2", C.c_float), ("cta_pair", C.c_int), ("split", C.c_int), ("ld32", C.c_int),
     ]
 
 
@@ -87,15 +87,17 @@ def _declare(lib):
         "vda_gemm_bf16": [vp, i, vp, i, i, i, i, ep, vp],
         "vda_conv3x3_nhwc": [vp, i, vp, i, i, i, i, i, ep, vp],
         "vda_flash_attn_fwd": [vp, vp, vp, i, i, i, i, vp],
-        "vda_layernorm": [vp, i, vp, vp, vp, vp, vp, i, i, f, i, i, i, i, vp],
-        "vda_groupnorm_nhwc": [vp, i, vp, vp, vp, vp, i, i, i, f, vp],
-        "vda_patch_im2col": [vp, vp, i, i, i, i, vp],
+        "vda_layernorm": [vp, i, vp, vp, vp, vp, vp, i, i, f, i, i, i, i, i, vp],
+        "vda_groupnorm_nhwc": [vp, i, vp, vp, vp, vp, i, i, i, f, i, vp],
+        "vda_patch_im2col": [vp, vp, i, i, i, i, i, vp],
         "vda_add_cls_pos": [vp, vp, vp, vp, i, i, i, vp],
-        "vda_bilinear_nhwc": [vp, i, vp, i, i, i, i, i, i, i, vp],
+        "vda_bilinear_nhwc": [vp, i, vp, i, i, i, i, i, i, i, i, i, vp],
         "vda_bilinear_f32": [vp, vp, i, i, i, i, i, i, vp],
         "vda_im2col_s2": [vp, vp, i, i, i, i, vp],
         "vda_temporal_attn": [vp, i, vp, i, vp, i, vp, i, i, i, i, i, i, vp],
         "vda_temporal_attn_stream": [vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, vp],
+        "vda_attn_f32": [vp, i, vp, i, i, i, i, i, vp],
+        "vda_temporal_attn_f32": [vp, vp, vp, i, vp, i, i, i, i, i, i, i, vp],
         "vda_lsq_accum": [vp, vp, C.c_longlong, vp, vp],
         "vda_lsq_solve": [vp, vp, i, vp],
         "vda_affine_clamp": [vp, vp, C.c_longlong, vp, vp],
@@ -139,7 +141,7 @@ def ptr(t):
 
 def make_epilogue(bias=None, scale=None, res_f32=None, res1=None, res2=None, out=None, out_relu=None,
                   out_f32=None, ldo=0, act=ACT_NONE, store_mode=ST_PLAIN, block_n=0, ct=None, qkv=None,
-                  w2=None, b2=0.0, cta_pair=0):
+                  w2=None, b2=0.0, cta_pair=0, split=0, ld32=0):
     e = Epilogue()
     e.bias, e.scale, e.res_f32 = ptr(bias), ptr(scale), ptr(res_f32)
     e.res1, e.res2 = ptr(res1), ptr(res2)
@@ -151,6 +153,7 @@ def make_epilogue(bias=None, scale=None, res_f32=None, res1=None, res2=None, out
         vt, d, heads, s, spad = qkv
         e.vt, e.qkv_d, e.qkv_heads, e.qkv_s, e.qkv_spad = ptr(vt), d, heads, s, spad
     e.w2, e.b2, e.cta_pair = ptr(w2), b2, cta_pair
+    e.split, e.ld32 = split, ld32
     return e
 
 
@@ -179,23 +182,36 @@ def flash_attn(qk, vt, out, frames, S, heads, s_pad):
     _launched()
 
 
+def attn_f32(qkv, out, split, frames, S, heads):
+    with _timed("attn", 4.0 * frames * heads * S * S * 64):
+        check(load().vda_attn_f32(ptr(qkv), qkv.shape[1], ptr(out), out.shape[1], split, frames, S, heads, stream_ptr()))
+    _launched()
+
+
+def temporal_attn_f32(qkv, C_, out, split, hw, heads, Tq, Tk):
+    """qkv f32 [T*hw, 3*C_] (q | k | v); out split bf16 [Tq*hw, 3*split]."""
+    check(load().vda_temporal_attn_f32(ptr(qkv), ptr(qkv[:, C_:]), ptr(qkv[:, 2 * C_:]), qkv.shape[1], ptr(out),
+                                       out.shape[1], split, hw, heads, C_ // heads, Tq, Tk, stream_ptr()))
+    _launched()
+
+
 def layernorm(x, gamma, beta, out, eps, rows=None, C=None, tokens_per_frame=0, skip=0, pe=None, out_nope=None,
-              pe_rows_per_t=0, pe_T=0):
+              pe_rows_per_t=0, pe_T=0, split=0):
     rows = x.shape[0] if rows is None else rows
     C = x.shape[-1] if C is None else C
     check(load().vda_layernorm(ptr(x), int(x.dtype == torch.float32), ptr(gamma), ptr(beta), ptr(out), ptr(out_nope),
-                               ptr(pe), rows, C, eps, tokens_per_frame, skip, pe_rows_per_t, pe_T, stream_ptr()))
+                               ptr(pe), rows, C, eps, tokens_per_frame, skip, pe_rows_per_t, pe_T, split, stream_ptr()))
     _launched(1)
 
 
-def groupnorm_nhwc(x, gamma, beta, out, stats_ws, n, hw, C, eps, ldx=None):
+def groupnorm_nhwc(x, gamma, beta, out, stats_ws, n, hw, C, eps, ldx=None, split=0):
     check(load().vda_groupnorm_nhwc(ptr(x), C if ldx is None else ldx, ptr(gamma), ptr(beta), ptr(out), ptr(stats_ws),
-                                    n, hw, C, eps, stream_ptr()))
+                                    n, hw, C, eps, split, stream_ptr()))
     _launched(2)
 
 
-def patch_im2col(x, a, frames, H, W, ldk):
-    check(load().vda_patch_im2col(ptr(x), ptr(a), frames, H, W, ldk, stream_ptr()))
+def patch_im2col(x, a, frames, H, W, ldk, split=0):
+    check(load().vda_patch_im2col(ptr(x), ptr(a), frames, H, W, ldk, split, stream_ptr()))
     _launched(1)
 
 
@@ -204,9 +220,9 @@ def add_cls_pos(patch, cls, pos, tokens, frames, hw, D):
     _launched(1)
 
 
-def bilinear_nhwc(x, out, n, h, w, H, W, C, ldx=None, ldo=None):
+def bilinear_nhwc(x, out, n, h, w, H, W, C, ldx=None, ldo=None, split_in=0, split_out=0):
     check(load().vda_bilinear_nhwc(ptr(x), C if ldx is None else ldx, ptr(out), C if ldo is None else ldo,
-                                   n, h, w, H, W, C, stream_ptr()))
+                                   n, h, w, H, W, C, split_in, split_out, stream_ptr()))
     _launched(1)
 
 

@@ -8,7 +8,33 @@ window.  Layout rules:
   * ConvTranspose(k=s) weights are [(kh, kw, cout_padded), cin];
   * GEGLU projection rows are interleaved in 16-row value/gate groups (gemm.cu epilogue).
 """
+import contextlib
+
 import torch
+
+# FP32-accuracy mode (engine.Engine(fp32=True)): every weight is packed [Wh | Wh | Wl] along K (per
+# 3x3 tap for the implicit-GEMM convs), Wh = bf16(W), Wl = bf16(W - Wh), to be multiplied with split
+# activations [hi | lo | hi]: x.W ~= hi.Wh + lo.Wh + hi.Wl (include/vda_b200.h, vda_epilogue::split).
+SPLIT = False
+
+
+@contextlib.contextmanager
+def split_mode(on):
+    global SPLIT
+    old, SPLIT = SPLIT, bool(on)
+    try:
+        yield
+    finally:
+        SPLIT = old
+
+
+def to_kernel(w):
+    """f32 [..., K] -> bf16 [..., K], or [..., 3K] = [Wh | Wh | Wl] in split mode."""
+    hi = w.bfloat16()
+    if not SPLIT:
+        return hi.contiguous()
+    lo = (w - hi.float()).bfloat16()
+    return torch.cat([hi, hi, lo], dim=-1).contiguous()
 
 
 def _pad_to(n, m):
@@ -20,13 +46,13 @@ def linear(w, b=None, n_pad=16, device=None):
     w = w.detach().reshape(w.shape[0], -1).float()
     n, k = w.shape
     npad = _pad_to(n, n_pad)
-    wk = torch.zeros(npad, k, dtype=torch.bfloat16, device=device or w.device)
-    wk[:n] = w.to(wk.device).bfloat16()
+    wk = torch.zeros(npad, k, dtype=torch.float32, device=device or w.device)
+    wk[:n] = w.to(wk.device)
     bk = None
     if b is not None:
         bk = torch.zeros(npad, dtype=torch.float32, device=wk.device)
         bk[:n] = b.detach().float().to(wk.device)
-    return wk, bk
+    return to_kernel(wk), bk
 
 
 def conv3x3(w, b=None, cin_pad=64, cout_pad=16, device=None):
@@ -41,7 +67,7 @@ def conv3x3(w, b=None, cin_pad=64, cout_pad=16, device=None):
     if b is not None:
         bk = torch.zeros(cop, dtype=torch.float32, device=dev)
         bk[:co] = b.detach().float().to(dev)
-    return wk.reshape(cop, 9 * cip).bfloat16().contiguous(), bk
+    return to_kernel(wk.reshape(cop, 9, cip)).reshape(cop, -1).contiguous(), bk
 
 
 def conv_transpose(w, b, cout_pad=64, device=None):
@@ -54,7 +80,7 @@ def conv_transpose(w, b, cout_pad=64, device=None):
     wk[:, :, :co] = w.permute(2, 3, 1, 0).to(dev)
     bk = torch.zeros(s, s, cop, dtype=torch.float32, device=dev)
     bk[:, :, :co] = b.detach().float().to(dev)
-    return wk.reshape(s * s * cop, ci).bfloat16().contiguous(), bk.reshape(-1).contiguous(), s, cop
+    return to_kernel(wk.reshape(s * s * cop, ci)), bk.reshape(-1).contiguous(), s, cop
 
 
 def geglu(w, b, device=None):
@@ -64,7 +90,7 @@ def geglu(w, b, device=None):
     assert inner % 16 == 0
     idx = torch.arange(n).view(2, inner // 16, 16).permute(1, 0, 2).reshape(-1)
     dev = device or w.device
-    return (w.detach().float()[idx].to(dev).bfloat16().contiguous(),
+    return (to_kernel(w.detach().float()[idx].to(dev)),
             b.detach().float()[idx].to(dev).contiguous())
 
 

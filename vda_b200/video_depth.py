@@ -74,26 +74,37 @@ class VideoDepthAnything(nn.Module):
         self.head = DPTTemporalHead(self.pretrained.embed_dim, features, out_channels, num_frames)
         self.metric = metric
         self._engine = None
+        self._engine32 = None
+        # forward() precision: "bf16" (autocast path of the reference, video_depth.py:108) or "fp32"
+        # (the reference's forward outside autocast); infer_video_depth(fp32=...) selects it per call.
+        self.precision = "bf16"
 
     # -- lifecycle: packed weights are rebuilt lazily after .to()/.cuda()/load_state_dict()
     def _apply(self, fn, *a, **k):
-        self._engine = None
+        self._engine = self._engine32 = None
         return super()._apply(fn, *a, **k)
 
     def load_state_dict(self, *a, **k):
-        self._engine = None
+        self._engine = self._engine32 = None
         return super().load_state_dict(*a, **k)
 
-    def engine(self):
+    def engine(self, fp32=False):
+        """Window executor for the module's current device; fp32=True -> the FP32-accuracy executor
+        (split-bf16 tensor-core products, fp32 everywhere else; engine.Engine)."""
         dev = self.pretrained.cls_token.device
+        if fp32:
+            if self._engine32 is None or self._engine32.device != dev:
+                self._engine32 = Engine(self, dev, fp32=True)
+            return self._engine32
         if self._engine is None or self._engine.device != dev:
             self._engine = Engine(self, dev)
         return self._engine
 
-    def forward(self, x):
-        """x f32 [B,T,3,H,W], H and W multiples of 14 -> depth f32 [B,T,H,W] (>= 0)."""
+    def forward(self, x, fp32=None):
+        """x f32 [B,T,3,H,W], H and W multiples of 14 -> depth f32 [B,T,H,W] (>= 0).
+        fp32=None follows self.precision."""
         B, T = x.shape[:2]
-        eng = self.engine()
+        eng = self.engine(self.precision == "fp32" if fp32 is None else fp32)
         out = [eng.forward(x[b].float()).clone() for b in range(B)]
         return torch.stack(out, 0)
 
@@ -102,16 +113,16 @@ class VideoDepthAnything(nn.Module):
     def infer_video_depth(self, frames, target_fps, input_size=518, device="cuda", fp32=False):
         """frames uint8 [N,H0,W0,3] RGB -> (float32 [N,H0,W0], target_fps).
 
-        `fp32=True` is accepted for interface parity; this build's only arithmetic path is BF16
-        tensor-core GEMMs with FP32 accumulation/statistics (precision policy)."""
-        depth = self.infer_video_depth_device(frames, input_size=input_size, device=device)
+        fp32=False: BF16 tensor-core path (the reference's autocast branch, video_depth.py:108).
+        fp32=True: FP32-accuracy path (rtol 1e-3 against the reference's fp32 forward)."""
+        depth = self.infer_video_depth_device(frames, input_size=input_size, device=device, fp32=fp32)
         host = torch.empty(depth.shape, dtype=torch.float32, pin_memory=True)
         host.copy_(depth, non_blocking=True)
         torch.cuda.current_stream(depth.device).synchronize()
         return host.numpy(), target_fps
 
     @torch.no_grad()
-    def infer_video_depth_device(self, frames, input_size=518, device="cuda", windows=None, return_raw=False):
+    def infer_video_depth_device(self, frames, input_size=518, device="cuda", windows=None, return_raw=False, fp32=False):
         """Same as infer_video_depth but leaves the aligned depth [N,H0,W0] on the GPU.
         `windows` restricts the forward passes to a subset (multi-GPU sharding, vda_b200.parallel)."""
         if windows is None and not return_raw and parallel.active():
@@ -119,10 +130,11 @@ class VideoDepthAnything(nn.Module):
             n = len(frames)
             return parallel.distributed_infer(
                 n, window_frame_indices,
-                lambda ids: self.infer_video_depth_device(frames, input_size, device, windows=ids, return_raw=True),
+                lambda ids: self.infer_video_depth_device(frames, input_size, device, windows=ids, return_raw=True,
+                                                          fp32=fp32),
                 lambda raw: align_windows_device(raw, self.metric))
         prep = self.prepare_video(frames, input_size, device, windows)
-        raw = self.run_windows(prep)
+        raw = self.run_windows(prep, fp32=fp32)
         if return_raw:
             return raw
         return align_windows_device(raw, self.metric)[:prep["n"]]
@@ -145,9 +157,9 @@ class VideoDepthAnything(nn.Module):
             idx = [torch.tensor([slot[f] for f in wins[k]], device=dev) for k in mine]
         return dict(n=n, h0=h0, w0=w0, nh=nh, nw=nw, mine=mine, net_in=net_in, idx=idx, dev=dev)
 
-    def run_windows(self, prep):
+    def run_windows(self, prep, fp32=False):
         """Device side: one forward per owned window + bilinear to the source size -> raw [len*32,H0,W0]."""
-        eng = self.engine()
+        eng = self.engine(fp32)
         dev, h0, w0, nh, nw = prep["dev"], prep["h0"], prep["w0"], prep["nh"], prep["nw"]
         with torch.cuda.device(dev):
             raw = torch.empty(len(prep["mine"]) * INFER_LEN, h0, w0, dtype=torch.float32, device=dev)
