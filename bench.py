@@ -42,11 +42,14 @@ def parse():
     ap.add_argument("--size", type=int, default=518)
     ap.add_argument("--cpu-frames", type=int, default=2, help="frames of the CPU-baseline sample window")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"],
+                    help="fp32 = the FP32-accuracy mode (split-bf16 products, DESIGN.md 4b); not the headline config")
     return ap.parse_args()
 
 
 def config_of(a):
-    return {"workload": f"Video-Depth-Anything ({a.arch}) BF16, one {a.frames}-frame window {a.size}x{a.size} per GPU "
+    prec = "BF16" if a.precision == "bf16" else "FP32-accuracy mode (3-term split-bf16 products)"
+    return {"workload": f"Video-Depth-Anything ({a.arch}) {prec}, one {a.frames}-frame window {a.size}x{a.size} per GPU "
                         f"per step (BASELINE configs[1])",
             "arch": a.arch, "frames_per_window": a.frames, "height": a.size, "width": a.size,
             "weights": "random-init (seeded)", "sharding": "one independent window per rank per step",
@@ -174,7 +177,8 @@ def run_ours(a):
     x_host = torch.randn(1, T, 3, H, W, generator=g).pin_memory()
     out_host = torch.empty(1, T, H, W, dtype=torch.float32).pin_memory()
     x_dev = x_host.to(dev)
-    eng = model.engine()
+    fp32 = a.precision == "fp32"
+    eng = model.engine(fp32)
 
     # ---- device-resident timing (value): K window forwards, each one CUDA-graph replay of the
     # window's ~270 kernel launches
@@ -209,7 +213,7 @@ def run_ours(a):
     # ---- end to end through the public module call, host buffers in and out
     def e2e_step():
         xd = x_host.to(dev, non_blocking=True)
-        d = model(xd)
+        d = model(xd, fp32=fp32)
         out_host.copy_(d, non_blocking=True)
 
     e2e_step()
@@ -238,7 +242,8 @@ def run_ours(a):
     line = {
         "metric": METRIC, "value": total_frames / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": config_of(a),
+        "vs_baseline": None, "dtype": "bf16" if not fp32 else "bf16x3 (fp32-accurate)", "data": "synthetic",
+        "config": config_of(a),
         "p50_window_latency_ms": ms / a.steps, "ms_per_step_eager_instrumented": ms_eager / a.steps,
         "e2e": {"value": total_frames / (ms_e2e * 1e-3), "unit": UNIT,
                 "h2d_bytes_per_step": x_host.numel() * 4, "d2h_bytes_per_step": out_host.numel() * 4,
