@@ -141,6 +141,18 @@ def peaks():
         return 1400.0, 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def ncu_traffic():
+    """DRAM bytes (read + write) of the largest plain-GEMM launch (vitl fc1) from the committed
+    `ncu --set full` capture under profiles/ -- a profiler artefact, not measured in this run."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_fc1_gemm_tc2.json")))
+        mb = lambda k: float(d[k].split()[0]) * 1e6
+        alg = sum(d["algorithmic_bytes"].values())
+        return mb("dram__bytes_read.sum") + mb("dram__bytes_write.sum"), alg
+    except Exception:
+        return None, None
+
+
 def run_ours(a):
     import torch
     import torch.distributed as dist
@@ -197,6 +209,8 @@ def run_ours(a):
     barrier()
     launches = L.LAUNCHES - n0
     ms = max_over_ranks(e0.elapsed_time(e1))
+    d_last = eng.forward(x_dev[0])
+    depth_stats = [float(d_last.min()), float(d_last.mean()), float(d_last.max())]
     clk = clocks.stop() if clocks else None
 
     # ---- the same K steps launched eagerly with CUDA events around every tensor-core launch
@@ -248,11 +262,14 @@ def run_ours(a):
         "e2e": {"value": total_frames / (ms_e2e * 1e-3), "unit": UNIT,
                 "h2d_bytes_per_step": x_host.numel() * 4, "d2h_bytes_per_step": out_host.numel() * 4,
                 "ms_per_step": ms_e2e / a.steps},
-        "gpu_launches": launches,
+        "gpu_launches": launches, "depth_min_mean_max": depth_stats,
         "clocks": clk,
         "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (plain GEMM launches: encoder/motion Linears, 1x1 convs)",
                      "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s", "frac": achieved / tf_peak,
-                     "traffic": None, "peak_source": peak_src, "launches": n_g,
+                     "traffic": ncu_traffic()[0], "traffic_algorithmic_bytes": ncu_traffic()[1],
+                     "traffic_note": "DRAM read+write bytes of one fc1 launch (M=43840,N=4096,K=1024), ncu --set full, "
+                                     "profiles/r01_ncu_fc1_gemm_tc2.json",
+                     "peak_source": peak_src, "launches": n_g,
                      "flops_per_launch": f_g / n_g, "ms_per_launch": t_g / n_g},
         "breakdown_ms_per_step": {k: v[2] / a.steps for k, v in kinds.items()},
         "breakdown_tflops": {k: v[1] / (v[2] * 1e-3) / 1e12 for k, v in kinds.items() if v[2] > 0},

@@ -111,9 +111,10 @@ static int pick_epi_tma(const vda_epilogue* e, bool conv) {
   const bool off = off_lvl == 1;
   if (off || e->act == ACT_GEGLU || e->out_relu || e->res1 || e->res2 || e->split) return 0;
   const auto aligned = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
-  if (!conv && e->store_mode == ST_PLAIN && e->res_f32 && e->out_f32 == e->res_f32 && !e->out && e->ldo % 4 == 0 &&
-      aligned(e->out_f32))
-    return 1;
+  const int ldf = e->ld32 ? e->ld32 : e->ldo;
+  if (!conv && e->store_mode == ST_PLAIN && e->out_f32 && !e->out && ldf % 4 == 0 && aligned(e->out_f32) &&
+      (e->res_f32 == e->out_f32 || !e->res_f32))
+    return 1;  // in-place residual update (reduce-add) or plain fp32 output (store)
   if ((e->store_mode == ST_PLAIN || (!conv && e->store_mode == ST_QKV)) && e->out && !e->out_f32 && !e->res_f32 &&
       e->ldo % 8 == 0 && aligned(e->out) && off_lvl != 2)
     return 2;
@@ -222,6 +223,8 @@ int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, 
   p.epi_tma = pick_epi_tma(epi, false);
   p.stages = pick_stages(bn, two, epi, p.epi_tma);
   if (p.epi_tma == 1) {
+    const char* rs = getenv("VDA_GEMM_RED_AS_STORE");  // knob for timing experiments only (drops the residual)
+    p.f32_store = epi->res_f32 == nullptr || (rs && atoi(rs));
     const uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
     const uint64_t str[1] = {(uint64_t)(epi->ld32 ? epi->ld32 : epi->ldo) * 4};
     const uint32_t box[2] = {16, 128};

@@ -268,7 +268,9 @@ constexpr int kA2Smem = kQBytes + 2 * kKBytes + 2 * kVBytes + 256;
 constexpr float kRescaleThreshold = 8.0f;
 
 // POLY: one in POLY exponentials (0 = none, 2/4/8) is evaluated with poly_exp2 on the FMA pipe.
-template <int POLY>
+// LATE: the wait for PV_{j-1} (needed before P is overwritten / O rescaled) is taken after the
+// exponentials of tile j instead of before them, so that MMA latency hides behind the MUFU work.
+template <int POLY, bool LATE>
 __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __grid_constant__ AttnParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
@@ -432,26 +434,29 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
           m_run = m_tile;
           l_run *= alpha;
         }
-        // PV_{j-1} must be complete before P is overwritten (and before O is rescaled)
-        mbar_wait(o_done, (j - 1) & 1);
-        tc_fence_after();
-        if (__any_sync(0xffffffffu, need)) {
+        if (!LATE) {
+          // PV_{j-1} must be complete before P is overwritten (and before O is rescaled)
+          mbar_wait(o_done, (j - 1) & 1);
+          tc_fence_after();
+          if (__any_sync(0xffffffffu, need)) {
 #pragma unroll
-          for (int c0 = 0; c0 < 64; c0 += 32) {
-            uint32_t o[32];
-            tmem_ld32(tmem_O + lane_off + c0, o);
-            tmem_ld_wait();
+            for (int c0 = 0; c0 < 64; c0 += 32) {
+              uint32_t o[32];
+              tmem_ld32(tmem_O + lane_off + c0, o);
+              tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-            tmem_st32(tmem_O + lane_off + c0, o);
+              for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+              tmem_st32(tmem_O + lane_off + c0, o);
+            }
           }
         }
       }
       const float neg_m = -m_run;
       float l0 = 0.f, l1 = 0.f;
+      uint32_t pk[LATE ? 64 : 16];
 #pragma unroll
       for (int c0 = 0; c0 < 128; c0 += 32) {
-        uint32_t pk[16];
+        uint32_t* pc = LATE ? pk + (c0 >> 1) : pk;
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
           const float x0 = fmaf(__uint_as_float(s[c0 + i]), sc, neg_m);
@@ -461,9 +466,29 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
           l0 += p0;
           l1 += p1;
           __nv_bfloat162 h = __floats2bfloat162_rn(p0, p1);
-          pk[i >> 1] = *reinterpret_cast<uint32_t*>(&h);
+          pc[i >> 1] = *reinterpret_cast<uint32_t*>(&h);
         }
-        tmem_st16(tmem_P + lane_off + (c0 >> 1), pk);
+        if (!LATE) tmem_st16(tmem_P + lane_off + (c0 >> 1), *reinterpret_cast<uint32_t(*)[16]>(pc));
+      }
+      if (LATE) {
+        if (j > 0) {
+          mbar_wait(o_done, (j - 1) & 1);
+          tc_fence_after();
+          if (__any_sync(0xffffffffu, need)) {
+#pragma unroll
+            for (int c0 = 0; c0 < 64; c0 += 32) {
+              uint32_t o[32];
+              tmem_ld32(tmem_O + lane_off + c0, o);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+              tmem_st32(tmem_O + lane_off + c0, o);
+            }
+          }
+        }
+#pragma unroll
+        for (int c0 = 0; c0 < 128; c0 += 32)
+          tmem_st16(tmem_P + lane_off + (c0 >> 1), *reinterpret_cast<uint32_t(*)[16]>(pk + (c0 >> 1)));
       }
       l_run += l0 + l1;
       tmem_st_wait();
@@ -536,32 +561,30 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
   p.kv_tiles = (S + 127) / 128;
   p.scale_log2 = 0.125f * 1.4426950408889634f;
   static bool configured = false;
-  static int variant = 2, poly = 0;
   if (!configured) {
-    const char* v = getenv("VDA_ATTN_VARIANT");  // 1 = first-generation kernel (P via smem), kept for A/B runs
-    if (v && v[0] == '1') variant = 1;
-    const char* pe = getenv("VDA_ATTN_POLY");    // 0 / 2 / 4 / 8: share of exponentials on the FMA pipe (tuning)
-    if (pe) poly = atoi(pe);
     int rc = check_cuda(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmem),
                         "attn smem attribute");
     if (rc) return rc;
-    rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
-    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
-    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
-    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
+    rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
     if (rc) return rc;
     configured = true;
   }
+  // A/B knobs: VDA_ATTN_VARIANT=1 first-generation kernel (P via smem); VDA_ATTN_POLY=4 a quarter of the
+  // exponentials on the FMA pipe; VDA_ATTN_LATE=0/1 position of the PV_{j-1} wait
+  const char* ev = getenv("VDA_ATTN_VARIANT");
+  const char* ep = getenv("VDA_ATTN_POLY");
+  const char* el = getenv("VDA_ATTN_LATE");
+  const int variant = (ev && ev[0] == '1') ? 1 : 2, poly = ep ? atoi(ep) : 0, late = el ? atoi(el) : 1;
   dim3 grid(p.q_tiles, heads, frames);
   if (variant == 1)
     attn_fwd_kernel<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(stream)>>>(p);
-  else if (poly == 0)
-    attn_fwd_v2_kernel<0><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
-  else if (poly == 2)
-    attn_fwd_v2_kernel<2><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
-  else if (poly == 8)
-    attn_fwd_v2_kernel<8><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+  else if (poly != 0)
+    attn_fwd_v2_kernel<4, false><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+  else if (late)
+    attn_fwd_v2_kernel<0, true><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
   else
-    attn_fwd_v2_kernel<4><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+    attn_fwd_v2_kernel<0, false><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
   return check_cuda(cudaGetLastError(), "attn launch");
 }

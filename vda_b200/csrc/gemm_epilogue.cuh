@@ -399,7 +399,10 @@ __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_til
     if (issuer) {
       if (col < p.N) {  // rows >= M / cols >= N / pixels outside the map are clipped by TMA
         if constexpr (MODE == 1) {
-          tma_reduce_add_2d(&p.tmD, box, col, m_tile * kBlockM);
+          if (p.f32_store)
+            tma_store_2d(&p.tmD, box, col, m_tile * kBlockM);  // plain fp32 output, no residual
+          else
+            tma_reduce_add_2d(&p.tmD, box, col, m_tile * kBlockM);
         } else if (p.a_mode == A_CONV3X3) {
           const int tpi = p.tiles_w * p.tiles_h;
           const int img = m_tile / tpi;

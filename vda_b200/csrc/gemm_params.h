@@ -26,6 +26,7 @@ struct alignas(64) GemmParams {
   int num_k_blocks;
   int m_tiles, n_tiles;
   int a_mode;
+  int f32_store;  // epi_tma == 1 only: store the fp32 box instead of reduce-adding it (no residual)
   int ld32;    // row pitch of out_f32 / res_f32 when it differs from ldo (0 = ldo)
   int split;   // > 0: bf16 outputs / residuals are split tensors [hi | lo | hi], parts `split` elements apart
   int stages;  // smem ring depth used by this launch (<= compiled maximum); freed stages hold the residual ring

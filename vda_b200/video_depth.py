@@ -42,6 +42,12 @@ def randomize_zero_init_(model, seed=0):
         with torch.no_grad():
             po.weight.copy_(torch.randn(po.weight.shape, generator=g) * po.weight.shape[1] ** -0.5)
             po.bias.copy_(torch.randn(po.bias.shape, generator=g) * 0.02)
+    # keep the regressed depth strictly positive on random weights (the last 1x1 conv sums ReLU outputs:
+    # non-negative weights + a positive bias cannot be zeroed by the final ReLU)
+    last = model.head.scratch.output_conv2[2]
+    with torch.no_grad():
+        last.weight.abs_()
+        last.bias.fill_(0.1)
     return model
 
 
