@@ -143,3 +143,15 @@ def test_streaming_vs_reference_golden():
     errs = [absrel(got[i], gold[i]) for i in range(v["n"])]
     print(f"stream: absrel first {errs[0]:.2e} max {max(errs):.2e} last {errs[-1]:.2e}")
     assert max(errs) <= ABSREL_TOL
+
+
+def test_forward_pipelined_matches_forward():
+    """Host-buffer pipeline (side-stream H2D / D2H, double-buffered) returns what forward() returns."""
+    model, _ = build("vits")
+    xs = [G.window_input(4, 70, 98, seed=s)[0].pin_memory() for s in range(5)]
+    with torch.no_grad():
+        want = [model(x[None].cuda())[0].cpu() for x in xs]
+        got = model.forward_pipelined(iter(xs))
+    assert len(got) == 5
+    for g, w_ in zip(got, want):
+        assert g.is_pinned() and torch.equal(g, w_)

@@ -114,6 +114,59 @@ class VideoDepthAnything(nn.Module):
         out = [eng.forward(x[b].float()).clone() for b in range(B)]
         return torch.stack(out, 0)
 
+    @torch.no_grad()
+    def forward_pipelined(self, host_windows, out=None, fp32=False):
+        """Window forwards with HOST buffers in and out, copies overlapped with compute.
+        host_windows: iterable of pinned f32 [T,3,H,W] tensors; out: optional list of pinned f32 [T,H,W]
+        tensors to fill (allocated otherwise).  Window i+1's H2D copy and window i-1's D2H copy run on
+        two side streams while window i computes; two staging buffers each way.  Returns the list of
+        host depth tensors (valid after the call: it synchronises at the end)."""
+        eng = self.engine(fp32)
+        dev = eng.device
+        outs = []
+        with torch.cuda.device(dev):
+            main = torch.cuda.current_stream()
+            s_in, s_out = self._side_streams(dev)
+            st = None
+            for i, xh in enumerate(host_windows):
+                if st is None or st["shape"] != tuple(xh.shape):
+                    T, _, H, W = xh.shape
+                    st = dict(shape=tuple(xh.shape),
+                              xin=[torch.empty(T, 3, H, W, device=dev) for _ in range(2)],
+                              dout=[torch.empty(T, H, W, device=dev) for _ in range(2)],
+                              in_ready=[torch.cuda.Event() for _ in range(2)], in_free=[None, None],
+                              out_ready=[torch.cuda.Event() for _ in range(2)], out_free=[None, None])
+                b = i & 1
+                oh = out[i] if out is not None else torch.empty(st["shape"][0], *st["shape"][2:], pin_memory=True)
+                with torch.cuda.stream(s_in):
+                    if st["in_free"][b] is not None:
+                        s_in.wait_event(st["in_free"][b])       # window i-2 has consumed this staging buffer
+                    st["xin"][b].copy_(xh, non_blocking=True)
+                    st["in_ready"][b].record(s_in)
+                main.wait_event(st["in_ready"][b])
+                d = eng.forward(st["xin"][b])
+                st["in_free"][b] = torch.cuda.Event()
+                st["in_free"][b].record(main)
+                if st["out_free"][b] is not None:
+                    main.wait_event(st["out_free"][b])          # window i-2's D2H has drained this buffer
+                st["dout"][b].copy_(d)                          # d is a workspace buffer the next window overwrites
+                st["out_ready"][b].record(main)
+                with torch.cuda.stream(s_out):
+                    s_out.wait_event(st["out_ready"][b])
+                    oh.copy_(st["dout"][b], non_blocking=True)
+                    st["out_free"][b] = torch.cuda.Event()
+                    st["out_free"][b].record(s_out)
+                outs.append(oh)
+            s_out.synchronize()
+            main.synchronize()
+        return outs
+
+    def _side_streams(self, dev):
+        key = str(dev)
+        if getattr(self, "_streams", None) is None or self._streams[0] != key:
+            self._streams = (key, torch.cuda.Stream(dev), torch.cuda.Stream(dev))
+        return self._streams[1], self._streams[2]
+
     # ------------------------------------------------------------------ offline driver
     @torch.no_grad()
     def infer_video_depth(self, frames, target_fps, input_size=518, device="cuda", fp32=False):
