@@ -126,6 +126,10 @@ int vda_temporal_attn_stream(const void* q, const void* knew, const void* vnew, 
                              const int* slots, const float* pe_q, const float* pe_k, const float* pe_v, void* out,
                              int ldo, int hw, int heads, int head_dim, int Tk, void* stream);
 
+/* Frame pre-processing (util/transform.py:51-157 via video_depth.py:77-89): frames uint8 RGB [n,H0,W0,3]
+ * -> out f32 [n,3,nh,nw] = ((cv2-compatible INTER_CUBIC resize of frame/255) - mean) / std. */
+int vda_preprocess_u8(const void* frames, int n, int H0, int W0, float* out, int nh, int nw, void* stream);
+
 /* FP32-accuracy mode attention (fp32=True of infer_video_depth, video_depth.py:108).  Inputs are the
  * fp32 q/k/v written by the projection GEMM, outputs are split tensors (vda_epilogue::split).
  * vda_attn_f32: qkv f32 [frames*S, ld >= 3*heads*64] laid out q | k | v (dinov2_layers/attention.py:51-59);

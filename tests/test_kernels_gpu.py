@@ -219,3 +219,19 @@ def test_attention_throughput_report(L, capsys):
     fl = 4 * frames * heads * S * S * 64
     with capsys.disabled():
         print(f"\n[attn] vitl block: {ms:.3f} ms = {fl / ms / 1e9:.0f} TFLOP/s")
+
+
+@pytest.mark.parametrize("h0,w0,size", [(90, 120, 112), (720, 1280, 518), (518, 518, 518), (300, 200, 518)])
+def test_preprocess_u8_matches_cv2_path(L, h0, w0, size):
+    """GPU pre-processing against the reference's own host path (cv2 INTER_CUBIC + float64 normalise)."""
+    from vda_b200.preprocess import net_input_size, preprocess_frames, preprocess_frames_cv2
+
+    rng = np.random.default_rng(0)
+    frames = rng.integers(0, 256, (3, h0, w0, 3), dtype=np.uint8)
+    nh, nw = net_input_size(h0, w0, size)
+    got = preprocess_frames(frames, [2, 0], nh, nw, "cuda")
+    want = preprocess_frames_cv2(frames, [2, 0], nh, nw, "cuda")
+    assert got.shape == want.shape == (2, 3, nh, nw)
+    err = (got - want).abs().max().item()
+    print(f"preprocess {h0}x{w0}->{nh}x{nw}: max abs diff vs cv2 {err:.2e}")
+    assert err < 1e-4  # cv2 sums the 16 taps in a different (SIMD) order: a few 1e-6 before the 1/std scaling

@@ -96,6 +96,7 @@ def _declare(lib):
         "vda_im2col_s2": [vp, vp, i, i, i, i, vp],
         "vda_temporal_attn": [vp, i, vp, i, vp, i, vp, i, i, i, i, i, i, vp],
         "vda_temporal_attn_stream": [vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, vp],
+        "vda_preprocess_u8": [vp, i, i, i, vp, i, i, vp],
         "vda_attn_f32": [vp, i, vp, i, i, i, i, i, vp],
         "vda_temporal_attn_f32": [vp, vp, vp, i, vp, i, i, i, i, i, i, i, vp],
         "vda_lsq_accum": [vp, vp, C.c_longlong, vp, vp],
@@ -179,6 +180,13 @@ def conv3x3(x, w, epi, n, H, W, Cin, Cout, ldx=None):
 def flash_attn(qk, vt, out, frames, S, heads, s_pad):
     with _timed("attn", 4.0 * frames * heads * S * S * 64):
         check(load().vda_flash_attn_fwd(ptr(qk), ptr(vt), ptr(out), frames, S, heads, s_pad, stream_ptr()))
+    _launched()
+
+
+def preprocess_u8(frames_u8, out, nh, nw):
+    """frames_u8 uint8 [n,H0,W0,3] on the GPU -> out f32 [n,3,nh,nw]."""
+    n, h0, w0, _ = frames_u8.shape
+    check(load().vda_preprocess_u8(ptr(frames_u8), n, h0, w0, ptr(out), nh, nw, stream_ptr()))
     _launched()
 
 
