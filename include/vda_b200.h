@@ -126,6 +126,12 @@ int vda_temporal_attn_stream(const void* q, const void* knew, const void* vnew, 
                              const int* slots, const float* pe_q, const float* pe_k, const float* pe_v, void* out,
                              int ldo, int hw, int heads, int head_dim, int Tk, void* stream);
 
+/* Fused depth tail (dpt_temporal.py:116-123, dpt.py:117-124): bilinear(align_corners=True) of the NHWC bf16
+ * map x [n,h,w,ldx>=C] to (H,W), 3x3 conv C->32 (w3 bf16 [32, 9*C], k=(kh,kw,c); b3) + ReLU, 1x1 conv
+ * 32->1 (w1, b1) + ReLU -> out f32 [n,H,W].  C in {64, 128}. */
+int vda_depth_tail(const void* x, int ldx, const void* w3, const float* b3, const float* w1, float b1, float* out,
+                   int n, int h, int w, int H, int W, int C, void* stream);
+
 /* Frame pre-processing (util/transform.py:51-157 via video_depth.py:77-89): frames uint8 RGB [n,H0,W0,3]
  * -> out f32 [n,3,nh,nw] = ((cv2-compatible INTER_CUBIC resize of frame/255) - mean) / std. */
 int vda_preprocess_u8(const void* frames, int n, int H0, int W0, float* out, int nh, int nw, void* stream);

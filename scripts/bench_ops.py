@@ -42,7 +42,17 @@ up_out = torch.empty(T, 296, 296, 256, device=dev, dtype=torch.bfloat16)
 up2_in = r(T, 296, 296, 128).to(torch.bfloat16)
 up2_out = torch.empty(T, 518, 518, 128, device=dev, dtype=torch.bfloat16)
 
+from vda_b200 import packing as _P
+tw3, tb3 = _P.conv3x3(r(32, 128, 3, 3, sc=1152 ** -0.5), r(32), device=dev)
+tw1 = r(32).abs()
+tdepth = torch.empty(T, 518, 518, device=dev)
+
 ops = {
+    "tail": (lambda: L.depth_tail(up2_in, tw3, tb3, tw1, 0.1, tdepth, T, 296, 296, 518, 518, 128), 2 * T * 518 * 518 * 32 * 1152),
+    "tail_unfused": (lambda: (L.bilinear_nhwc(up2_in, up2_out, T, 296, 296, 518, 518, 128),
+                              L.conv3x3(up2_out, tw3, L.make_epilogue(bias=tb3, out_f32=tdepth, w2=tw1, b2=0.1,
+                                                                      store_mode=L.ST_HEADDOT), T, 518, 518, 128, 32)),
+                     2 * T * 518 * 518 * 32 * 1152),
     "tattn0": (lambda: L.temporal_attn(tq0, 3072, tq0[:, 1024:], 3072, tq0[:, 2048:], 3072, to0, 1024, 1369, 8, 128, 32, 32),
                4 * 1369 * 8 * 32 * 32 * 128),
     "tattn3": (lambda: L.temporal_attn(tq3, 768, tq3[:, 256:], 768, tq3[:, 512:], 768, to3, 256, 5476, 8, 32, 32, 32),

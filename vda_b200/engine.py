@@ -6,6 +6,8 @@ Data layout: activations are row-major [rows, channels] --
 two residual streams (ViT tokens, motion-module hidden states) kept in fp32.  torch only owns the
 buffers (one workspace per input shape, reused for every window); no torch op runs per window.
 """
+import os
+
 import torch
 
 from . import lib as L
@@ -334,11 +336,17 @@ class Engine:
         o1 = ws.get("out1", (T * 64 * hw, F2p * Wd))
         L.conv3x3(p1, w.w_oc1, self._ep(F2p, bias=w.b_oc1, out=o1), T, 8 * gh, 8 * gw, Fc * Wd, F2p)
         Ho, Wo = gh * PATCH, gw * PATCH
+        depth = ws.get("depth", (T, Ho, Wo), torch.float32)
+        if not sp and F2p in (64, 128) and os.environ.get("VDA_TAIL_FUSED", "0") == "1":
+            # upsample + 3x3(->32) + ReLU + 1x1(->1) + ReLU in one kernel (csrc/depth_tail.cu).  Opt-in: at
+            # one 8-warp CTA per SM its interpolation phase is issue-bound (1.9 ms) and the mma.sync phase
+            # takes 1.5 ms, 3.3 ms together against 3.25 ms for the two-kernel path below.
+            L.depth_tail(o1, w.w_oc2, w.b_oc2, w.w_last, w.b_last, depth, T, 8 * gh, 8 * gw, Ho, Wo, F2p)
+            return depth
         up = ws.get("out1_up", (T * Ho * Wo, F2p * Wd))
         sp_stride = F2p if sp else 0
         L.bilinear_nhwc(o1, up, T, 8 * gh, 8 * gw, Ho, Wo, F2p, ldx=F2p * Wd, ldo=F2p * Wd, split_in=sp_stride,
                         split_out=sp_stride)
-        depth = ws.get("depth", (T, Ho, Wo), torch.float32)
         L.conv3x3(up, w.w_oc2, L.make_epilogue(bias=w.b_oc2, out_f32=depth, w2=w.w_last, b2=w.b_last,
                                                store_mode=L.ST_HEADDOT), T, Ho, Wo, F2p * Wd, 32)
         return depth
