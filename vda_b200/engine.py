@@ -160,6 +160,7 @@ class Engine:
         self.graphs = {}
         self.launches_per_run = {}
         self.use_graph = True
+        self._warm = set()
 
     def _ep(self, width, **kw):
         """Epilogue of a launch whose bf16 outputs / residuals are `width` channels wide (x3 parts in
@@ -368,8 +369,33 @@ class Engine:
         key = ("win", T, H, W)
         ws = self._ws(key)
         with torch.cuda.device(self.device):
-            if stream_ctx is not None or not self.use_graph or L.PROFILE is not None:
+            if not self.use_graph or L.PROFILE is not None:
                 return self._run(x.contiguous(), ws, stream_ctx)
+            if stream_ctx is not None:
+                # Streaming step: once the cache is full (Tk == 32, from the second frame on) the launch
+                # sequence is fixed -- the per-frame slot list lives in a device buffer that begin_frame()
+                # refreshes -- so it is captured once per cache and replayed (per-frame latency is
+                # launch-bound otherwise: ~300 launches for one frame of work).
+                if stream_ctx.Tk != 32:
+                    return self._run(x.contiguous(), ws, stream_ctx)
+                key = ("stream", T, H, W, id(stream_ctx))
+                xin = ws.get("graph_in", (T, 3, H, W), torch.float32)
+                xin.copy_(x)
+                g = self.graphs.get(key)
+                if g is None:
+                    if key not in self._warm:          # first full-cache frame runs eagerly (allocates buffers)
+                        self._warm = {key}
+                        self.graphs = {k: v for k, v in self.graphs.items() if k[0] != "stream"}
+                        return self._run(xin, ws, stream_ctx)
+                    torch.cuda.current_stream().synchronize()
+                    graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(graph):
+                        out = self._run(xin, ws, stream_ctx)
+                    g = self.graphs[key] = (graph, out)
+                n0 = L.LAUNCHES
+                g[0].replay()
+                L.LAUNCHES = n0 + self.launches_per_run[("win", T, H, W)]
+                return g[1]
             xin = ws.get("graph_in", (T, 3, H, W), torch.float32)
             xin.copy_(x)
             g = self.graphs.get(key)
