@@ -88,7 +88,7 @@ int vda_layernorm(const void* x, int x_is_f32, const float* gamma, const float* 
 /* split != 0 (FP32-accuracy mode): out / out_nope rows are 3*C wide, [hi | lo | hi] (see vda_epilogue::split). */
 
 /* GroupNorm(32 groups) on an NHWC bf16 map [n, hw, ldx>=C] -> [n, hw, C] bf16 (motion_module.py:112).
- * stats_ws: 64*n doubles of scratch. */
+ * stats_ws: 96*n doubles of scratch (64*n fp64 sums + 32*n float2 mean/rstd). */
 int vda_groupnorm_nhwc(const void* x, int ldx, const float* gamma, const float* beta, void* out, double* stats_ws,
                        int n, int hw, int C, float eps, int split, void* stream);
 /* split > 0: x is a split tensor whose parts are `split` elements apart; out is [n, hw, 3*C] split, parts C apart. */

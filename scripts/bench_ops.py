@@ -47,7 +47,13 @@ tw3, tb3 = _P.conv3x3(r(32, 128, 3, 3, sc=1152 ** -0.5), r(32), device=dev)
 tw1 = r(32).abs()
 tdepth = torch.empty(T, 518, 518, device=dev)
 
+gn_x = r(T * 5476, 256).to(torch.bfloat16)
+gn_o = torch.empty_like(gn_x)
+gn_w, gn_b = r(256), r(256)
+gn_ws = torch.empty(96 * T, device=dev, dtype=torch.float64)
+
 ops = {
+    "gn74": (lambda: L.groupnorm_nhwc(gn_x, gn_w, gn_b, gn_o, gn_ws, T, 5476, 256, 1e-6), 0),
     "tail": (lambda: L.depth_tail(up2_in, tw3, tb3, tw1, 0.1, tdepth, T, 296, 296, 518, 518, 128), 2 * T * 518 * 518 * 32 * 1152),
     "tail_unfused": (lambda: (L.bilinear_nhwc(up2_in, up2_out, T, 296, 296, 518, 518, 128),
                               L.conv3x3(up2_out, tw3, L.make_epilogue(bias=tb3, out_f32=tdepth, w2=tw1, b2=0.1,

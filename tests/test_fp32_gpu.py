@@ -126,7 +126,7 @@ def test_split_elementwise_kernels(L):
     xm = _rand(n * hw, Cg, seed=4) * 2 + 1
     gg, gb = _rand(Cg, seed=5), _rand(Cg, seed=6)
     og = torch.empty(n * hw, 3 * Cg, device="cuda", dtype=torch.bfloat16)
-    stats = torch.empty(64 * n, device="cuda", dtype=torch.float64)
+    stats = torch.empty(96 * n, device="cuda", dtype=torch.float64)
     L.groupnorm_nhwc(split3(xm), gg, gb, og, stats, n, hw, Cg, 1e-6, ldx=3 * Cg, split=Cg)
     want = F.group_norm(xm.double().view(n, hw, Cg).permute(0, 2, 1), 32, gg.double(), gb.double(), 1e-6)
     want = want.permute(0, 2, 1).reshape(-1, Cg).float()

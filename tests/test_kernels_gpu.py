@@ -101,7 +101,7 @@ def test_groupnorm_nhwc(L, n, h, w, C):
     want = F.group_norm(x.float(), 32, g, b, 1e-6).permute(0, 2, 3, 1)
     xn = x.permute(0, 2, 3, 1).contiguous()
     out = torch.empty(n, h, w, C, device="cuda", dtype=torch.bfloat16)
-    ws = torch.empty(64 * n, device="cuda", dtype=torch.float64)
+    ws = torch.empty(96 * n, device="cuda", dtype=torch.float64)
     L.groupnorm_nhwc(xn, g, b, out, ws, n, h * w, C, 1e-6)
     _close(out, want, 1e-2)
 

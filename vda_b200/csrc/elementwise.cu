@@ -46,6 +46,8 @@ __global__ void layernorm_kernel(const TIn* __restrict__ x, const float* __restr
                                  const float* __restrict__ beta, bf16* __restrict__ out, bf16* __restrict__ out_nope,
                                  const float* __restrict__ pe, int rows, int C, float eps, int S, int skip,
                                  int pe_rows_per_t, int pe_T, int split) {
+  // each lane owns MAXV/2 groups of 4 consecutive channels: 16-byte fp32 loads, 8-byte bf16 stores
+  constexpr int kQ = MAXV / 2;
   const int warps_per_block = blockDim.x >> 5;
   const int row = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
@@ -54,31 +56,32 @@ __global__ void layernorm_kernel(const TIn* __restrict__ x, const float* __restr
   if (s < skip) return;
   const long long orow = static_cast<long long>(f) * (S - skip) + (s - skip);
   const TIn* xr = x + static_cast<long long>(row) * C;
-  float v[MAXV], w[MAXV];  // even / odd element of each channel pair owned by this lane
+  float4 v[kQ];
   float sum = 0.f;
 #pragma unroll
-  for (int i = 0; i < MAXV; ++i) {
-    const int c = (i * 32 + lane) * 2;
-    v[i] = 0.f, w[i] = 0.f;
+  for (int i = 0; i < kQ; ++i) {
+    const int c = (i * 32 + lane) * 4;
+    v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (c < C) {
-      float2 t;
       if constexpr (sizeof(TIn) == 4) {
-        t = *reinterpret_cast<const float2*>(xr + c);
+        v[i] = *reinterpret_cast<const float4*>(xr + c);
       } else {
-        t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(xr + c));
+        const uint2 u = *reinterpret_cast<const uint2*>(xr + c);
+        const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.x));
+        const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.y));
+        v[i] = make_float4(a.x, a.y, b.x, b.y);
       }
-      v[i] = t.x, w[i] = t.y;
-      sum += t.x + t.y;
+      sum += (v[i].x + v[i].y) + (v[i].z + v[i].w);
     }
   }
   const float mean = warp_sum(sum) / C;
   float sq = 0.f;
 #pragma unroll
-  for (int i = 0; i < MAXV; ++i) {
-    const int c = (i * 32 + lane) * 2;
+  for (int i = 0; i < kQ; ++i) {
+    const int c = (i * 32 + lane) * 4;
     if (c < C) {
-      const float da = v[i] - mean, db = w[i] - mean;
-      sq += da * da + db * db;
+      const float d0 = v[i].x - mean, d1 = v[i].y - mean, d2 = v[i].z - mean, d3 = v[i].w - mean;
+      sq += (d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3);
     }
   }
   const float rstd = rsqrtf(warp_sum(sq) / C + eps);
@@ -87,19 +90,31 @@ __global__ void layernorm_kernel(const TIn* __restrict__ x, const float* __restr
   bf16* o = out + orow * ldo;
   bf16* o2 = out_nope ? out_nope + orow * ldo : nullptr;
 #pragma unroll
-  for (int i = 0; i < MAXV; ++i) {
-    const int c = (i * 32 + lane) * 2;
+  for (int i = 0; i < kQ; ++i) {
+    const int c = (i * 32 + lane) * 4;
     if (c < C) {
-      const float2 g = *reinterpret_cast<const float2*>(gamma + c);
-      const float2 bb = *reinterpret_cast<const float2*>(beta + c);
-      float a = (v[i] - mean) * rstd * g.x + bb.x;
-      float b = (w[i] - mean) * rstd * g.y + bb.y;
-      if (o2) st_pair(o2 + c, a, b, split);
-      if (per) {
-        const float2 pp = *reinterpret_cast<const float2*>(per + c);
-        a += pp.x, b += pp.y;
+      const float4 g = *reinterpret_cast<const float4*>(gamma + c);
+      const float4 bb = *reinterpret_cast<const float4*>(beta + c);
+      float r0 = (v[i].x - mean) * rstd * g.x + bb.x, r1 = (v[i].y - mean) * rstd * g.y + bb.y;
+      float r2 = (v[i].z - mean) * rstd * g.z + bb.z, r3 = (v[i].w - mean) * rstd * g.w + bb.w;
+      if (o2) {
+        if (split) {
+          st_pair(o2 + c, r0, r1, split), st_pair(o2 + c + 2, r2, r3, split);
+        } else {
+          const __nv_bfloat162 h0 = __floats2bfloat162_rn(r0, r1), h1 = __floats2bfloat162_rn(r2, r3);
+          *reinterpret_cast<uint2*>(o2 + c) = make_uint2(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1));
+        }
       }
-      st_pair(o + c, a, b, split);
+      if (per) {
+        const float4 pp = *reinterpret_cast<const float4*>(per + c);
+        r0 += pp.x, r1 += pp.y, r2 += pp.z, r3 += pp.w;
+      }
+      if (split) {
+        st_pair(o + c, r0, r1, split), st_pair(o + c + 2, r2, r3, split);
+      } else {
+        const __nv_bfloat162 h0 = __floats2bfloat162_rn(r0, r1), h1 = __floats2bfloat162_rn(r2, r3);
+        *reinterpret_cast<uint2*>(o + c) = make_uint2(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1));
+      }
     }
   }
 }
@@ -132,26 +147,64 @@ __global__ void groupnorm_stats_kernel(const bf16* __restrict__ x, double* __res
     atomicAdd(&stats[static_cast<long long>(img) * 64 + i], static_cast<double>(sh[i]));
 }
 
-__global__ void groupnorm_apply_kernel(const bf16* __restrict__ x, const double* __restrict__ stats,
-                                       const float* __restrict__ gamma, const float* __restrict__ beta,
-                                       bf16* __restrict__ out, int hw, int C, int ldx, float eps, long long total_pairs,
-                                       int split) {
-  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (idx >= total_pairs) return;
-  const int half_c = C / 2;
-  const long long pix = idx / half_c;
-  const int c = static_cast<int>(idx - pix * half_c) * 2;
-  const int img = static_cast<int>(pix / hw);
-  const int g = c / (C / 32);
+// mean / rstd per (image, group) from the fp64 sums, once (the apply kernel used to redo the fp64
+// divisions per element pair, which made it 6x slower than its HBM time).
+__global__ void groupnorm_finalize_kernel(const double* __restrict__ stats, float2* __restrict__ mr, int total, int hw,
+                                          int C, float eps) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
   const double n = static_cast<double>(hw) * (C / 32);
-  const double mean = stats[img * 64 + 2 * g] / n;
-  const double var = stats[img * 64 + 2 * g + 1] / n - mean * mean;
-  const float rstd = rsqrtf(static_cast<float>(var > 0 ? var : 0) + eps);
-  const float m = static_cast<float>(mean);
-  const float2 t = ld_pair(x + pix * ldx + c, split);
-  const float a = (t.x - m) * rstd * gamma[c] + beta[c];
-  const float b = (t.y - m) * rstd * gamma[c + 1] + beta[c + 1];
-  st_pair(out + pix * (split ? 3 * C : C) + c, a, b, split ? C : 0);  // split in -> split out, parts C apart
+  const double mean = stats[2 * i] / n;
+  const double var = stats[2 * i + 1] / n - mean * mean;
+  mr[i] = make_float2(static_cast<float>(mean), rsqrtf(static_cast<float>(var > 0 ? var : 0) + eps));
+}
+
+// One thread per (pixel, 8 channels): 16-byte loads and stores (8 channels never straddle a group: C/32 % 8 == 0
+// or C/32 in {2, 4} handled per pair).
+__global__ void groupnorm_apply_kernel(const bf16* __restrict__ x, const float2* __restrict__ mr,
+                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                       bf16* __restrict__ out, int hw, int C, int ldx, long long total_oct, int split) {
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= total_oct) return;
+  const int c8 = C >> 3;
+  const long long pix = idx / c8;
+  const int c = static_cast<int>(idx - pix * c8) << 3;
+  const int img = static_cast<int>(pix / hw);
+  const int cg = C / 32;
+  const bf16* src = x + pix * ldx + c;
+  bf16* dst = out + pix * (split ? 3 * C : C) + c;
+  const uint4 hi = __ldg(reinterpret_cast<const uint4*>(src));
+  uint4 lo = make_uint4(0, 0, 0, 0);
+  if (split) lo = __ldg(reinterpret_cast<const uint4*>(src + split));
+  const uint32_t* ph = &hi.x;
+  const uint32_t* pl = &lo.x;
+  float r[8];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int cc = c + 2 * i;
+    const float2 m = __ldg(mr + img * 32 + cc / cg);
+    float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(ph + i));
+    if (split) {
+      const float2 l = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(pl + i));
+      t.x += l.x, t.y += l.y;
+    }
+    const float2 g = __ldg(reinterpret_cast<const float2*>(gamma + cc));
+    const float2 b = __ldg(reinterpret_cast<const float2*>(beta + cc));
+    r[2 * i] = (t.x - m.x) * m.y * g.x + b.x;
+    r[2 * i + 1] = (t.y - m.x) * m.y * g.y + b.y;
+  }
+  if (split) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) st_pair(dst + 2 * i, r[2 * i], r[2 * i + 1], C);  // split in -> split out, parts C apart
+  } else {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const __nv_bfloat162 h = __floats2bfloat162_rn(r[2 * i], r[2 * i + 1]);
+      w[i] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    *reinterpret_cast<uint4*>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
 }
 
 // ------------------------------------------------------------------ patch im2col (14x14, stride 14)
@@ -387,7 +440,7 @@ extern "C" {
 int vda_layernorm(const void* x, int x_is_f32, const float* gamma, const float* beta, void* out, void* out_nope,
                   const float* pe, int rows, int C, float eps, int tokens_per_frame, int skip, int pe_rows_per_t,
                   int pe_T, int split, void* stream) {
-  if (!x || !gamma || !beta || !out || rows <= 0 || C % 2) return set_error(-1, "vda_layernorm: bad arguments");
+  if (!x || !gamma || !beta || !out || rows <= 0 || C % 4) return set_error(-1, "vda_layernorm: bad arguments (C%%4)");
   if (tokens_per_frame <= 0) tokens_per_frame = rows, skip = 0;
   if (pe && (pe_rows_per_t <= 0 || pe_T <= 0)) return set_error(-1, "vda_layernorm: pe needs rows_per_t and T");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -407,9 +460,12 @@ int vda_groupnorm_nhwc(const void* x, int ldx, const float* gamma, const float* 
   dim3 grid((hw + rows_per_block - 1) / rows_per_block, n);
   const int threads = C / 2 < 512 ? C / 2 : 512;
   groupnorm_stats_kernel<<<grid, threads, 0, st>>>(static_cast<const bf16*>(x), stats_ws, hw, C, ldx, rows_per_block, split);
-  const long long total = static_cast<long long>(n) * hw * (C / 2);
+  // stats_ws: 64*n doubles of sums, reused in place for the 32*n float2 (mean, rstd) pairs behind them
+  float2* mr = reinterpret_cast<float2*>(stats_ws + 64 * n) ;
+  groupnorm_finalize_kernel<<<(32 * n + 127) / 128, 128, 0, st>>>(stats_ws, mr, 32 * n, hw, C, eps);
+  const long long total = static_cast<long long>(n) * hw * (C / 8);
   groupnorm_apply_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(
-      static_cast<const bf16*>(x), stats_ws, gamma, beta, static_cast<bf16*>(out), hw, C, ldx, eps, total, split);
+      static_cast<const bf16*>(x), mr, gamma, beta, static_cast<bf16*>(out), hw, C, ldx, total, split);
   return check_cuda(cudaGetLastError(), "groupnorm launch");
 }
 

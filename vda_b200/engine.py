@@ -229,7 +229,7 @@ class Engine:
             raise L.VdaError("the streaming cache runs in BF16 only")
         tag = f"mm{idx}_"
         gn = ws.get(tag + "gn", (rows, C * Wd))
-        stats = ws.get(tag + "gnstats", (64 * T,), torch.float64)
+        stats = ws.get(tag + "gnstats", (96 * T,), torch.float64)
         L.groupnorm_nhwc(x, m.gn_w, m.gn_b, gn, stats, T, hw, C, 1e-6, ldx=C * Wd, split=C if sp else 0)
         h = ws.get(tag + "h", (rows, C), torch.float32)
         L.gemm(gn, m.w_in, L.make_epilogue(bias=m.b_in, out_f32=h, ldo=C))
