@@ -132,6 +132,10 @@ int vda_temporal_attn_stream(const void* q, const void* knew, const void* vnew, 
 int vda_depth_tail(const void* x, int ldx, const void* w3, const float* b3, const float* w1, float b1, float* out,
                    int n, int h, int w, int H, int W, int C, void* stream);
 
+/* Debug probe (tests only): D f32 [128,32] = A[128,64] * W[32,64]^T where A's row 8g+i is row
+ * g*(sbo/128) + row0 + i of the bf16 source G [320,64], read through a tap-shifted tcgen05 descriptor. */
+int vda_debug_umma_shift(const void* G, const void* W, float* D, int row0, int sbo, int base_offset, void* stream);
+
 /* Frame pre-processing (util/transform.py:51-157 via video_depth.py:77-89): frames uint8 RGB [n,H0,W0,3]
  * -> out f32 [n,3,nh,nw] = ((cv2-compatible INTER_CUBIC resize of frame/255) - mean) / std. */
 int vda_preprocess_u8(const void* frames, int n, int H0, int W0, float* out, int nh, int nw, void* stream);

@@ -6,6 +6,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 
 import vda_b200.lib as L
+from vda_b200 import packing as _P
 
 L.init()
 T, S, D, heads = 32, 1370, 1024, 16
@@ -42,7 +43,6 @@ up_out = torch.empty(T, 296, 296, 256, device=dev, dtype=torch.bfloat16)
 up2_in = r(T, 296, 296, 128).to(torch.bfloat16)
 up2_out = torch.empty(T, 518, 518, 128, device=dev, dtype=torch.bfloat16)
 
-from vda_b200 import packing as _P
 tw3, tb3 = _P.conv3x3(r(32, 128, 3, 3, sc=1152 ** -0.5), r(32), device=dev)
 tw1 = r(32).abs()
 tdepth = torch.empty(T, 518, 518, device=dev)
@@ -52,7 +52,18 @@ gn_o = torch.empty_like(gn_x)
 gn_w, gn_b = r(256), r(256)
 gn_ws = torch.empty(96 * T, device=dev, dtype=torch.float64)
 
+oc_x = r(T, 296, 296, 256).to(torch.bfloat16)
+oc_w, oc_b = _P.conv3x3(r(128, 256, 3, 3, sc=2304 ** -0.5), r(128), device=dev)
+oc_y = torch.empty(T, 296, 296, 128, device=dev, dtype=torch.bfloat16)
+
 ops = {
+    "oc1": (lambda: L.conv3x3(oc_x, oc_w, L.make_epilogue(bias=oc_b, out=oc_y, ldo=128), T, 296, 296, 256, 128),
+            2 * T * 296 * 296 * 128 * 2304),
+    "oc1_1cta": (lambda: L.conv3x3(oc_x, oc_w, L.make_epilogue(bias=oc_b, out=oc_y, ldo=128, cta_pair=1), T, 296, 296, 256, 128),
+                 2 * T * 296 * 296 * 128 * 2304),
+    "tailconv": (lambda: L.conv3x3(up2_out, tw3, L.make_epilogue(bias=tb3, out_f32=tdepth, w2=tw1, b2=0.1,
+                                                                  store_mode=L.ST_HEADDOT), T, 518, 518, 128, 32),
+                 2 * T * 518 * 518 * 32 * 1152),
     "gn74": (lambda: L.groupnorm_nhwc(gn_x, gn_w, gn_b, gn_o, gn_ws, T, 5476, 256, 1e-6), 0),
     "tail": (lambda: L.depth_tail(up2_in, tw3, tb3, tw1, 0.1, tdepth, T, 296, 296, 518, 518, 128), 2 * T * 518 * 518 * 32 * 1152),
     "tail_unfused": (lambda: (L.bilinear_nhwc(up2_in, up2_out, T, 296, 296, 518, 518, 128),

@@ -282,6 +282,29 @@ int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W,
   p.n_tiles = (Cout + bn - 1) / bn;
   p.epi_tma = pick_epi_tma(epi, true);
   p.stages = pick_stages(bn, two, epi, p.epi_tma);
+  // halo mode (gemm.cu): few output channels -> one halo patch + 9 W tiles per channel block instead of
+  // 9 separate (tap, block) stages.  1-CTA kernel, 8 x 16-pixel tiles, BN <= 64.
+  {
+    const char* hv = getenv("VDA_CONV_HALO");  // A/B knob: 0 disables
+    p.halo = !(hv && atoi(hv) == 0) && !two && bn <= 64 && C % 64 == 0;
+    if (p.halo) {
+      const int halo_stage = 23 * 1024 + 9 * bn * 128;
+      const int max_halo = bn <= 32 ? 3 : 2;
+      const bool staged = p.epi_tma || (epi->res_f32 && epi->store_mode == ST_PLAIN && epi->act != ACT_GEGLU);
+      p.stages = staged ? 2 : max_halo;  // the epilogue's 48 KB of boxes / residual ring sit behind the ring
+      const int ring = (bn <= 32 ? 8 * 20480 : 8 * 24576) > max_halo * halo_stage ? (bn <= 32 ? 8 * 20480 : 8 * 24576) : max_halo * halo_stage;
+      if (staged && p.stages * halo_stage + 48 * 1024 > ring) p.halo = 0, p.stages = pick_stages(bn, two, epi, p.epi_tma);
+    }
+  }
+  if (p.halo) {
+    p.tw_log2 = 3;
+    p.tiles_w = (W + 7) / 8, p.tiles_h = (H + 15) / 16;
+    p.m_tiles = n * p.tiles_w * p.tiles_h;
+    const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)n};
+    const uint64_t str[3] = {(uint64_t)ldx * 2, (uint64_t)W * ldx * 2, (uint64_t)H * W * ldx * 2};
+    const uint32_t box[4] = {64, 10, 18, 1};
+    if ((rc = encode_bf16_map(&p.tmH, x, 4, dims, str, box))) return rc;
+  }
   if (p.epi_tma == 2) {
     const uint64_t dims[4] = {(uint64_t)Cout, (uint64_t)W, (uint64_t)H, (uint64_t)n};
     const uint64_t str[3] = {(uint64_t)epi->ldo * 2, (uint64_t)W * epi->ldo * 2, (uint64_t)H * W * epi->ldo * 2};
@@ -292,7 +315,7 @@ int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W,
   {
     const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)n};
     const uint64_t str[3] = {(uint64_t)ldx * 2, (uint64_t)W * ldx * 2, (uint64_t)H * W * ldx * 2};
-    const uint32_t box[4] = {64, (uint32_t)tw, (uint32_t)th, 1};
+    const uint32_t box[4] = {64, 1u << p.tw_log2, 128u >> p.tw_log2, 1};
     if ((rc = encode_bf16_map(&p.tmA, x, 4, dims, str, box))) return rc;
   }
   {

@@ -199,6 +199,15 @@ __device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t saddr) {
   const uint32_t hi = 64u | (1u << 14) | (2u << 29);
   return (static_cast<uint64_t>(hi) << 32) | lo;
 }
+// Same, with the 8-row groups `sbo` bytes apart and an arbitrary 128-byte-row start address.  The
+// swizzle is a function of the absolute shared-memory address bits (measured with
+// vda_debug_umma_shift, scripts/umma_probe.py: any row shift and any group pitch read correctly with
+// base_offset = 0), so a tile written by ONE TMA box can be read at tap-shifted row origins.
+__device__ __forceinline__ uint64_t umma_desc_k_sw128_sbo(uint32_t saddr, uint32_t sbo) {
+  const uint32_t lo = ((saddr >> 4) & 0x3FFFu) | (1u << 16);
+  const uint32_t hi = ((sbo >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
+  return (static_cast<uint64_t>(hi) << 32) | lo;
+}
 // kind::f16 instruction descriptor: f32 accumulate, K-major A and B.
 __host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N, bool is_bf16) {
   return (1u << 4) | ((is_bf16 ? 1u : 0u) << 7) | ((is_bf16 ? 1u : 0u) << 10) |

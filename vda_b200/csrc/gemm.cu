@@ -33,7 +33,11 @@ struct GemmCfg {
   static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
   static constexpr int kTmemCols = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
   static constexpr int kBiasBytes = 2 * 2 * BN * 4;  // {bias, scale} x 2 tile parities
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kBiasBytes;
+  // halo mode (3x3 convs, BN <= 64) re-partitions the same buffer into stages of {patch, 9 W tiles}
+  static constexpr int kHaloStageBytes = 23 * 1024 + 9 * BN * kBlockK * 2;
+  static constexpr int kHaloStages = BN <= 32 ? 3 : (BN <= 64 ? 2 : 0);
+  static constexpr int kRingBytes = (kStages * kStageBytes > kHaloStages * kHaloStageBytes) ? kStages * kStageBytes : kHaloStages * kHaloStageBytes;
+  static constexpr int kSmemBytes = kRingBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kBiasBytes;
 };
 
 template <int BN>
@@ -46,6 +50,11 @@ struct Gemm2Cfg {
   static constexpr int kBiasBytes = 2 * 2 * BN * 4;
   static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kBiasBytes;
 };
+
+// halo mode of the 1-CTA kernel: patch of an 8 x 16-pixel tile plus a 1-pixel border, one 64-channel block
+constexpr int kHaloW = 10, kHaloH = 18;
+constexpr int kHaloBytes = kHaloW * kHaloH * 128;                  // 23,040 B written by one TMA box
+constexpr int kHaloSlotBytes = (kHaloBytes + 1023) / 1024 * 1024;  // keeps the W tiles behind it 1024-aligned
 
 struct TileCoord {
   int img, h0, w0;
@@ -67,12 +76,14 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   using Cfg = GemmCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kRingBytes);
   uint64_t* empty_bar = full_bar + Cfg::kStages;
   uint64_t* tfull_bar = empty_bar + Cfg::kStages;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
-  float* s_epi = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 256);
+  float* s_epi = reinterpret_cast<float*>(smem + Cfg::kRingBytes + 256);
+  // bytes of the operand ring this launch uses; the epilogue's boxes / residual ring live behind it
+  const int ring_used = p.stages * (p.halo ? Cfg::kHaloStageBytes : Cfg::kStageBytes);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -112,6 +123,67 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  // ---- halo mode (3x3 convs with few output channels).  Fetching every (tap, channel block) A tile
+  // separately pulls each input pixel through L2 nine times; with BN <= 64 there is too little math
+  // per byte to hide that (Cout = 32 tail: 2.5 ms at ~8 TB/s of L2 traffic).  Here a stage holds the
+  // 10 x 18-pixel halo patch of one channel block (ONE TMA box, 23 KB instead of 9 x 16 KB) plus the W
+  // tiles of its 9 taps, and the taps are nine tap-shifted UMMA descriptors into the patch: row 8g+i of
+  // the A operand is pixel (y=g, x=i) of the 8 x 16 tile, i.e. patch row (g+dy)*10 + i+dx -> start
+  // address + (dy*10+dx)*128, group pitch 1280 B.  36 MMAs are issued per barrier wait.
+  if (p.halo && warp == 0) {
+    const int cblocks = p.C / kBlockK;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = tile_begin; tile < tile_end; tile += tile_step) {
+      const int m_t = tile / p.n_tiles, n_t = tile - m_t * p.n_tiles;
+      const TileCoord tc = conv_tile_coord(p, m_t);
+      for (int cb = 0; cb < cblocks; ++cb) {
+        mbar_wait(&empty_bar[stage], phase ^ 1);
+        uint8_t* st = smem + stage * Cfg::kHaloStageBytes;
+        if (elect_one()) {
+          mbar_expect_tx(&full_bar[stage], kHaloBytes + 9 * Cfg::kBBytes);
+          tma_load_4d(st, &p.tmH, &full_bar[stage], cb * kBlockK, tc.w0 - 1, tc.h0 - 1, tc.img);
+#pragma unroll
+          for (int tap = 0; tap < 9; ++tap)
+            tma_load_2d(st + kHaloSlotBytes + tap * Cfg::kBBytes, &p.tmB, &full_bar[stage], (tap * cblocks + cb) * kBlockK, n_t * BN);
+        }
+        __syncwarp();
+        if (++stage == p.stages) stage = 0, phase ^= 1;
+      }
+    }
+  } else if (p.halo && warp == 1) {
+    constexpr uint32_t idesc = umma_idesc_f16(kBlockM, BN, true);
+    const int cblocks = p.C / kBlockK;
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
+      const int as = it & 1;
+      const uint32_t aphase = (it >> 1) & 1;
+      mbar_wait(&tempty_bar[as], aphase ^ 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BN;
+      for (int cb = 0; cb < cblocks; ++cb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t patch = smem_u32(smem + stage * Cfg::kHaloStageBytes);
+        if (elect_one()) {
+#pragma unroll
+          for (int tap = 0; tap < 9; ++tap) {
+            const int dy = tap / 3, dx = tap - dy * 3;
+            const uint64_t adesc = umma_desc_k_sw128_sbo(patch + (dy * kHaloW + dx) * 128, kHaloW * 128);
+            const uint64_t bdesc = umma_desc_k_sw128(patch + kHaloSlotBytes + tap * Cfg::kBBytes);
+#pragma unroll
+            for (int k = 0; k < kBlockK / 16; ++k) umma_f16_ss(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (cb | tap | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (cb == cblocks - 1) umma_commit(&tfull_bar[as]);
+        }
+        __syncwarp();
+        if (++stage == p.stages) stage = 0, phase ^= 1;
+      }
+    }
+  } else
   // The producer and MMA loops are executed by their WHOLE warp (all addresses and descriptors stay
   // warp-uniform, i.e. in uniform registers) and only the issuing instructions are predicated on one
   // elected lane.  Running the loops under `if (lane == 0)` made ptxas wrap every tcgen05.mma in an
@@ -184,10 +256,9 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     const int r = quad * 32 + lane;
     const int et = threadIdx.x - 128;
     const TileSched ts = {tile_begin, tile_step, tile_end, 1, 0};
-    ResRing rr = make_res_ring<BN>(p, ts, smem + p.stages * Cfg::kStageBytes, (Cfg::kStages - p.stages) * Cfg::kStageBytes, et,
-                                   r, half);
+    ResRing rr = make_res_ring<BN>(p, ts, smem + ring_used, Cfg::kRingBytes - ring_used, et, r, half);
     // TMA reduce-add epilogue: 3 boxes per column slice in the freed stages; thread 0 of each slice issues
-    const uint32_t red_base = smem_u32(smem + p.stages * Cfg::kStageBytes) + static_cast<uint32_t>(half) * kRedBoxes * kRedBoxBytes;
+    const uint32_t red_base = smem_u32(smem + ring_used) + static_cast<uint32_t>(half) * kRedBoxes * kRedBoxBytes;
     const bool red_issuer = (et & 127) == 0;
     int box_ctr = 0;
     int it = 0;

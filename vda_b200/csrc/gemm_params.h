@@ -19,6 +19,8 @@ enum : int { ACT_NONE = 0, ACT_GELU = 1, ACT_RELU = 2, ACT_GEGLU = 3 };
 
 struct alignas(64) GemmParams {
   CUtensorMap tmA;  // 2D [M,K] or 4D [N,H,W,C] bf16, box 64 x 128 rows, SWIZZLE_128B
+  CUtensorMap tmH;  // halo mode: 4D NHWC view of x, box 64c x 10 x 18 x 1 (tile 8x16 pixels + 1-pixel halo)
+  int halo;         // A_CONV3X3 only: one halo patch per channel block, 9 tap-shifted descriptors (gemm.cu)
   CUtensorMap tmB;  // 2D [N,K] bf16, box 64 x BLOCK_N
   CUtensorMap tmD;  // epi_tma: 2D [N,M] f32 view of out_f32, box 16 x 128 rows, SWIZZLE_64B
   int epi_tma;      // 1 = in-place fp32 residual update done as TMA reduce-add (gemm_epilogue.cuh)

@@ -97,6 +97,7 @@ def _declare(lib):
         "vda_temporal_attn": [vp, i, vp, i, vp, i, vp, i, i, i, i, i, i, vp],
         "vda_temporal_attn_stream": [vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, vp],
         "vda_preprocess_u8": [vp, i, i, i, vp, i, i, vp],
+        "vda_debug_umma_shift": [vp, vp, vp, i, i, i, vp],
         "vda_depth_tail": [vp, i, vp, vp, vp, f, vp, i, i, i, i, i, i, vp],
         "vda_attn_f32": [vp, i, vp, i, i, i, i, i, vp],
         "vda_temporal_attn_f32": [vp, vp, vp, i, vp, i, i, i, i, i, i, i, vp],
