@@ -132,6 +132,12 @@ int vda_temporal_attn_stream(const void* q, const void* knew, const void* vnew, 
 int vda_depth_tail(const void* x, int ldx, const void* w3, const float* b3, const float* w1, float b1, float* out,
                    int n, int h, int w, int H, int W, int C, void* stream);
 
+/* Depth visualisation (utils/dc_utils.py:72-86): minmax2 = {min, max} of max(x, 0) as two fp32 words;
+ * colorize: q = uint8((d - min) / (max - min) * 255), out = lut_rgb[q] (3 bytes per pixel) or q if grey. */
+int vda_minmax_f32(const float* x, long long n, void* minmax2, void* stream);
+int vda_depth_colorize(const float* depth, long long n, const void* minmax2, const void* lut_rgb, void* out, int grey,
+                       void* stream);
+
 /* Debug probe (tests only): D f32 [128,32] = A[128,64] * W[32,64]^T where A's row 8g+i is row
  * g*(sbo/128) + row0 + i of the bf16 source G [320,64], read through a tap-shifted tcgen05 descriptor. */
 int vda_debug_umma_shift(const void* G, const void* W, float* D, int row0, int sbo, int base_offset, void* stream);

@@ -260,3 +260,18 @@ def test_depth_tail_fused(L, n, h, w, H, W, C):
     scale = want.abs().max().item()
     assert (out - ref2).abs().max().item() < 2e-3 * scale      # same operands, different summation order
     assert (out - want).abs().max().item() < 2e-2 * scale      # torch rounds the upsample differently in the last bf16 bit
+
+
+def test_depth_colorize_matches_numpy(L):
+    """dc_utils.py:72-86 semantics: global min/max, truncating uint8 cast, LUT."""
+    from utils.dc_utils import depth_to_vis, inferno_lut
+
+    rng = np.random.default_rng(0)
+    d = rng.uniform(0.2, 7.5, (3, 37, 53)).astype(np.float32)
+    lo, hi = d.min(), d.max()
+    q = ((d - lo) / (hi - lo) * 255).astype(np.uint8)
+    got_grey = depth_to_vis(d, grayscale=True)
+    assert got_grey.shape == q.shape and np.abs(got_grey.astype(int) - q.astype(int)).max() <= 1
+    assert (got_grey == q).mean() > 0.999
+    got = depth_to_vis(d)
+    assert got.shape == d.shape + (3,) and np.array_equal(got, inferno_lut()[got_grey])

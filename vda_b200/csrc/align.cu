@@ -121,3 +121,63 @@ int vda_affine_clamp_blend(float* pre, const float* post, long long per_frame, i
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Depth visualisation (utils/dc_utils.py:72-86: global min/max over the whole clip, 8-bit
+// quantisation, "inferno" look-up or grey).  Two bandwidth kernels: a min/max reduction (depth >= 0,
+// so the IEEE bit patterns order like unsigned integers) and the per-pixel LUT.
+namespace vda {
+
+__global__ void minmax_init_kernel(unsigned int* mm) { mm[0] = 0x7f800000u, mm[1] = 0u; }  // +inf, 0
+
+__global__ void minmax_f32_kernel(const float* __restrict__ x, long long n, unsigned int* __restrict__ mm) {
+  float lo = INFINITY, hi = 0.f;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float v = fmaxf(x[i], 0.f);
+    lo = fminf(lo, v), hi = fmaxf(hi, v);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMin(mm, __float_as_uint(lo));
+    atomicMax(mm + 1, __float_as_uint(hi));
+  }
+}
+
+// out[i] = lut[q] (3 bytes) or q (grey), q = uint8((d - min) / (max - min) * 255) with numpy's truncating cast
+__global__ void depth_colorize_kernel(const float* __restrict__ d, long long n, const unsigned int* __restrict__ mm,
+                                      const uint8_t* __restrict__ lut, uint8_t* __restrict__ out, int grey) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float lo = __uint_as_float(mm[0]), hi = __uint_as_float(mm[1]);
+  const float q = (d[i] - lo) / (hi - lo) * 255.f;
+  const int k = min(max(static_cast<int>(q), 0), 255);
+  if (grey) {
+    out[i] = static_cast<uint8_t>(k);
+  } else {
+    out[3 * i] = lut[3 * k], out[3 * i + 1] = lut[3 * k + 1], out[3 * i + 2] = lut[3 * k + 2];
+  }
+}
+
+}  // namespace vda
+
+extern "C" int vda_minmax_f32(const float* x, long long n, void* minmax2, void* stream) {
+  if (!x || !minmax2 || n <= 0) return set_error(-1, "vda_minmax_f32: bad arguments");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  vda::minmax_init_kernel<<<1, 1, 0, st>>>(static_cast<unsigned int*>(minmax2));
+  const int blocks = static_cast<int>(n / 1024 < 1184 ? (n + 1023) / 1024 : 1184);
+  vda::minmax_f32_kernel<<<blocks, 256, 0, st>>>(x, n, static_cast<unsigned int*>(minmax2));
+  return vda::check_cuda(cudaGetLastError(), "minmax launch");
+}
+
+extern "C" int vda_depth_colorize(const float* depth, long long n, const void* minmax2, const void* lut_rgb, void* out,
+                                  int grey, void* stream) {
+  if (!depth || !minmax2 || !out || n <= 0 || (!grey && !lut_rgb)) return set_error(-1, "vda_depth_colorize: bad arguments");
+  vda::depth_colorize_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      depth, n, static_cast<const unsigned int*>(minmax2), static_cast<const uint8_t*>(lut_rgb), static_cast<uint8_t*>(out), grey);
+  return vda::check_cuda(cudaGetLastError(), "depth_colorize launch");
+}

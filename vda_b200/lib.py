@@ -97,6 +97,8 @@ def _declare(lib):
         "vda_temporal_attn": [vp, i, vp, i, vp, i, vp, i, i, i, i, i, i, vp],
         "vda_temporal_attn_stream": [vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, vp],
         "vda_preprocess_u8": [vp, i, i, i, vp, i, i, vp],
+        "vda_minmax_f32": [vp, C.c_longlong, vp, vp],
+        "vda_depth_colorize": [vp, C.c_longlong, vp, vp, vp, i, vp],
         "vda_debug_umma_shift": [vp, vp, vp, i, i, i, vp],
         "vda_depth_tail": [vp, i, vp, vp, vp, f, vp, i, i, i, i, i, i, vp],
         "vda_attn_f32": [vp, i, vp, i, i, i, i, i, vp],
@@ -190,6 +192,16 @@ def depth_tail(x, w3, b3, w1, b1, out, n, h, w, H, W, C, ldx=None):
         check(load().vda_depth_tail(ptr(x), C if ldx is None else ldx, ptr(w3), ptr(b3), ptr(w1), b1, ptr(out), n, h, w, H, W,
                                     C, stream_ptr()))
     _launched()
+
+
+def depth_colorize(depth, lut_rgb=None, grey=False):
+    """depth f32 [...] on the GPU -> uint8 [..., 3] (or [...] if grey) with the clip-global min/max."""
+    mm = torch.empty(2, dtype=torch.float32, device=depth.device)
+    check(load().vda_minmax_f32(ptr(depth), depth.numel(), ptr(mm), stream_ptr()))
+    out = torch.empty(tuple(depth.shape) + (() if grey else (3,)), dtype=torch.uint8, device=depth.device)
+    check(load().vda_depth_colorize(ptr(depth), depth.numel(), ptr(mm), ptr(lut_rgb), ptr(out), int(grey), stream_ptr()))
+    _launched(3)
+    return out
 
 
 def preprocess_u8(frames_u8, out, nh, nw):
