@@ -23,7 +23,7 @@ def test_read_video_frames_stride_length_and_max_res(tmp_path):
     w.release()
     frames, fps = read_video_frames(path, -1, -1, -1)
     assert frames.shape == (12, 48, 64, 3) and frames.dtype == np.uint8 and fps == 24.0
-    assert abs(int(frames[5].mean()) - 100) <= 3
+    assert abs(int(frames[5].mean()) - 100) <= 8  # mp4v is lossy
     frames, fps = read_video_frames(path, 6, 12, 32)       # first 6 source frames, every 2nd, longest side 32
     assert frames.shape == (3, 24, 32, 3) and fps == 12
     lut = inferno_lut()
