@@ -38,6 +38,7 @@ _inited = set()
 # when PROFILE is a list, every tensor-core launch appends (kind, flops, start_event, end_event).
 LAUNCHES = 0
 PROFILE = None
+NOTES = None   # optional list filled alongside PROFILE with a shape string per launch (scripts/prof_launches.py)
 
 
 def _launched(n=1):
@@ -48,8 +49,8 @@ def _launched(n=1):
 class _timed:
     """Brackets one launch with CUDA events on the current stream when profiling is on."""
 
-    def __init__(self, kind, flops):
-        self.kind, self.flops = kind, flops
+    def __init__(self, kind, flops, note=""):
+        self.kind, self.flops, self.note = kind, flops, note
 
     def __enter__(self):
         if PROFILE is not None:
@@ -61,6 +62,8 @@ class _timed:
         if PROFILE is not None:
             self.e1.record()
             PROFILE.append((self.kind, self.flops, self.e0, self.e1))
+            if NOTES is not None:
+                NOTES.append(self.note)
 
 
 def load():
@@ -169,14 +172,16 @@ def gemm(a, w, epi, M=None, N=None, K=None, lda=None, ldw=None):
     N = w.shape[0] if N is None else N
     lda = a.stride(0) if lda is None else lda
     ldw = w.stride(0) if ldw is None else ldw
-    with _timed("gemm", 2.0 * M * N * K):
+    with _timed("gemm", 2.0 * M * N * K, f"gemm M={M} N={N} K={K} act={epi.act} st={epi.store_mode} r32={int(bool(epi.res_f32))} "
+                                          f"o={int(bool(epi.out))} of={int(bool(epi.out_f32))} r1={int(bool(epi.res1))}"):
         check(load().vda_gemm_bf16(ptr(a), lda, ptr(w), ldw, M, N, K, C.byref(epi), stream_ptr()))
     _launched()
 
 
 def conv3x3(x, w, epi, n, H, W, Cin, Cout, ldx=None):
     ldx = Cin if ldx is None else ldx
-    with _timed("conv3x3", 2.0 * n * H * W * Cout * 9 * Cin):
+    with _timed("conv3x3", 2.0 * n * H * W * Cout * 9 * Cin, f"conv n={n} {H}x{W} {Cin}->{Cout} act={epi.act} r1={int(bool(epi.res1))} "
+                                                             f"r2={int(bool(epi.res2))} orelu={int(bool(epi.out_relu))}"):
         check(load().vda_conv3x3_nhwc(ptr(x), ldx, ptr(w), n, H, W, Cin, Cout, C.byref(epi), stream_ptr()))
     _launched()
 
