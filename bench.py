@@ -252,6 +252,8 @@ def run_ours(a):
         k[1] += flops
         k[2] += s.elapsed_time(e)
     tf_peak, hbm_peak, peak_src = peaks()
+    hbm = {k[4:]: v for k, v in kinds.items() if k.startswith("hbm:")}
+    kinds = {k: v for k, v in kinds.items() if not k.startswith("hbm:")}
     n_g, f_g, t_g = kinds.get("gemm", [1, 0.0, 1e-9])
     achieved = f_g / (t_g * 1e-3) / 1e12
     total_frames = T * a.steps * world
@@ -276,6 +278,9 @@ def run_ours(a):
                      "flops_per_launch": f_g / n_g, "ms_per_launch": t_g / n_g},
         "breakdown_ms_per_step": {k: v[2] / a.steps for k, v in kinds.items()},
         "breakdown_tflops": {k: v[1] / (v[2] * 1e-3) / 1e12 for k, v in kinds.items() if v[2] > 0},
+        # bandwidth-bound kernels: algorithmic bytes / event time, against the measured HBM peak
+        "hbm_kernels": {k: {"ms_per_step": v[2] / a.steps, "GBps": v[1] / (v[2] * 1e-3) / 1e9,
+                            "frac_of_hbm_peak": v[1] / (v[2] * 1e-3) / 1e9 / hbm_peak} for k, v in hbm.items() if v[2] > 0},
     }
     if world == 1 and not a.no_cpu_baseline:
         line["cpu_baseline"], _ = cpu_arm(a, 1, 1)

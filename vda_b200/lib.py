@@ -233,15 +233,19 @@ def layernorm(x, gamma, beta, out, eps, rows=None, C=None, tokens_per_frame=0, s
               pe_rows_per_t=0, pe_T=0, split=0):
     rows = x.shape[0] if rows is None else rows
     C = x.shape[-1] if C is None else C
-    check(load().vda_layernorm(ptr(x), int(x.dtype == torch.float32), ptr(gamma), ptr(beta), ptr(out), ptr(out_nope),
-                               ptr(pe), rows, C, eps, tokens_per_frame, skip, pe_rows_per_t, pe_T, split, stream_ptr()))
+    nbytes = rows * C * (x.element_size() + 2 * (3 if split else 1) * (2 if out_nope is not None else 1))
+    with _timed("hbm:layernorm", nbytes, f"layernorm rows={rows} C={C}"):   # for hbm:* kinds `flops` holds algorithmic bytes
+        check(load().vda_layernorm(ptr(x), int(x.dtype == torch.float32), ptr(gamma), ptr(beta), ptr(out), ptr(out_nope),
+                                   ptr(pe), rows, C, eps, tokens_per_frame, skip, pe_rows_per_t, pe_T, split, stream_ptr()))
     _launched(1)
 
 
 def groupnorm_nhwc(x, gamma, beta, out, stats_ws, n, hw, C, eps, ldx=None, split=0):
-    check(load().vda_groupnorm_nhwc(ptr(x), C if ldx is None else ldx, ptr(gamma), ptr(beta), ptr(out), ptr(stats_ws),
-                                    n, hw, C, eps, split, stream_ptr()))
-    _launched(2)
+    parts = 3 if split else 1
+    with _timed("hbm:groupnorm", n * hw * C * 2 * (2 * (2 if split else 1) + parts), f"groupnorm n={n} hw={hw} C={C}"):
+        check(load().vda_groupnorm_nhwc(ptr(x), C if ldx is None else ldx, ptr(gamma), ptr(beta), ptr(out), ptr(stats_ws),
+                                        n, hw, C, eps, split, stream_ptr()))
+    _launched(3)
 
 
 def patch_im2col(x, a, frames, H, W, ldk, split=0):
@@ -255,8 +259,10 @@ def add_cls_pos(patch, cls, pos, tokens, frames, hw, D):
 
 
 def bilinear_nhwc(x, out, n, h, w, H, W, C, ldx=None, ldo=None, split_in=0, split_out=0):
-    check(load().vda_bilinear_nhwc(ptr(x), C if ldx is None else ldx, ptr(out), C if ldo is None else ldo,
-                                   n, h, w, H, W, C, split_in, split_out, stream_ptr()))
+    parts = 3 if split_out else 1
+    with _timed("hbm:bilinear", n * C * 2 * (h * w * (2 if split_in else 1) + H * W * parts), f"bilinear n={n} {h}x{w}->{H}x{W} C={C}"):
+        check(load().vda_bilinear_nhwc(ptr(x), C if ldx is None else ldx, ptr(out), C if ldo is None else ldo,
+                                       n, h, w, H, W, C, split_in, split_out, stream_ptr()))
     _launched(1)
 
 
@@ -271,8 +277,10 @@ def im2col_s2(x, a, n, h, w, C):
 
 
 def temporal_attn(q, ldq, k, ldk, v, ldv, out, ldo, hw, heads, head_dim, Tq, Tk):
-    check(load().vda_temporal_attn(ptr(q), ldq, ptr(k), ldk, ptr(v), ldv, ptr(out), ldo, hw, heads, head_dim, Tq, Tk,
-                                   stream_ptr()))
+    C_ = heads * head_dim
+    with _timed("hbm:temporal_attn", hw * C_ * 2 * (2 * Tq + 2 * Tk), f"temporal_attn hw={hw} C={C_} T={Tk}"):
+        check(load().vda_temporal_attn(ptr(q), ldq, ptr(k), ldk, ptr(v), ldv, ptr(out), ldo, hw, heads, head_dim, Tq, Tk,
+                                       stream_ptr()))
     _launched(1)
 
 
