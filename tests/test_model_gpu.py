@@ -155,3 +155,20 @@ def test_forward_pipelined_matches_forward():
     assert len(got) == 5
     for g, w_ in zip(got, want):
         assert g.is_pinned() and torch.equal(g, w_)
+
+
+@pytest.mark.parametrize("n_frames", [1, 5, 22, 23, 33, 55])
+def test_video_driver_ragged_lengths_vs_oracle(n_frames):
+    """Edge cases of the window composition (video_depth.py:92-118): a single frame, clips shorter than one
+    window (padded by repeating the last frame), exactly one stride, one frame into the next window, ..."""
+    v = G.VIDEO_CASE
+    frames = G.video_frames(n_frames, v["h"], v["w"], seed=n_frames)
+    model, sd = build(v["arch"])
+    got, _ = model.infer_video_depth(frames, 24, input_size=v["input_size"], device="cuda")
+    sd_gpu = {k: t.cuda() for k, t in sd.items()}
+    with torch.no_grad():
+        want = O.infer_video_depth(sd_gpu, frames, input_size=v["input_size"], arch=v["arch"], device="cuda")
+    assert got.shape == want.shape == (n_frames, v["h"], v["w"])
+    e = absrel(got, want)
+    print(f"driver n={n_frames}: absrel {e:.2e}")
+    assert e <= ABSREL_TOL
