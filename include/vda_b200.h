@@ -141,6 +141,8 @@ int vda_depth_colorize(const float* depth, long long n, const void* minmax2, con
 /* Debug probe (tests only): D f32 [128,32] = A[128,64] * W[32,64]^T where A's row 8g+i is row
  * g*(sbo/128) + row0 + i of the bf16 source G [320,64], read through a tap-shifted tcgen05 descriptor. */
 int vda_debug_umma_shift(const void* G, const void* W, float* D, int row0, int sbo, int base_offset, void* stream);
+/* Debug probe: `ctas` x `threads` threads each issue iters*8 mma.sync.m16n8k16 bf16 (no memory traffic). */
+int vda_debug_mma_rate(float* out, int ctas, int threads, int iters, void* stream);
 
 /* Frame pre-processing (util/transform.py:51-157 via video_depth.py:77-89): frames uint8 RGB [n,H0,W0,3]
  * -> out f32 [n,3,nh,nw] = ((cv2-compatible INTER_CUBIC resize of frame/255) - mean) / std. */
@@ -148,9 +150,12 @@ int vda_preprocess_u8(const void* frames, int n, int H0, int W0, float* out, int
 
 /* FP32-accuracy mode attention (fp32=True of infer_video_depth, video_depth.py:108).  Inputs are the
  * fp32 q/k/v written by the projection GEMM, outputs are split tensors (vda_epilogue::split).
- * vda_attn_f32: qkv f32 [frames*S, ld >= 3*heads*64] laid out q | k | v (dinov2_layers/attention.py:51-59);
+ * vda_attn_f32: q | k | v (dinov2_layers/attention.py:51-59) either as f32 [frames*S, ld >= 3*heads*64]
+ * (in_split = 0) or as a split bf16 tensor [frames*S, ld] with hi at column c and lo at c + in_split
+ * (in_split >= 3*heads*64; the fast path: the projection GEMM writes it with vda_epilogue::split);
  * out [frames*S, ldo] with parts `split` apart.  vda_temporal_attn_f32: as vda_temporal_attn. */
-int vda_attn_f32(const float* qkv, int ld, void* out, int ldo, int split, int frames, int S, int heads, void* stream);
+int vda_attn_f32(const void* qkv, int ld, int in_split, void* out, int ldo, int split, int frames, int S, int heads,
+                 void* stream);
 int vda_temporal_attn_f32(const float* q, const float* k, const float* v, int ld, void* out, int ldo, int split, int hw,
                           int heads, int head_dim, int Tq, int Tk, void* stream);
 

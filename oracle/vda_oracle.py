@@ -305,6 +305,13 @@ def infer_video_depth(sd, frames, input_size=518, metric=False, arch=None, devic
     return np.stack(align_windows(depth_list, metric)[:n], axis=0)
 
 
+def upscale_to_original(depth, original_height, original_width):
+    """external_engine/video_depth_anything/video_depth.py:181-203: per-frame bilinear (align_corners=True)
+    upscale of the aligned maps [N,H0,W0] to the caller's original plate size."""
+    t = torch.from_numpy(np.ascontiguousarray(depth)).unsqueeze(1).float()
+    return F.interpolate(t, size=(original_height, original_width), mode="bilinear", align_corners=True)[:, 0].numpy()
+
+
 class StreamOracle:
     """video_depth_stream.py:77-161 (fp32): one frame in, one depth map out, 8-tensor cache per frame."""
 

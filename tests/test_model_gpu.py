@@ -172,3 +172,23 @@ def test_video_driver_ragged_lengths_vs_oracle(n_frames):
     e = absrel(got, want)
     print(f"driver n={n_frames}: absrel {e:.2e}")
     assert e <= ABSREL_TOL
+
+
+def test_video_driver_original_size_upscale_vs_oracle():
+    """original_width / original_height of the fork's engine copy (external_engine/video_depth_anything/
+    video_depth.py:81-90, :181-203): aligned maps are upscaled bilinearly (align_corners=True) on the GPU."""
+    v = G.VIDEO_CASE
+    frames = G.video_frames(9, v["h"], v["w"], seed=3)
+    model, sd = build(v["arch"])
+    oh, ow = 2 * v["h"] + 3, 3 * v["w"] - 1
+    base, _ = model.infer_video_depth(frames, 24, input_size=v["input_size"], device="cuda")
+    got, fps = model.infer_video_depth(frames, 24, input_size=v["input_size"], device="cuda", original_width=ow,
+                                       original_height=oh)
+    assert fps == 24 and got.shape == (9, oh, ow)
+    want = O.upscale_to_original(base, oh, ow)
+    err = np.abs(got - want).max() / np.abs(want).max()
+    print(f"original-size upscale: max rel err {err:.2e}")
+    assert err <= 2e-6
+    # only one of the two given: ignored, like the reference
+    same, _ = model.infer_video_depth(frames, 24, input_size=v["input_size"], device="cuda", original_width=ow)
+    assert same.shape == base.shape

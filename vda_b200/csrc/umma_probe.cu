@@ -68,9 +68,36 @@ __global__ void __launch_bounds__(128) umma_probe_kernel(const __grid_constant__
   }
 }
 
+// Issue-rate probe of the legacy warp-level tensor path: every warp runs `iters` rounds of 8 independent
+// mma.sync.m16n8k16 bf16 chains (no memory traffic).  Sets the ceiling for the split-bf16 attention kernels.
+__global__ void __launch_bounds__(512) mma_rate_kernel(float* out, int iters) {
+  float c[8][4];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) c[i][0] = c[i][1] = c[i][2] = c[i][3] = 0.f;
+  uint32_t a[4] = {threadIdx.x, threadIdx.x * 3u, threadIdx.x * 5u, threadIdx.x * 7u};
+  uint32_t b0 = threadIdx.x * 11u, b1 = threadIdx.x * 13u;
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                   : "+f"(c[i][0]), "+f"(c[i][1]), "+f"(c[i][2]), "+f"(c[i][3])
+                   : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  }
+  float acc = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc += c[i][0] + c[i][1] + c[i][2] + c[i][3];
+  if (acc == 123.456f) out[0] = acc;
+}
+
 }  // namespace vda
 
 using namespace vda;
+
+extern "C" int vda_debug_mma_rate(float* out, int ctas, int threads, int iters, void* stream) {
+  if (!out || ctas <= 0 || threads <= 0 || threads > 512 || threads % 32) return set_error(-1, "vda_debug_mma_rate: bad arguments");
+  mma_rate_kernel<<<ctas, threads, 0, static_cast<cudaStream_t>(stream)>>>(out, iters);
+  return check_cuda(cudaGetLastError(), "mma rate launch");
+}
 
 extern "C" int vda_debug_umma_shift(const void* G, const void* W, float* D, int row0, int sbo, int base_offset, void* stream) {
   if (!G || !W || !D || row0 < 0 || sbo % 16) return set_error(-1, "vda_debug_umma_shift: bad arguments");

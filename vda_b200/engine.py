@@ -195,7 +195,7 @@ class Engine:
         ao = ws.get("attn_out", (M, D * Wd))
         h1 = ws.get("mlp_h", (M, 4 * D * Wd))
         if sp:
-            qkv32 = ws.get("qkv_f32", (M, 3 * D), torch.float32)
+            qkvs = ws.get("qkv_split", (M, 9 * D))   # q | k | v as [hi | lo | hi], parts 3D apart
         else:
             qk = ws.get("qk", (M, 2 * D))
             vt = ws.get("vt", (T * heads, 64, spad), zero=True)
@@ -203,8 +203,8 @@ class Engine:
         for i, b in enumerate(w.blocks):
             L.layernorm(tok, b["n1w"], b["n1b"], xn, 1e-6, C=D, split=int(sp))
             if sp:
-                L.gemm(xn, b["wqkv"], L.make_epilogue(bias=b["bqkv"], out_f32=qkv32, ldo=3 * D))
-                L.attn_f32(qkv32, ao, D, T, S, heads)
+                L.gemm(xn, b["wqkv"], self._ep(3 * D, bias=b["bqkv"], out=qkvs))
+                L.attn_f32(qkvs, ao, D, T, S, heads, in_split=3 * D)
             else:
                 L.gemm(xn, b["wqkv"], L.make_epilogue(bias=b["bqkv"], out=qk, ldo=2 * D, store_mode=L.ST_QKV,
                                                       qkv=(vt, D, heads, S, spad)))

@@ -103,8 +103,9 @@ def _declare(lib):
         "vda_minmax_f32": [vp, C.c_longlong, vp, vp],
         "vda_depth_colorize": [vp, C.c_longlong, vp, vp, vp, i, vp],
         "vda_debug_umma_shift": [vp, vp, vp, i, i, i, vp],
+        "vda_debug_mma_rate": [vp, i, i, i, vp],
         "vda_depth_tail": [vp, i, vp, vp, vp, f, vp, i, i, i, i, i, i, vp],
-        "vda_attn_f32": [vp, i, vp, i, i, i, i, i, vp],
+        "vda_attn_f32": [vp, i, i, vp, i, i, i, i, i, vp],
         "vda_temporal_attn_f32": [vp, vp, vp, i, vp, i, i, i, i, i, i, i, vp],
         "vda_lsq_accum": [vp, vp, C.c_longlong, vp, vp],
         "vda_lsq_solve": [vp, vp, i, vp],
@@ -216,9 +217,11 @@ def preprocess_u8(frames_u8, out, nh, nw):
     _launched()
 
 
-def attn_f32(qkv, out, split, frames, S, heads):
+def attn_f32(qkv, out, split, frames, S, heads, in_split=0):
+    """qkv: f32 [frames*S, 3D] (in_split=0) or split bf16 [frames*S, 3*in_split] (hi | lo | hi); out split bf16."""
     with _timed("attn", 4.0 * frames * heads * S * S * 64):
-        check(load().vda_attn_f32(ptr(qkv), qkv.shape[1], ptr(out), out.shape[1], split, frames, S, heads, stream_ptr()))
+        check(load().vda_attn_f32(ptr(qkv), qkv.shape[1], in_split, ptr(out), out.shape[1], split, frames, S, heads,
+                                  stream_ptr()))
     _launched()
 
 

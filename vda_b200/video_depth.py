@@ -169,12 +169,22 @@ class VideoDepthAnything(nn.Module):
 
     # ------------------------------------------------------------------ offline driver
     @torch.no_grad()
-    def infer_video_depth(self, frames, target_fps, input_size=518, device="cuda", fp32=False):
+    def infer_video_depth(self, frames, target_fps, input_size=518, device="cuda", fp32=False, original_width=None,
+                          original_height=None):
         """frames uint8 [N,H0,W0,3] RGB -> (float32 [N,H0,W0], target_fps).
 
         fp32=False: BF16 tensor-core path (the reference's autocast branch, video_depth.py:108).
-        fp32=True: FP32-accuracy path (rtol 1e-3 against the reference's fp32 forward)."""
+        fp32=True: FP32-accuracy path (rtol 1e-3 against the reference's fp32 forward).
+        original_width / original_height (both given): the aligned maps are upscaled bilinearly
+        (align_corners=True) to that size before they leave the GPU -- the kwargs of the fork's engine copy,
+        external_engine/video_depth_anything/video_depth.py:81-90, :181-203."""
         depth = self.infer_video_depth_device(frames, input_size=input_size, device=device, fp32=fp32)
+        if original_width is not None and original_height is not None:
+            up = torch.empty(depth.shape[0], int(original_height), int(original_width), dtype=torch.float32,
+                             device=depth.device)
+            with torch.cuda.device(depth.device):
+                L.bilinear_f32(depth.contiguous(), up, depth.shape[0], depth.shape[1], depth.shape[2], up.shape[1], up.shape[2])
+            depth = up
         host = torch.empty(depth.shape, dtype=torch.float32, pin_memory=True)
         host.copy_(depth, non_blocking=True)
         torch.cuda.current_stream(depth.device).synchronize()
