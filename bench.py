@@ -42,6 +42,9 @@ def parse():
     ap.add_argument("--size", type=int, default=518)
     ap.add_argument("--cpu-frames", type=int, default=2, help="frames of the CPU-baseline sample window")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--torch-eager-gpu", action="store_true",
+                    help="also time the oracle (plain torch ops, the reference's own op sequence) on this GPU: fp32 and "
+                         "autocast bf16 -- SURVEY.md 8(d)'s second comparand; reported, never the measured product")
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"],
                     help="fp32 = the FP32-accuracy mode (split-bf16 products, DESIGN.md 4b); not the headline config")
     return ap.parse_args()
@@ -78,6 +81,38 @@ def cpu_arm(a, steps, warmup):
     return {"value": T / dt, "unit": UNIT, "cores": cores, "kind": "port",
             "sample": f"oracle forward on a {T}-frame {a.size}x{a.size} {a.arch} window, fp32 torch CPU, "
                       f"{steps} timed pass(es) of {dt:.2f} s"}, dt
+
+
+def torch_eager_gpu_arm(a, steps=3, warmup=2):
+    """The oracle's op sequence (what the reference executes: F.linear / naive softmax attention / conv2d /
+    interpolate ...) as eager PyTorch on the same B200, full window, fp32 and autocast(bf16)."""
+    import torch
+
+    from oracle import refload
+    from oracle import vda_oracle as O
+
+    torch.set_grad_enabled(False)
+    sd = {k: v.cuda() for k, v in refload.seeded_state_dict(a.arch, 0).items()}
+    x = torch.randn(1, a.frames, 3, a.size, a.size, generator=torch.Generator().manual_seed(0)).cuda()
+    out = {}
+    for name, ctx in (("fp32", torch.autocast("cuda", enabled=False)),
+                      ("autocast_bf16", torch.autocast("cuda", dtype=torch.bfloat16)),
+                      ("autocast_fp16", torch.autocast("cuda", dtype=torch.float16))):
+        with ctx:
+            for _ in range(warmup):
+                O.forward(sd, x, a.arch)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(steps):
+                O.forward(sd, x, a.arch)
+            e1.record()
+            torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        out[name] = {"frames_per_s": a.frames / ms * 1e3, "ms_per_window": ms}
+    out["note"] = (f"oracle forward (eager torch {torch.__version__}, naive attention as attention.py:53-59, TF32 off), "
+                   f"{a.frames}-frame {a.size}x{a.size} {a.arch} window, {steps} timed passes")
+    return out
 
 
 def run_reference(a):
@@ -284,6 +319,10 @@ def run_ours(a):
     }
     if world == 1 and not a.no_cpu_baseline:
         line["cpu_baseline"], _ = cpu_arm(a, 1, 1)
+    if world == 1 and a.torch_eager_gpu:
+        del model
+        torch.cuda.empty_cache()
+        line["torch_eager_same_gpu"] = torch_eager_gpu_arm(a)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
