@@ -42,6 +42,48 @@ __device__ __forceinline__ float poly_exp2(float x) {
   return __int_as_float(__float_as_int(r) + (__float_as_int(fl) << 23));
 }
 
+// Packed fp32x2 arithmetic (FFMA2 / FADD2) and the 3-input max (FMNMX3) of sm_100: the softmax warps are
+// issue-slot bound next to the MUFU limit, and these halve the FMA-pipe instruction count per score.
+__device__ __forceinline__ uint64_t pack2(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+
+// poly_exp2 on a pair of scores with packed arithmetic (10 FMA-pipe instructions per pair).
+__device__ __forceinline__ void poly_exp2_x2(uint64_t x, float& p0, float& p1) {
+  float x0, x1;
+  unpack2(x, x0, x1);
+  x = pack2(fmaxf(x0, -126.0f), fmaxf(x1, -126.0f));
+  const uint64_t magic = pack2(12582912.0f, 12582912.0f), nmagic = pack2(-12582912.0f, -12582912.0f);
+  const uint64_t fl = fadd2(x, magic);
+  const uint64_t f = ffma2(fadd2(fl, nmagic), pack2(-1.0f, -1.0f), x);
+  uint64_t r = ffma2(pack2(0.05459282f, 0.05459282f), f, pack2(0.24221784f, 0.24221784f));
+  r = ffma2(r, f, pack2(0.6933686f, 0.6933686f));
+  r = ffma2(r, f, pack2(1.0f, 1.0f));
+  float r0, r1, f0, f1;
+  unpack2(r, r0, r1);
+  unpack2(fl, f0, f1);
+  p0 = __int_as_float(__float_as_int(r0) + (__float_as_int(f0) << 23));
+  p1 = __int_as_float(__float_as_int(r1) + (__float_as_int(f1) << 23));
+}
+
 constexpr int kAttThreads = 192;
 constexpr int kQBytes = 128 * 64 * 2;        // 16 KB
 constexpr int kKBytes = 128 * 64 * 2;        // 16 KB
@@ -270,7 +312,8 @@ constexpr float kRescaleThreshold = 8.0f;
 // POLY: one in POLY exponentials (0 = none, 2/4/8) is evaluated with poly_exp2 on the FMA pipe.
 // LATE: the wait for PV_{j-1} (needed before P is overwritten / O rescaled) is taken after the
 // exponentials of tile j instead of before them, so that MMA latency hides behind the MUFU work.
-template <int POLY, bool LATE>
+// PK: packed f32x2 scale / row-sum and 3-input max (helpers above).
+template <int POLY, bool LATE, bool PK = false>
 __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __grid_constant__ AttnParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   if ((smem_u32(smem) & 1023u) != 0) __trap();
@@ -415,12 +458,22 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
           if (c >= kv_left) s[c] = 0xff800000u;  // -inf
       }
       float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+      if (PK) {
 #pragma unroll
-      for (int c = 0; c < 128; c += 4) {
-        mx0 = fmaxf(mx0, __uint_as_float(s[c]));
-        mx1 = fmaxf(mx1, __uint_as_float(s[c + 1]));
-        mx2 = fmaxf(mx2, __uint_as_float(s[c + 2]));
-        mx3 = fmaxf(mx3, __uint_as_float(s[c + 3]));
+        for (int c = 0; c < 128; c += 8) {
+          mx0 = fmax3(mx0, __uint_as_float(s[c]), __uint_as_float(s[c + 1]));
+          mx1 = fmax3(mx1, __uint_as_float(s[c + 2]), __uint_as_float(s[c + 3]));
+          mx2 = fmax3(mx2, __uint_as_float(s[c + 4]), __uint_as_float(s[c + 5]));
+          mx3 = fmax3(mx3, __uint_as_float(s[c + 6]), __uint_as_float(s[c + 7]));
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 128; c += 4) {
+          mx0 = fmaxf(mx0, __uint_as_float(s[c]));
+          mx1 = fmaxf(mx1, __uint_as_float(s[c + 1]));
+          mx2 = fmaxf(mx2, __uint_as_float(s[c + 2]));
+          mx3 = fmaxf(mx3, __uint_as_float(s[c + 3]));
+        }
       }
       const float m_tile = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * sc;
       bool need = false;
@@ -453,18 +506,36 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
       }
       const float neg_m = -m_run;
       float l0 = 0.f, l1 = 0.f;
+      const uint64_t sc2 = pack2(sc, sc), nm2 = pack2(neg_m, neg_m);
+      uint64_t la = pack2(0.f, 0.f), lb = la;
       uint32_t pk[LATE ? 64 : 16];
 #pragma unroll
       for (int c0 = 0; c0 < 128; c0 += 32) {
         uint32_t* pc = LATE ? pk + (c0 >> 1) : pk;
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          const float x0 = fmaf(__uint_as_float(s[c0 + i]), sc, neg_m);
-          const float x1 = fmaf(__uint_as_float(s[c0 + i + 1]), sc, neg_m);
-          const float p0 = fast_exp2(x0);
-          const float p1 = (POLY > 0 && ((i >> 1) % (POLY / 2 > 0 ? POLY / 2 : 1)) == 0) ? poly_exp2(x1) : fast_exp2(x1);
-          l0 += p0;
-          l1 += p1;
+          float x0, x1, p0, p1;
+          if (PK) {
+            const uint64_t x2 = ffma2(pack2(__uint_as_float(s[c0 + i]), __uint_as_float(s[c0 + i + 1])), sc2, nm2);
+            if (POLY > 0 && ((i >> 1) % POLY) == 0) {   // one pair in POLY entirely on the FMA pipe
+              poly_exp2_x2(x2, p0, p1);
+            } else {
+              unpack2(x2, x0, x1);
+              p0 = fast_exp2(x0), p1 = fast_exp2(x1);
+            }
+          } else {
+            x0 = fmaf(__uint_as_float(s[c0 + i]), sc, neg_m);
+            x1 = fmaf(__uint_as_float(s[c0 + i + 1]), sc, neg_m);
+            p0 = fast_exp2(x0);
+            p1 = (POLY > 0 && ((i >> 1) % (POLY / 2 > 0 ? POLY / 2 : 1)) == 0) ? poly_exp2(x1) : fast_exp2(x1);
+          }
+          if (PK) {
+            if (i & 2) lb = fadd2(lb, pack2(p0, p1));
+            else la = fadd2(la, pack2(p0, p1));
+          } else {
+            l0 += p0;
+            l1 += p1;
+          }
           __nv_bfloat162 h = __floats2bfloat162_rn(p0, p1);
           pc[i >> 1] = *reinterpret_cast<uint32_t*>(&h);
         }
@@ -490,6 +561,7 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
         for (int c0 = 0; c0 < 128; c0 += 32)
           tmem_st16(tmem_P + lane_off + (c0 >> 1), *reinterpret_cast<uint32_t(*)[16]>(pk + (c0 >> 1)));
       }
+      if (PK) unpack2(fadd2(la, lb), l0, l1);
       l_run += l0 + l1;
       tmem_st_wait();
       tc_fence_before();
@@ -568,6 +640,12 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
     rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
     if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
     if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<4, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<8, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<2, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<6, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<16, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
     if (rc) return rc;
     configured = true;
   }
@@ -576,10 +654,23 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
   const char* ev = getenv("VDA_ATTN_VARIANT");
   const char* ep = getenv("VDA_ATTN_POLY");
   const char* el = getenv("VDA_ATTN_LATE");
-  const int variant = (ev && ev[0] == '1') ? 1 : 2, poly = ep ? atoi(ep) : 0, late = el ? atoi(el) : 1;
+  const char* ek = getenv("VDA_ATTN_PK");  // packed f32x2 softmax arithmetic
+  const int variant = (ev && ev[0] == '1') ? 1 : 2, poly = ep ? atoi(ep) : 8, late = el ? atoi(el) : 1, pk = ek ? atoi(ek) : 1;
   dim3 grid(p.q_tiles, heads, frames);
   if (variant == 1)
     attn_fwd_kernel<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(stream)>>>(p);
+  else if (pk && late && poly == 8)
+    attn_fwd_v2_kernel<8, true, true><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+  else if (pk && late && poly == 6)
+    attn_fwd_v2_kernel<6, true, true><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+  else if (pk && late && poly == 16)
+    attn_fwd_v2_kernel<16, true, true><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+  else if (pk && late && poly == 2)
+    attn_fwd_v2_kernel<2, true, true><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+  else if (pk && late && poly != 0)
+    attn_fwd_v2_kernel<4, true, true><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+  else if (pk && late)
+    attn_fwd_v2_kernel<0, true, true><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
   else if (poly != 0)
     attn_fwd_v2_kernel<4, false><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
   else if (late)
