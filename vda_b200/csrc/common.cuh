@@ -304,4 +304,48 @@ __device__ __forceinline__ float gelu_fast(float x) {
   return fmaf(fabsf(half_x), erf_abs, half_x);  // 0.5*x*(1 + sign(x)*erf|.|) = 0.5x + |0.5x|*erf_abs
 }
 
+// gelu_fast on two values at once with the packed fp32x2 FMA-pipe instructions of sm_100 (FFMA2 / FMUL2):
+// 14 FMA-pipe instructions per pair instead of 12 per value; same formula, same constants.
+__device__ __forceinline__ uint64_t f2pack(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void f2unpack(uint64_t v, float& a, float& b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f2fma(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t f2mul(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ void gelu_fast2(float& x0, float& x1) {
+  const float kr = 0.70710678118654752440f;
+  const uint64_t x = f2pack(x0, x1);
+  const uint64_t z = f2pack(fabsf(x0) * kr, fabsf(x1) * kr);
+  float d0, d1, t0, t1, a0, a1, e0, e1;
+  f2unpack(f2fma(f2pack(0.3275911f, 0.3275911f), z, f2pack(1.0f, 1.0f)), d0, d1);
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t0) : "f"(d0));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t1) : "f"(d1));
+  const uint64_t t = f2pack(t0, t1);
+  // -poly(t): constants negated so that erf_abs = 1 + (-poly) * e needs no sign flip
+  uint64_t np = f2fma(f2pack(-1.061405429f, -1.061405429f), t, f2pack(1.453152027f, 1.453152027f));
+  np = f2fma(np, t, f2pack(-1.421413741f, -1.421413741f));
+  np = f2fma(np, t, f2pack(0.284496736f, 0.284496736f));
+  np = f2fma(np, t, f2pack(-0.254829592f, -0.254829592f));
+  np = f2mul(np, t);
+  f2unpack(f2mul(f2mul(z, z), f2pack(-1.4426950408889634f, -1.4426950408889634f)), a0, a1);
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e0) : "f"(a0));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e1) : "f"(a1));
+  const uint64_t erf_abs = f2fma(np, f2pack(e0, e1), f2pack(1.0f, 1.0f));
+  const uint64_t half_x = f2mul(x, f2pack(0.5f, 0.5f));
+  const uint64_t abs_half = f2mul(z, f2pack(0.70710678118654752440f, 0.70710678118654752440f));  // |x|/sqrt2 * 1/sqrt2 = |x|/2
+  f2unpack(f2fma(abs_half, erf_abs, half_x), x0, x1);
+}
+
 }  // namespace vda

@@ -139,7 +139,7 @@ __device__ __forceinline__ void finish_group16(const GemmParams& p, const RowMap
                                                const float* s_scale16, const float4* res_pre) {
   if (p.act == ACT_GELU) {
 #pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = gelu_fast(v[i]);
+    for (int i = 0; i < 16; i += 2) gelu_fast2(v[i], v[i + 1]);
   } else if (p.act == ACT_RELU) {
 #pragma unroll
     for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);
@@ -362,7 +362,7 @@ __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_til
       for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(raw[16 * g + i]) + b[i];
       if (p.act == ACT_GELU) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = gelu_fast(v[i]);
+        for (int i = 0; i < 16; i += 2) gelu_fast2(v[i], v[i + 1]);
       } else if (p.act == ACT_RELU) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) v[i] = fmaxf(v[i], 0.f);
@@ -492,8 +492,12 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, int m_tile, i
       float bg[16];
       lds_f32x16(s_bias + c0 + 16, bg);
 #pragma unroll
-      for (int i = 0; i < 16; ++i)
-        v[i] = (__uint_as_float(raw[i]) + b[i]) * gelu_fast(__uint_as_float(gate[i]) + bg[i]);
+      for (int i = 0; i < 16; i += 2) {
+        float g0 = __uint_as_float(gate[i]) + bg[i], g1 = __uint_as_float(gate[i + 1]) + bg[i + 1];
+        gelu_fast2(g0, g1);
+        v[i] = (__uint_as_float(raw[i]) + b[i]) * g0;
+        v[i + 1] = (__uint_as_float(raw[i + 1]) + b[i + 1]) * g1;
+      }
       if (p.split)
         store_split16(p.out + rm.row * p.ldo + (col >> 1), v, p.split);
       else
