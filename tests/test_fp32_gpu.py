@@ -216,3 +216,22 @@ def test_fp32_video_driver_vs_reference_golden():
     model = build(v["arch"])
     got, _ = model.infer_video_depth(frames, 24, input_size=v["input_size"], device="cuda", fp32=True)
     check_close(got, gold["offline"], what="driver fp32")
+
+
+def test_fp32_streaming_vs_reference_golden():
+    """infer_video_depth_one(..., fp32=True): fp32 K/V caches + fp32 cached-attention kernel, frame by frame
+    against the reference's streaming outputs (46 frames: past the cache's steady state)."""
+    from video_depth_anything.video_depth_stream import VideoDepthAnything as Stream
+
+    v = G.VIDEO_CASE
+    frames = G.video_frames(v["n"], v["h"], v["w"])
+    gold = np.load(os.path.join(G.GOLDEN_DIR, "video_vits_46x44x60.npz"))["stream"]
+    cfg = O.ARCH[v["arch"]]
+    m = Stream(encoder=v["arch"], features=cfg["features"], out_channels=cfg["out_channels"])
+    m.load_state_dict(refload.seeded_state_dict(v["arch"], 0), strict=True)
+    m = m.to("cuda").eval()
+    got = np.stack([m.infer_video_depth_one(frames[i], input_size=v["input_size"], device="cuda", fp32=True)
+                    for i in range(v["n"])])
+    check_close(got, gold, what="stream fp32")
+    with pytest.raises(RuntimeError):      # the cache holds fp32 projections: no switching mid-stream
+        m.infer_video_depth_one(frames[0], input_size=v["input_size"], device="cuda", fp32=False)

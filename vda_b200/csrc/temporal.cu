@@ -329,20 +329,55 @@ static int launch_temporal_mma(const TemporalParams& p, cudaStream_t stream) {
 // at read time.  `slots[p]` names the cache slot of list position p; slots[Tk-1] is where the new
 // frame's k_c / v_c are stored by this kernel.  One warp per (token, head); lane p owns position p.
 struct TemporalStreamParams {
-  const bf16* q;     // [hw, ldn] new frame, PE-free projection
-  const bf16* knew;  // [hw, ldn]
-  const bf16* vnew;
-  bf16* kcache;      // [cap, hw, C]
-  bf16* vcache;
+  const void* q;     // [hw, ldn] new frame, PE-free projection (bf16, or f32 in the FP32-accuracy mode)
+  const void* knew;  // [hw, ldn]
+  const void* vnew;
+  void* kcache;      // [cap, hw, C], same element type as q
+  void* vcache;
   const int* slots;  // device, Tk entries
   const float* pe_q; // [32, C] projected PE tables (fp32)
   const float* pe_k;
   const float* pe_v;
-  bf16* out;         // [hw, ldo]
-  int ldn, ldo, hw, heads, hd, C, Tk;
+  bf16* out;         // [hw, ldo]; F32: split tensor, parts `split` apart
+  int ldn, ldo, hw, heads, hd, C, Tk, split;
   float scale;
 };
 
+template <bool F32>
+__device__ __forceinline__ void ld8(const void* base, long long off, float (&o)[8]) {
+  if (F32) {
+    const float4* s = reinterpret_cast<const float4*>(static_cast<const float*>(base) + off);
+    const float4 a = s[0], b = s[1];
+    o[0] = a.x, o[1] = a.y, o[2] = a.z, o[3] = a.w, o[4] = b.x, o[5] = b.y, o[6] = b.z, o[7] = b.w;
+  } else {
+    const uint4 v = *reinterpret_cast<const uint4*>(static_cast<const bf16*>(base) + off);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 f = bf2(w[i]);
+      o[2 * i] = f.x, o[2 * i + 1] = f.y;
+    }
+  }
+}
+// cache write of 8 values that were read with ld8 (exact: no re-rounding)
+template <bool F32>
+__device__ __forceinline__ void st8(void* base, long long off, const float (&v)[8]) {
+  if (F32) {
+    float4* d = reinterpret_cast<float4*>(static_cast<float*>(base) + off);
+    d[0] = make_float4(v[0], v[1], v[2], v[3]);
+    d[1] = make_float4(v[4], v[5], v[6], v[7]);
+  } else {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+      w[i] = *reinterpret_cast<uint32_t*>(&h);
+    }
+    *reinterpret_cast<uint4*>(static_cast<bf16*>(base) + off) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
+template <bool F32>
 __global__ void __launch_bounds__(kTWarps * 32) temporal_attn_stream_kernel(const TemporalStreamParams p) {
   extern __shared__ __align__(16) uint8_t tsm[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -356,32 +391,30 @@ __global__ void __launch_bounds__(kTWarps * 32) temporal_attn_stream_kernel(cons
   const bool is_new = pos == p.Tk - 1;
   const int slot = active ? p.slots[pos] : 0;
   const long long crow = (static_cast<long long>(slot) * p.hw + d) * p.C + head * hd;
-  const bf16* krow = is_new ? p.knew + static_cast<long long>(d) * p.ldn + head * hd : p.kcache + crow;
-  const bf16* vrow = is_new ? p.vnew + static_cast<long long>(d) * p.ldn + head * hd : p.vcache + crow;
-  const bf16* qrow = p.q + static_cast<long long>(d) * p.ldn + head * hd;
+  const long long nrow = static_cast<long long>(d) * p.ldn + head * hd;
   const float* peq = p.pe_q + static_cast<long long>(p.Tk - 1) * p.C + head * hd;
   const float* pek = p.pe_k + static_cast<long long>(pos) * p.C + head * hd;
   const float* pev = p.pe_v + static_cast<long long>(pos) * p.C + head * hd;
   float s = 0.f;
   if (active) {
     for (int c = 0; c < chunks; ++c) {
-      const uint4 qq = __ldg(reinterpret_cast<const uint4*>(qrow + c * 8));
-      const uint4 kk = *reinterpret_cast<const uint4*>(krow + c * 8);
-      if (is_new) *reinterpret_cast<uint4*>(p.kcache + crow + c * 8) = kk;
-      const uint32_t qw[4] = {qq.x, qq.y, qq.z, qq.w}, kw[4] = {kk.x, kk.y, kk.z, kk.w};
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const float2 qf = bf2(qw[i]), kf = bf2(kw[i]);
-        const int cc = c * 8 + 2 * i;
-        s += (qf.x + peq[cc]) * (kf.x + pek[cc]) + (qf.y + peq[cc + 1]) * (kf.y + pek[cc + 1]);
+      float qf[8], kf[8];
+      ld8<F32>(p.q, nrow + c * 8, qf);
+      if (is_new) {
+        ld8<F32>(p.knew, nrow + c * 8, kf);
+        st8<F32>(p.kcache, crow + c * 8, kf);
+      } else {
+        ld8<F32>(p.kcache, crow + c * 8, kf);
       }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s = fmaf(qf[i] + peq[c * 8 + i], kf[i] + pek[c * 8 + i], s);
     }
   }
   s = active ? s * p.scale : -INFINITY;
   float m = s;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-  float e = active ? __expf(s - m) : 0.f;
+  float e = active ? (F32 ? expf(s - m) : __expf(s - m)) : 0.f;
   float l = e;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
@@ -389,16 +422,15 @@ __global__ void __launch_bounds__(kTWarps * 32) temporal_attn_stream_kernel(cons
   float* mine = sW + lane * (hd + 1);
   if (active) {
     for (int c = 0; c < chunks; ++c) {
-      const uint4 vv = *reinterpret_cast<const uint4*>(vrow + c * 8);
-      if (is_new) *reinterpret_cast<uint4*>(p.vcache + crow + c * 8) = vv;
-      const uint32_t vw[4] = {vv.x, vv.y, vv.z, vv.w};
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const float2 vf = bf2(vw[i]);
-        const int cc = c * 8 + 2 * i;
-        mine[cc] = w * (vf.x + pev[cc]);
-        mine[cc + 1] = w * (vf.y + pev[cc + 1]);
+      float vf[8];
+      if (is_new) {
+        ld8<F32>(p.vnew, nrow + c * 8, vf);
+        st8<F32>(p.vcache, crow + c * 8, vf);
+      } else {
+        ld8<F32>(p.vcache, crow + c * 8, vf);
       }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) mine[c * 8 + i] = w * (vf[i] + pev[c * 8 + i]);
     }
   } else {
     for (int c = 0; c < hd; ++c) mine[c] = 0.f;
@@ -409,7 +441,12 @@ __global__ void __launch_bounds__(kTWarps * 32) temporal_attn_stream_kernel(cons
     float acc = 0.f;
 #pragma unroll 8
     for (int j = 0; j < 32; ++j) acc += sW[j * (hd + 1) + c];
-    orow[c] = __float2bfloat16(acc);
+    const bf16 hi = __float2bfloat16(acc);
+    orow[c] = hi;
+    if (F32) {
+      orow[c + p.split] = __float2bfloat16(acc - __bfloat162float(hi));
+      orow[c + 2 * p.split] = hi;
+    }
   }
 }
 
@@ -417,32 +454,54 @@ __global__ void __launch_bounds__(kTWarps * 32) temporal_attn_stream_kernel(cons
 
 using namespace vda;
 
-extern "C" int vda_temporal_attn_stream(const void* q, const void* knew, const void* vnew, int ldn, void* kcache,
-                                        void* vcache, const int* slots, const float* pe_q, const float* pe_k,
-                                        const float* pe_v, void* out, int ldo, int hw, int heads, int head_dim, int Tk,
-                                        void* stream) {
+static int launch_temporal_stream(bool f32, const void* q, const void* knew, const void* vnew, int ldn, void* kcache,
+                                  void* vcache, const int* slots, const float* pe_q, const float* pe_k, const float* pe_v,
+                                  void* out, int ldo, int split, int hw, int heads, int head_dim, int Tk, void* stream) {
   if (!q || !knew || !vnew || !kcache || !vcache || !slots || !pe_q || !pe_k || !pe_v || !out || hw <= 0 || heads <= 0 ||
-      head_dim % 8 || head_dim > 128 || Tk < 1 || Tk > 32 || ldn % 8 || ldo % 2)
+      head_dim % 8 || head_dim > 128 || Tk < 1 || Tk > 32 || ldn % 8 || ldo % 2 || split < 0)
     return set_error(-1, "vda_temporal_attn_stream: bad arguments");
   TemporalStreamParams p;
-  p.q = static_cast<const bf16*>(q), p.knew = static_cast<const bf16*>(knew), p.vnew = static_cast<const bf16*>(vnew);
-  p.kcache = static_cast<bf16*>(kcache), p.vcache = static_cast<bf16*>(vcache);
+  p.q = q, p.knew = knew, p.vnew = vnew, p.kcache = kcache, p.vcache = vcache;
   p.slots = slots, p.pe_q = pe_q, p.pe_k = pe_k, p.pe_v = pe_v;
   p.out = static_cast<bf16*>(out);
-  p.ldn = ldn, p.ldo = ldo, p.hw = hw, p.heads = heads, p.hd = head_dim, p.C = heads * head_dim, p.Tk = Tk;
+  p.ldn = ldn, p.ldo = ldo, p.hw = hw, p.heads = heads, p.hd = head_dim, p.C = heads * head_dim, p.Tk = Tk, p.split = split;
   p.scale = 1.0f / sqrtf(static_cast<float>(head_dim));
   const int smem = kTWarps * 32 * (head_dim + 1) * 4;
   static bool configured = false;
   if (!configured) {
-    int rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    int rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              kTWarps * 32 * 129 * 4),
                         "temporal stream smem attribute");
+    if (!rc)
+      rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           kTWarps * 32 * 129 * 4),
+                      "temporal stream smem attribute");
     if (rc) return rc;
     configured = true;
   }
-  const int units = hw * heads;
-  temporal_attn_stream_kernel<<<(units + kTWarps - 1) / kTWarps, kTWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  const int units = hw * heads, grid = (units + kTWarps - 1) / kTWarps;
+  if (f32)
+    temporal_attn_stream_kernel<true><<<grid, kTWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  else
+    temporal_attn_stream_kernel<false><<<grid, kTWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(p);
   return check_cuda(cudaGetLastError(), "temporal_attn_stream launch");
+}
+
+extern "C" int vda_temporal_attn_stream(const void* q, const void* knew, const void* vnew, int ldn, void* kcache,
+                                        void* vcache, const int* slots, const float* pe_q, const float* pe_k,
+                                        const float* pe_v, void* out, int ldo, int hw, int heads, int head_dim, int Tk,
+                                        void* stream) {
+  return launch_temporal_stream(false, q, knew, vnew, ldn, kcache, vcache, slots, pe_q, pe_k, pe_v, out, ldo, 0, hw, heads,
+                                head_dim, Tk, stream);
+}
+
+extern "C" int vda_temporal_attn_stream_f32(const float* q, const float* knew, const float* vnew, int ldn, float* kcache,
+                                            float* vcache, const int* slots, const float* pe_q, const float* pe_k,
+                                            const float* pe_v, void* out, int ldo, int split, int hw, int heads,
+                                            int head_dim, int Tk, void* stream) {
+  if (split <= 0 || split % 2) return set_error(-1, "vda_temporal_attn_stream_f32: split must be the part stride");
+  return launch_temporal_stream(true, q, knew, vnew, ldn, kcache, vcache, slots, pe_q, pe_k, pe_v, out, ldo, split, hw, heads,
+                                head_dim, Tk, stream);
 }
 
 

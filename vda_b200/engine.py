@@ -225,8 +225,6 @@ class Engine:
         m = self.w.motion[idx]
         C, rows = m.C, T * hw
         sp, Wd = self.fp32, self.W
-        if sp and stream_ctx is not None:
-            raise L.VdaError("the streaming cache runs in BF16 only")
         tag = f"mm{idx}_"
         gn = ws.get(tag + "gn", (rows, C * Wd))
         stats = ws.get(tag + "gnstats", (96 * T,), torch.float64)
@@ -236,18 +234,18 @@ class Engine:
         n = ws.get(tag + "n", (rows, C * Wd))
         o = ws.get(tag + "o", (rows, C * Wd))
         for a_i, a in enumerate(m.attn):
-            if sp:
+            if stream_ctx is not None:
+                stream_ctx.attend(self, idx, a_i, a, h, n, o, hw, C, ws)
+            elif sp:
                 qkv32 = ws.get(tag + "qkv_f32", (rows, 3 * C), torch.float32)
                 L.layernorm(h, a["ln_w"], a["ln_b"], n, 1e-5, C=C, pe=a["pe"], pe_rows_per_t=hw, pe_T=32, split=1)
                 L.gemm(n, a["wqkv"], L.make_epilogue(out_f32=qkv32, ldo=3 * C))
                 L.temporal_attn_f32(qkv32, C, o, C, hw, 8, T, T)
-            elif stream_ctx is None:
+            else:
                 qkv = ws.get(tag + "qkv", (rows, 3 * C))
                 L.layernorm(h, a["ln_w"], a["ln_b"], n, 1e-5, pe=a["pe"], pe_rows_per_t=hw, pe_T=32)
                 L.gemm(n, a["wqkv"], L.make_epilogue(out=qkv, ldo=3 * C))
                 L.temporal_attn(qkv, 3 * C, qkv[:, C:], 3 * C, qkv[:, 2 * C:], 3 * C, o, C, hw, 8, C // 8, T, T)
-            else:
-                stream_ctx.attend(self, idx, a_i, a, h, n, o, hw, C, ws)
             L.gemm(o, a["wo"], L.make_epilogue(bias=a["bo"], res_f32=h, out_f32=h, ldo=C))
         L.layernorm(h, m.ffn_w, m.ffn_b, n, 1e-5, C=C, split=int(sp))
         g = ws.get(tag + "geglu", (rows, 4 * C * Wd))
@@ -435,8 +433,10 @@ class StreamCache:
         dev = engine.device
         gh4, gw4 = (gh - 1) // 2 + 1, (gw - 1) // 2 + 1
         geo = [(gh * gw, w.oc[2]), (gh4 * gw4, w.oc[3]), (gh * gw, w.F), (4 * gh * gw, w.F)]
-        self.k = [[torch.zeros(self.CAP, hw, C, dtype=torch.bfloat16, device=dev) for _ in range(2)] for hw, C in geo]
-        self.v = [[torch.zeros(self.CAP, hw, C, dtype=torch.bfloat16, device=dev) for _ in range(2)] for hw, C in geo]
+        self.fp32 = engine.fp32
+        dt = torch.float32 if engine.fp32 else torch.bfloat16   # FP32-accuracy mode keeps fp32 projections
+        self.k = [[torch.zeros(self.CAP, hw, C, dtype=dt, device=dev) for _ in range(2)] for hw, C in geo]
+        self.v = [[torch.zeros(self.CAP, hw, C, dtype=dt, device=dev) for _ in range(2)] for hw, C in geo]
         self.slots_dev = torch.zeros(32, dtype=torch.int32, device=dev)
         self.slots_host = torch.zeros(32, dtype=torch.int32).pin_memory()
         self.Tk = 1
@@ -449,6 +449,13 @@ class StreamCache:
         self.slots_dev.copy_(self.slots_host, non_blocking=True)
 
     def attend(self, eng, idx, a_i, a, h, n, o, hw, C, ws):
+        if eng.fp32:
+            qkv32 = ws.get(f"mm{idx}_qkv_f32", (hw, 3 * C), torch.float32)
+            L.layernorm(h, a["ln_w"], a["ln_b"], n, 1e-5, C=C, split=1)
+            L.gemm(n, a["wqkv"], L.make_epilogue(out_f32=qkv32, ldo=3 * C))
+            L.temporal_attn_stream_f32(qkv32, qkv32[:, C:], qkv32[:, 2 * C:], 3 * C, self.k[idx][a_i], self.v[idx][a_i],
+                                       self.slots_dev, a["pe_q"], a["pe_k"], a["pe_v"], o, C, hw, 8, C // 8, self.Tk)
+            return
         qkv = ws.get(f"mm{idx}_qkv", (hw, 3 * C))
         L.layernorm(h, a["ln_w"], a["ln_b"], n, 1e-5)
         L.gemm(n, a["wqkv"], L.make_epilogue(out=qkv, ldo=3 * C))

@@ -45,11 +45,14 @@ class VideoDepthAnything(nn.Module):
         self._engine = None
         return super().load_state_dict(*a, **k)
 
-    def engine(self):
+    def engine(self, fp32=False):
+        """One executor per precision (BF16 tensor-core path / FP32-accuracy path), built on first use."""
         dev = self.pretrained.cls_token.device
-        if self._engine is None or self._engine.device != dev:
-            self._engine = Engine(self, dev)
-        return self._engine
+        if self._engine is None or self._engine.get("dev") != dev:
+            self._engine = {"dev": dev}
+        if fp32 not in self._engine:
+            self._engine[fp32] = Engine(self, dev, fp32=fp32)
+        return self._engine[fp32]
 
     def forward(self, x):
         """Cache-free forward, x f32 [B,T,3,H,W] -> [B,T,H,W] (video_depth_stream.py:62-63)."""
@@ -76,10 +79,13 @@ class VideoDepthAnything(nn.Module):
             assert frame.shape[0] == self.frame_height
             assert frame.shape[1] == self.frame_width
         nh, nw = self.transform
-        eng = self.engine()
+        eng = self.engine(bool(fp32))
         with torch.cuda.device(dev):
             if self._cache is None or self.id == 0:
                 self._cache = StreamCache(eng, nh // 14, nw // 14)
+            elif self._cache.fp32 != eng.fp32:
+                raise RuntimeError("infer_video_depth_one: `fp32` must stay the same for all frames of a stream "
+                                   "(the temporal cache holds projections in that precision)")
             x = preprocess_frames(frame[None], [0], nh, nw, dev)
             slot = self._free_slot()
             if self.id == 0:
