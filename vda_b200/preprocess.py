@@ -57,6 +57,52 @@ def preprocess_frames(frames, indices, nh, nw, device):
     return out
 
 
+class FrameFeeder:
+    """Incremental host -> device feed of source frames for the window loop (video_depth.py:100-107).
+
+    Every source frame is uploaded and pre-processed exactly once, just before the first window that
+    needs it: uint8 frames are gathered into one of two pinned staging slots (allocated once per frame
+    size and reused: pinning ~1 GB per call costs more than a whole second on the GPU box), copied to the
+    device on the caller's stream and converted by `vda_preprocess_u8` into rows of the resident network
+    input table.  The host runs at most two windows ahead of the GPU (slot reuse waits on the copy)."""
+
+    SLOT_FRAMES = 32
+
+    def __init__(self, h0, w0, nh, nw, device):
+        self.key = (h0, w0, nh, nw, str(device))
+        self.device = device
+        self.nh, self.nw = nh, nw
+        self.pinned = [torch.empty(self.SLOT_FRAMES, h0, w0, 3, dtype=torch.uint8, pin_memory=True) for _ in range(2)]
+        self.staged = [torch.empty(self.SLOT_FRAMES, h0, w0, 3, dtype=torch.uint8, device=device) for _ in range(2)]
+        self.done = [None, None]
+        self.turn = 0
+
+    def feed(self, frames, indices, table, rows):
+        """Upload frames[indices] and write their network inputs into table[rows[0] : rows[0]+len(indices)]
+        (rows are consecutive).  Asynchronous on the current stream."""
+        from . import lib as L
+
+        pos = 0
+        while pos < len(indices):
+            part = indices[pos:pos + self.SLOT_FRAMES]
+            t = self.turn
+            self.turn ^= 1
+            if self.done[t] is not None:
+                self.done[t].synchronize()
+            m = len(part)
+            dst = self.pinned[t].numpy()
+            if part[-1] - part[0] == m - 1:               # consecutive frames: one block copy
+                dst[:m] = frames[part[0]:part[0] + m]
+            else:
+                np.take(frames, part, axis=0, out=dst[:m])
+            self.staged[t][:m].copy_(self.pinned[t][:m], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+            self.done[t] = ev
+            L.preprocess_u8(self.staged[t][:m], table[rows[0] + pos:rows[0] + pos + m], self.nh, self.nw)
+            pos += m
+
+
 def preprocess_frames_cv2(frames, indices, nh, nw, device):
     """The reference's host path (cv2 on a thread pool); test comparand of preprocess_frames."""
     global _POOL

@@ -16,7 +16,7 @@ from . import lib as L
 from . import parallel
 from .engine import Engine
 from .modules import ARCH, DinoEncoder, DPTTemporalHead
-from .preprocess import net_input_size, preprocess_frames
+from .preprocess import FrameFeeder, net_input_size, preprocess_frames
 
 # window semantics of the reference, "do not change" (video_depth.py:29-33)
 INFER_LEN = 32
@@ -177,23 +177,44 @@ class VideoDepthAnything(nn.Module):
         fp32=True: FP32-accuracy path (rtol 1e-3 against the reference's fp32 forward).
         original_width / original_height (both given): the aligned maps are upscaled bilinearly
         (align_corners=True) to that size before they leave the GPU -- the kwargs of the fork's engine copy,
-        external_engine/video_depth_anything/video_depth.py:81-90, :181-203."""
-        depth = self.infer_video_depth_device(frames, input_size=input_size, device=device, fp32=fp32)
-        if original_width is not None and original_height is not None:
-            up = torch.empty(depth.shape[0], int(original_height), int(original_width), dtype=torch.float32,
-                             device=depth.device)
-            with torch.cuda.device(depth.device):
-                L.bilinear_f32(depth.contiguous(), up, depth.shape[0], depth.shape[1], depth.shape[2], up.shape[1], up.shape[2])
-            depth = up
-        host = torch.empty(depth.shape, dtype=torch.float32, pin_memory=True)
-        host.copy_(depth, non_blocking=True)
-        torch.cuda.current_stream(depth.device).synchronize()
-        return host.numpy(), target_fps
+        external_engine/video_depth_anything/video_depth.py:81-90, :181-203.
+
+        One pass, pipelined per window: upload + pre-process the window's new frames, forward, resize to the
+        source size, alignment scan step, then the frames that scan step made final go device -> pinned ring
+        -> the result array on a side stream while the next window computes."""
+        frames = np.asarray(frames)
+        n, h0, w0 = frames.shape[:3]
+        up = (int(original_height), int(original_width)) if original_width is not None and original_height is not None else None
+        out = np.empty((n,) + (up or (h0, w0)), np.float32)
+        if parallel.active():
+            depth = self.infer_video_depth_device(frames, input_size=input_size, device=device, fp32=fp32)
+            dl = self._downloader(depth.device, h0, w0, up)
+            dl.begin(out)
+            for lo in range(0, n, dl.FRAMES):
+                dl.push(depth[lo:min(lo + dl.FRAMES, n)], lo)
+            dl.finish()
+            return out, target_fps
+        dl = None
+
+        def on_window(scan, final_lo, final_hi):
+            nonlocal dl
+            if dl is None:
+                dl = self._downloader(scan.out.device, h0, w0, up)
+                dl.begin(out)
+            hi = min(final_hi, n)
+            if hi > final_lo:
+                dl.push(scan.out[final_lo:hi], final_lo)
+
+        self._run_video(frames, input_size, device, fp32, None, on_window)
+        dl.finish()
+        return out, target_fps
 
     @torch.no_grad()
     def infer_video_depth_device(self, frames, input_size=518, device="cuda", windows=None, return_raw=False, fp32=False):
         """Same as infer_video_depth but leaves the aligned depth [N,H0,W0] on the GPU.
-        `windows` restricts the forward passes to a subset (multi-GPU sharding, vda_b200.parallel)."""
+        `windows` restricts the forward passes to a subset (multi-GPU sharding, vda_b200.parallel) and
+        return_raw returns their un-aligned maps [len(windows)*32, H0, W0]."""
+        frames = np.asarray(frames)
         if windows is None and not return_raw and parallel.active():
             # one process per GPU (torchrun): shard the windows, all-gather the per-window depth over NCCL
             n = len(frames)
@@ -202,65 +223,161 @@ class VideoDepthAnything(nn.Module):
                 lambda ids: self.infer_video_depth_device(frames, input_size, device, windows=ids, return_raw=True,
                                                           fp32=fp32),
                 lambda raw: align_windows_device(raw, self.metric))
-        prep = self.prepare_video(frames, input_size, device, windows)
-        raw = self.run_windows(prep, fp32=fp32)
-        if return_raw:
-            return raw
-        return align_windows_device(raw, self.metric)[:prep["n"]]
+        res = self._run_video(frames, input_size, device, fp32, windows, None, keep_raw=return_raw)
+        return res if return_raw else res[:len(frames)]
 
-    def prepare_video(self, frames, input_size=518, device="cuda", windows=None):
-        """Host side of the driver: window composition, one cv2 pre-process per needed source frame
-        (util/transform.py via vda_b200.preprocess), one async H2D copy.  Returns the state run_windows needs."""
+    def _run_video(self, frames, input_size, device, fp32, windows, on_window, keep_raw=False):
+        """The window loop.  keep_raw: returns raw [len(windows)*32, H0, W0]; otherwise runs the alignment scan
+        as it goes (all windows must be present, in order), calls on_window(scan, lo, hi) with the range of
+        aligned frames that became final, and returns the aligned maps (device)."""
         dev = torch.device(device if device != "cuda" else f"cuda:{torch.cuda.current_device()}")
         if self.pretrained.cls_token.device != dev:
             raise RuntimeError(f"model is on {self.pretrained.cls_token.device}, call .to('{dev}') first")
-        frames = np.asarray(frames)
         n, h0, w0 = frames.shape[:3]
         nh, nw = net_input_size(h0, w0, input_size)
         wins = window_frame_indices(n)
         mine = list(range(len(wins))) if windows is None else list(windows)
+        assert keep_raw or mine == list(range(len(wins))), "the alignment scan needs every window, in order"
         needed = sorted({i for k in mine for i in wins[k]})
-        slot = {f: j for j, f in enumerate(needed)}
-        with torch.cuda.device(dev):
-            net_in = preprocess_frames(frames, needed, nh, nw, dev)            # [len(needed),3,nh,nw] f32 on GPU
-            idx = [torch.tensor([slot[f] for f in wins[k]], device=dev) for k in mine]
-        return dict(n=n, h0=h0, w0=w0, nh=nh, nw=nw, mine=mine, net_in=net_in, idx=idx, dev=dev)
-
-    def run_windows(self, prep, fp32=False):
-        """Device side: one forward per owned window + bilinear to the source size -> raw [len*32,H0,W0]."""
+        row = {f: j for j, f in enumerate(needed)}
         eng = self.engine(fp32)
-        dev, h0, w0, nh, nw = prep["dev"], prep["h0"], prep["w0"], prep["nh"], prep["nw"]
         with torch.cuda.device(dev):
-            raw = torch.empty(len(prep["mine"]) * INFER_LEN, h0, w0, dtype=torch.float32, device=dev)
-            for j, idx in enumerate(prep["idx"]):
-                d = eng.forward(prep["net_in"].index_select(0, idx))
-                L.bilinear_f32(d, raw[j * INFER_LEN:(j + 1) * INFER_LEN], INFER_LEN, nh, nw, h0, w0)
-        return raw
+            feeder = getattr(self, "_feeder", None)
+            if feeder is None or feeder.key != (h0, w0, nh, nw, str(dev)):
+                feeder = self._feeder = FrameFeeder(h0, w0, nh, nw, dev)
+            table = torch.empty(len(needed), 3, nh, nw, dtype=torch.float32, device=dev)   # network input per source frame
+            idx_all = torch.tensor([[row[f] for f in wins[k]] for k in mine], dtype=torch.long).reshape(len(mine), INFER_LEN)
+            idx_all = idx_all.to(dev, non_blocking=True)
+            fed = 0                                       # rows [0, fed) of `table` are resident
+            if keep_raw:
+                raw = torch.empty(len(mine) * INFER_LEN, h0, w0, dtype=torch.float32, device=dev)
+            else:
+                scan = AlignScan(len(wins), h0, w0, dev, self.metric)
+                slots = [torch.empty(INFER_LEN, h0, w0, dtype=torch.float32, device=dev) for _ in range(2)]
+            for j, k in enumerate(mine):
+                top = max(row[f] for f in wins[k]) + 1
+                if top > fed:                             # frames are needed in increasing order of index
+                    feeder.feed(frames, needed[fed:top], table, (fed, top))
+                    fed = top
+                d = eng.forward(table.index_select(0, idx_all[j]))
+                dst = raw[j * INFER_LEN:(j + 1) * INFER_LEN] if keep_raw else slots[j & 1]
+                L.bilinear_f32(d, dst, INFER_LEN, nh, nw, h0, w0)
+                if not keep_raw:
+                    lo, hi = scan.push(dst)
+                    if on_window is not None:
+                        on_window(scan, lo, hi)
+        return raw if keep_raw else scan.out
+
+    def _downloader(self, dev, h0, w0, up):
+        key = (str(dev), h0, w0, up)
+        dl = getattr(self, "_dl", None)
+        if dl is None or dl.key != key:
+            dl = self._dl = HostDownloader(dev, h0, w0, up)
+        return dl
+
+
+class AlignScan:
+    """Sequential scale/shift alignment + 8-frame cross-fade (video_depth.py:120-160) as an incremental
+    scan on the GPU: push() takes one window's raw maps [32, H0, W0] and extends the aligned sequence
+    `out` [32 + 22*(n_windows-1), H0, W0].  No host synchronisation."""
+
+    def __init__(self, n_windows, h0, w0, device, metric=False, out=None):
+        self.metric = bool(metric)
+        self.per = h0 * w0
+        total = INFER_LEN + (INFER_LEN - OVERLAP) * (n_windows - 1)
+        self.out = out if out is not None else torch.empty(total, h0, w0, dtype=torch.float32, device=device)
+        self.sums = torch.zeros(5, dtype=torch.float64, device=device)
+        self.ss = torch.empty(2, dtype=torch.float32, device=device)
+        self.filled = 0
+        self.n_windows, self.k = n_windows, 0
+        self.ref = None
+
+    def push(self, raw):
+        """Returns (lo, hi): aligned frames [lo, hi) can no longer change (the last INTERP_LEN frames of
+        the sequence are cross-faded with the next window, except after the last one)."""
+        out, per = self.out, self.per
+        step, n_align = INFER_LEN - OVERLAP, OVERLAP - INTERP_LEN
+        last = self.k == self.n_windows - 1
+        if self.k == 0:
+            out[:INFER_LEN].copy_(raw)
+            self.ref = [out[KEYFRAMES[0]], out[KEYFRAMES[1]]]
+            self.filled = INFER_LEN
+            lo = 0
+        else:
+            filled = self.filled
+            self.sums.zero_()
+            for i in range(n_align):
+                L.lsq_accum(raw[i], self.ref[i], per, self.sums)
+            L.lsq_solve(self.sums, self.ss, self.metric)
+            L.affine_clamp_blend(out[filled - INTERP_LEN:filled], raw[n_align:OVERLAP], per, INTERP_LEN, self.ss)
+            L.affine_clamp(raw[OVERLAP:INFER_LEN], out[filled:filled + step], per * step, self.ss)
+            self.ref = [self.ref[0], out[filled + KEYFRAMES[1] - OVERLAP]]
+            lo = filled - INTERP_LEN
+            self.filled = filled + step
+        self.k += 1
+        return lo, (self.filled if last else self.filled - INTERP_LEN)
 
 
 def align_windows_device(raw, metric=False, out=None):
-    """Sequential scale/shift alignment + 8-frame cross-fade (video_depth.py:120-160) on the GPU.
-    raw: f32 [n_windows*32, H0, W0] -> f32 [32 + 22*(n_windows-1), H0, W0].  No host sync."""
+    """All windows at once: raw f32 [n_windows*32, H0, W0] -> f32 [32 + 22*(n_windows-1), H0, W0]."""
     n_win = raw.shape[0] // INFER_LEN
-    per = raw.shape[1] * raw.shape[2]
-    step = INFER_LEN - OVERLAP
-    n_align = OVERLAP - INTERP_LEN
-    total = INFER_LEN + step * (n_win - 1)
-    if out is None:
-        out = torch.empty(total, raw.shape[1], raw.shape[2], dtype=torch.float32, device=raw.device)
-    out[:INFER_LEN].copy_(raw[:INFER_LEN])
-    ref = [raw[KEYFRAMES[0]], raw[KEYFRAMES[1]]]
-    sums = torch.zeros(5, dtype=torch.float64, device=raw.device)
-    ss = torch.empty(2, dtype=torch.float32, device=raw.device)
-    filled = INFER_LEN
-    for k in range(1, n_win):
-        base = k * INFER_LEN
-        sums.zero_()
-        for i in range(n_align):
-            L.lsq_accum(raw[base + i], ref[i], per, sums)
-        L.lsq_solve(sums, ss, metric)
-        L.affine_clamp_blend(out[filled - INTERP_LEN:filled], raw[base + n_align:base + OVERLAP], per, INTERP_LEN, ss)
-        L.affine_clamp(raw[base + OVERLAP:base + INFER_LEN], out[filled:filled + step], per * step, ss)
-        ref = [ref[0], out[filled + KEYFRAMES[1] - OVERLAP]]
-        filled += step
-    return out
+    scan = AlignScan(n_win, raw.shape[1], raw.shape[2], raw.device, metric, out=out)
+    for k in range(n_win):
+        scan.push(raw[k * INFER_LEN:(k + 1) * INFER_LEN])
+    return scan.out
+
+
+class HostDownloader:
+    """Device -> host path of the result (video_depth.py:113,162): chunks of <= 32 maps go through a
+    two-slot pinned ring on a side stream and are copied into the caller's (pageable) array while the GPU
+    works on the next window.  The ring is allocated once per frame size and reused across calls; the
+    optional bilinear upscale to the caller's plate size runs on the main stream before the copy."""
+
+    FRAMES = INFER_LEN
+
+    def __init__(self, dev, h0, w0, up=None):
+        self.key = (str(dev), h0, w0, up)
+        self.dev, self.h0, self.w0, self.up = dev, h0, w0, up
+        oh, ow = up or (h0, w0)
+        self.ring = [torch.empty(self.FRAMES, oh, ow, dtype=torch.float32, pin_memory=True) for _ in range(2)]
+        self.upbuf = [torch.empty(self.FRAMES, oh, ow, dtype=torch.float32, device=dev) for _ in range(2)] if up else None
+        self.side = torch.cuda.Stream(dev)
+        self.pending = [None, None]
+        self.turn = 0
+        self.out = None
+
+    def begin(self, out):
+        self.out = out
+        self.pending = [None, None]
+        self.turn = 0
+
+    def _drain(self, t):
+        if self.pending[t] is not None:
+            ev, lo, m = self.pending[t]
+            ev.synchronize()
+            self.out[lo:lo + m] = self.ring[t].numpy()[:m]
+            self.pending[t] = None
+
+    def push(self, src, lo):
+        """src: device f32 [m <= 32, h0, w0], final; becomes out[lo:lo+m]."""
+        t = self.turn
+        self.turn ^= 1
+        self._drain(t)
+        m = src.shape[0]
+        with torch.cuda.device(self.dev):
+            if self.up:
+                L.bilinear_f32(src.contiguous(), self.upbuf[t][:m], m, self.h0, self.w0, self.up[0], self.up[1])
+                src = self.upbuf[t][:m]
+            ready = torch.cuda.Event()
+            ready.record()
+            with torch.cuda.stream(self.side):
+                self.side.wait_event(ready)
+                self.ring[t][:m].copy_(src, non_blocking=True)
+                done = torch.cuda.Event()
+                done.record()
+        self.pending[t] = (done, lo, m)
+
+    def finish(self):
+        self._drain(self.turn)
+        self._drain(self.turn ^ 1)
+        self.out = None
