@@ -24,6 +24,8 @@ w2, b2 = r(D, 4 * D, sc=(4 * D) ** -0.5).bfloat16(), r(D)
 qk = torch.empty(M, 2 * D, device=dev, dtype=torch.bfloat16)
 vt = torch.zeros(T * heads, 64, spad, device=dev, dtype=torch.bfloat16)
 ao = torch.empty(M, D, device=dev, dtype=torch.bfloat16)
+qkvs = (torch.randn(M, 9 * D, device=dev) * 0.5).bfloat16()   # FP32-accuracy mode: q | k | v as [hi | lo | hi]
+ao3 = torch.empty(M, 3 * D, device=dev, dtype=torch.bfloat16)
 h1 = torch.empty(M, 4 * D, device=dev, dtype=torch.bfloat16)
 lnw, lnb = r(D), r(D)
 
@@ -81,6 +83,7 @@ ops = {
     "ln": (lambda: L.layernorm(tok, lnw, lnb, xn, 1e-6), 0),
     "qkv": (lambda: L.gemm(xn, wqkv, L.make_epilogue(bias=bqkv, out=qk, ldo=2 * D, store_mode=L.ST_QKV,
                                                      qkv=(vt, D, heads, S, spad))), 2 * M * 3 * D * D),
+    "attn_f32": (lambda: L.attn_f32(qkvs, ao3, D, T, S, heads, in_split=3 * D), 3 * 4 * T * heads * S * S * 64),
     "attn": (lambda: L.flash_attn(qk, vt, ao, T, S, heads, spad), 4 * T * heads * S * S * 64),
     "proj": (lambda: L.gemm(ao, wproj, L.make_epilogue(bias=bproj, scale=g1, res_f32=tok, out_f32=tok, ldo=D)),
              2 * M * D * D),
@@ -131,7 +134,7 @@ tot = {v: 0.0 for v in env_vals}
 for name in only:
     for val in env_vals:
         ms, flops = best[(name, val)], ops[name][1]
-        tot[val] += ms if "plain" not in name and "bias" not in name and "relu" not in name else 0
+        tot[val] += ms if "plain" not in name and "bias" not in name and "relu" not in name and "f32" not in name else 0
         tag = f" [{env_name}={val}]" if env_name else ""
         print(f"{name:10s} {ms * 1e3:8.1f} us  {flops / ms / 1e9:7.0f} TFLOP/s{tag}")
 for val in env_vals:

@@ -361,13 +361,11 @@ __global__ void __launch_bounds__(128, 3) attn_split_mma_kernel(const bf16* __re
   const int ntiles = (S + kAmKeys - 1) / kAmKeys;
   for (int t = 0; t < ntiles; ++t) {
     const int j0 = t * kAmKeys;
-    if (t + 1 < ntiles) {
-      load_tile(j0 + kAmKeys, (t + 1) & 1);
-      asm volatile("cp.async.wait_group 1;" ::: "memory");
-    } else {
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
-    }
+    // one barrier per tile: my copies of tile t have landed, and after the barrier so have everyone's --
+    // and every warp is done with tile t-1, whose stage the prefetch of tile t+1 now overwrites
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
+    if (t + 1 < ntiles) load_tile(j0 + kAmKeys, (t + 1) & 1);
     const uint32_t sKh = sbase + (t & 1) * kApStage, sKl = sKh + kApMat, sVh = sKl + kApMat, sVl = sVh + kApMat;
 
     float s[8][4];
@@ -375,20 +373,32 @@ __global__ void __launch_bounds__(128, 3) attn_split_mma_kernel(const bf16* __re
     for (int nt = 0; nt < 8; ++nt)
 #pragma unroll
       for (int i = 0; i < 4; ++i) s[nt][i] = 0.f;
+    // (the three terms of one accumulator are dependent MMAs: issue them term-major over four independent
+    // accumulators so that consecutive instructions never wait on each other)
 #pragma unroll
     for (int kk = 0; kk < 4; ++kk) {
 #pragma unroll
-      for (int np = 0; np < 4; ++np) {
-        uint32_t bh[4], bl[4];
-        const uint32_t off = (np * 16 + (lane & 7) + ((lane >> 4) << 3)) * kAmPitch + (kk * 2 + ((lane >> 3) & 1)) * 16;
-        f32_ldsm_x4(sKh + off, bh);
-        f32_ldsm_x4(sKl + off, bl);
+      for (int n2 = 0; n2 < 2; ++n2) {
+        uint32_t bh[2][4], bl[2][4];
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
-          f32_mma(s[2 * np + u], qh[kk], bh[2 * u], bh[2 * u + 1]);
-          f32_mma(s[2 * np + u], ql[kk], bh[2 * u], bh[2 * u + 1]);
-          f32_mma(s[2 * np + u], qh[kk], bl[2 * u], bl[2 * u + 1]);
+        for (int e = 0; e < 2; ++e) {
+          const int np = 2 * n2 + e;
+          const uint32_t off = (np * 16 + (lane & 7) + ((lane >> 4) << 3)) * kAmPitch + (kk * 2 + ((lane >> 3) & 1)) * 16;
+          f32_ldsm_x4(sKh + off, bh[e]);
+          f32_ldsm_x4(sKl + off, bl[e]);
         }
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+#pragma unroll
+          for (int u = 0; u < 2; ++u) f32_mma(s[4 * n2 + 2 * e + u], qh[kk], bh[e][2 * u], bh[e][2 * u + 1]);
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+#pragma unroll
+          for (int u = 0; u < 2; ++u) f32_mma(s[4 * n2 + 2 * e + u], ql[kk], bh[e][2 * u], bh[e][2 * u + 1]);
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+#pragma unroll
+          for (int u = 0; u < 2; ++u) f32_mma(s[4 * n2 + 2 * e + u], qh[kk], bl[e][2 * u], bl[e][2 * u + 1]);
       }
     }
     const bool ragged = j0 + kAmKeys > S;
@@ -430,21 +440,30 @@ __global__ void __launch_bounds__(128, 3) attn_split_mma_kernel(const bf16* __re
       split_pair(s[2 * k2 + 1][0], s[2 * k2 + 1][1], ph[2], pl[2]);
       split_pair(s[2 * k2 + 1][2], s[2 * k2 + 1][3], ph[3], pl[3]);
 #pragma unroll
-      for (int np = 0; np < 4; ++np) {
-        uint32_t vh[4], vl[4];
+      for (int n2 = 0; n2 < 2; ++n2) {
+        uint32_t vh[2][4], vl[2][4];
         const int mi = lane >> 3;
-        const uint32_t off = (k2 * 16 + (mi & 1) * 8 + (lane & 7)) * kAmPitch + (np * 16 + (mi >> 1) * 8) * 2;
-        f32_ldsm_x4_t(sVh + off, vh);
-        f32_ldsm_x4_t(sVl + off, vl);
 #pragma unroll
-        for (int u = 0; u < 2; ++u) {
-          f32_mma(o[2 * np + u], ph, vh[2 * u], vh[2 * u + 1]);
-          f32_mma(o[2 * np + u], pl, vh[2 * u], vh[2 * u + 1]);
-          f32_mma(o[2 * np + u], ph, vl[2 * u], vl[2 * u + 1]);
+        for (int e = 0; e < 2; ++e) {
+          const int np = 2 * n2 + e;
+          const uint32_t off = (k2 * 16 + (mi & 1) * 8 + (lane & 7)) * kAmPitch + (np * 16 + (mi >> 1) * 8) * 2;
+          f32_ldsm_x4_t(sVh + off, vh[e]);
+          f32_ldsm_x4_t(sVl + off, vl[e]);
         }
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+#pragma unroll
+          for (int u = 0; u < 2; ++u) f32_mma(o[4 * n2 + 2 * e + u], ph, vh[e][2 * u], vh[e][2 * u + 1]);
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+#pragma unroll
+          for (int u = 0; u < 2; ++u) f32_mma(o[4 * n2 + 2 * e + u], pl, vh[e][2 * u], vh[e][2 * u + 1]);
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+#pragma unroll
+          for (int u = 0; u < 2; ++u) f32_mma(o[4 * n2 + 2 * e + u], ph, vl[e][2 * u], vl[e][2 * u + 1]);
       }
     }
-    __syncthreads();   // this stage is refilled by the next iteration's load
   }
 #pragma unroll
   for (int h = 0; h < 2; ++h) {

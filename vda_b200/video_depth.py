@@ -8,6 +8,9 @@ What differs is underneath: every window is a fixed launch sequence of libvda_b2
 GPU; the sequential scale/shift alignment and the cross-fade run as GPU kernels without host
 synchronisation; one device->host copy returns the result.
 """
+import threading
+from concurrent.futures import ThreadPoolExecutor
+
 import numpy as np
 import torch
 from torch import nn
@@ -49,6 +52,15 @@ def randomize_zero_init_(model, seed=0):
         last.weight.abs_()
         last.bias.fill_(0.1)
     return model
+
+
+def _prefault(arr, chunk=16 << 20):
+    """Touch one element per 4 KB page of a freshly allocated array (chunked, so other threads get the GIL)."""
+    flat = arr.reshape(-1)
+    stride = max(1, 4096 // arr.itemsize)
+    per = chunk // arr.itemsize
+    for lo in range(0, flat.size, per):
+        flat[lo:lo + per:stride] = 0
 
 
 def window_frame_indices(n_frames):
@@ -187,7 +199,12 @@ class VideoDepthAnything(nn.Module):
         up = (int(original_height), int(original_width)) if original_width is not None and original_height is not None else None
         out = np.empty((n,) + (up or (h0, w0)), np.float32)
         if parallel.active():
+            # the result array is touched page by page on a helper thread while the GPUs work: first-touch
+            # faults of a fresh GB-sized array would otherwise serialise with the download at the end
+            toucher = threading.Thread(target=_prefault, args=(out,), daemon=True)
+            toucher.start()
             depth = self.infer_video_depth_device(frames, input_size=input_size, device=device, fp32=fp32)
+            toucher.join()
             dl = self._downloader(depth.device, h0, w0, up)
             dl.begin(out)
             for lo in range(0, n, dl.FRAMES):
@@ -327,6 +344,16 @@ def align_windows_device(raw, metric=False, out=None):
     return scan.out
 
 
+_POOL = None
+
+
+def _copy_pool():
+    global _POOL
+    if _POOL is None:
+        _POOL = ThreadPoolExecutor(max_workers=HostDownloader.THREADS)
+    return _POOL
+
+
 class HostDownloader:
     """Device -> host path of the result (video_depth.py:113,162): chunks of <= 32 maps go through a
     two-slot pinned ring on a side stream and are copied into the caller's (pageable) array while the GPU
@@ -334,6 +361,7 @@ class HostDownloader:
     optional bilinear upscale to the caller's plate size runs on the main stream before the copy."""
 
     FRAMES = INFER_LEN
+    THREADS = 4
 
     def __init__(self, dev, h0, w0, up=None):
         self.key = (str(dev), h0, w0, up)
@@ -355,7 +383,13 @@ class HostDownloader:
         if self.pending[t] is not None:
             ev, lo, m = self.pending[t]
             ev.synchronize()
-            self.out[lo:lo + m] = self.ring[t].numpy()[:m]
+            src = self.ring[t].numpy()
+            if m >= 8:      # numpy releases the GIL while copying: a few threads triple the host copy rate
+                cuts = [m * i // self.THREADS for i in range(self.THREADS + 1)]
+                list(_copy_pool().map(lambda i: self.out[lo + cuts[i]:lo + cuts[i + 1]].__setitem__(
+                    slice(None), src[cuts[i]:cuts[i + 1]]), range(self.THREADS)))
+            else:
+                self.out[lo:lo + m] = src[:m]
             self.pending[t] = None
 
     def push(self, src, lo):
