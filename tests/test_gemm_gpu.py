@@ -83,6 +83,24 @@ def test_gemm_gelu_scale_residual_inplace(L):
     _close(out, F.gelu(a.float() @ w.float().T + b))
 
 
+@pytest.mark.parametrize("M,N,K", [
+    (256 * 84, 256, 1024),      # 84 pair tiles on 74 SM pairs: 10 tail tiles, each cut into 4 K ranges
+    (256 * 96 + 77, 256, 4096),  # 97 tiles (ragged last pair): 23 tail tiles x 3 ranges
+    (43840, 1024, 1024),        # encoder proj: 688 tiles, 22 tail tiles x 3 ranges of 5/5/6 K blocks
+])
+def test_gemm_residual_reduce_add_tail_split_k(L, M, N, K):
+    """In-place fp32 residual update x += g*(a@w.T + b) on the CTA-pair kernel where the last, partial wave
+    of tiles is split along K (GemmParams::ksplit): partial sums meet in x through the TMA reduce-add."""
+    a = _rand(M, K, seed=1).bfloat16()
+    w = _rand(N, K, scale=K ** -0.5, seed=2).bfloat16()
+    b, g = _rand(N, seed=3), _rand(N, seed=4)
+    x = _rand(M, N, seed=5)
+    want = x + g * (a.float() @ w.float().T + b)
+    L.gemm(a, w, L.make_epilogue(bias=b, scale=g, res_f32=x, out_f32=x, ldo=N))
+    torch.cuda.synchronize()
+    _close(x, want, 1e-3)
+
+
 def test_gemm_bf16_residuals_and_relu_copy(L):
     M, N, K = 999, 256, 256
     a = _rand(M, K, seed=1).bfloat16()

@@ -32,6 +32,13 @@ int check_cuda(cudaError_t e, const char* what) {
   return set_error(static_cast<int>(e), "%s: %s", what, cudaGetErrorString(e));
 }
 int num_sms() { return g_num_sms; }
+bool pdl_enabled() {
+  static const int on = [] {
+    const char* v = getenv("VDA_PDL");
+    return (v && atoi(v) == 0) ? 0 : 1;
+  }();
+  return on != 0;
+}
 
 static int encode_map(CUtensorMap* tm, CUtensorMapDataType dt, CUtensorMapSwizzle sw, const void* base, int rank,
                       const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box);
@@ -230,6 +237,22 @@ int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, 
     const uint32_t box[2] = {16, 128};
     if ((rc = encode_map(&p.tmD, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, CU_TENSOR_MAP_SWIZZLE_64B, epi->out_f32, 2, dims, str, box)))
       return rc;
+    // Tail split-K: proj / fc2 of the encoder are 688 pair tiles for 74 SM pairs = 9.3 waves, i.e. the
+    // tenth wave keeps 22 pairs busy and 52 idle (7 % of the launch).  Their epilogue is a reduce-add into
+    // the fp32 residual, so the R tiles of the partial wave are cut into ksplit K ranges (one per otherwise
+    // idle pair) whose partial products simply meet in the residual; the bias goes with the first range.
+    // fp32 adds commute, so only the rounding order of those few tiles varies from run to run.
+    const char* kv = getenv("VDA_GEMM_KSPLIT");  // A/B knob: 0 disables
+    if (two && !p.f32_store && epi->act == ACT_NONE && p.sched != 2 && !(kv && atoi(kv) == 0)) {
+      const int tiles = ((p.m_tiles + 1) / 2) * p.n_tiles, nc = g_num_sms / 2;
+      const int rem = tiles % nc;
+      if (tiles > nc && rem) {
+        int ks = nc / rem;
+        if (ks > p.num_k_blocks / 4) ks = p.num_k_blocks / 4;
+        if (ks > 8) ks = 8;
+        if (ks >= 2) p.ksplit = ks, p.tail_begin = tiles - rem;
+      }
+    }
   } else if (p.epi_tma == 2) {
     // QKV: only the Q|K columns [0, 2D) are stored through the map
     const uint64_t dims[2] = {(uint64_t)(epi->store_mode == ST_QKV ? 2 * epi->qkv_d : N), (uint64_t)M};

@@ -139,6 +139,7 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_kernel(const __grid_c
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tmem_S = tmem_base, tmem_O = tmem_base + 128;
+  pdl_sync();
 
   // producer / MMA loops run warp-convergent with single-lane issue (see gemm.cu for why)
   if (warp == 0) {
@@ -359,6 +360,7 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tmem_S = tmem_base, tmem_P = tmem_base + 128, tmem_O = tmem_base + 192;
+  pdl_sync();  // the QKV GEMM's outputs are read from here on
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -657,25 +659,26 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
   const char* ek = getenv("VDA_ATTN_PK");  // packed f32x2 softmax arithmetic
   const int variant = (ev && ev[0] == '1') ? 1 : 2, poly = ep ? atoi(ep) : 8, late = el ? atoi(el) : 1, pk = ek ? atoi(ek) : 1;
   dim3 grid(p.q_tiles, heads, frames);
+  cudaError_t le = cudaSuccess;
   if (variant == 1)
-    attn_fwd_kernel<<<grid, kAttThreads, kAttSmem, static_cast<cudaStream_t>(stream)>>>(p);
+    le = launch_pdl(attn_fwd_kernel, grid, dim3(kAttThreads), kAttSmem, static_cast<cudaStream_t>(stream), p);
   else if (pk && late && poly == 8)
-    attn_fwd_v2_kernel<8, true, true><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+    le = launch_pdl(attn_fwd_v2_kernel<8, true, true>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
   else if (pk && late && poly == 6)
-    attn_fwd_v2_kernel<6, true, true><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+    le = launch_pdl(attn_fwd_v2_kernel<6, true, true>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
   else if (pk && late && poly == 16)
-    attn_fwd_v2_kernel<16, true, true><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+    le = launch_pdl(attn_fwd_v2_kernel<16, true, true>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
   else if (pk && late && poly == 2)
-    attn_fwd_v2_kernel<2, true, true><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+    le = launch_pdl(attn_fwd_v2_kernel<2, true, true>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
   else if (pk && late && poly != 0)
-    attn_fwd_v2_kernel<4, true, true><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+    le = launch_pdl(attn_fwd_v2_kernel<4, true, true>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
   else if (pk && late)
-    attn_fwd_v2_kernel<0, true, true><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+    le = launch_pdl(attn_fwd_v2_kernel<0, true, true>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
   else if (poly != 0)
-    attn_fwd_v2_kernel<4, false><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+    le = launch_pdl(attn_fwd_v2_kernel<4, false>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
   else if (late)
-    attn_fwd_v2_kernel<0, true><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
+    le = launch_pdl(attn_fwd_v2_kernel<0, true>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
   else
-    attn_fwd_v2_kernel<0, false><<<grid, kAttThreads, kA2Smem, static_cast<cudaStream_t>(stream)>>>(p);
-  return check_cuda(cudaGetLastError(), "attn launch");
+    le = launch_pdl(attn_fwd_v2_kernel<0, false>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
+  return check_cuda(le, "attn launch");
 }

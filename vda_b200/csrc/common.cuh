@@ -25,6 +25,35 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// Every kernel of the window / streaming launch sequence is launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization (launch_pdl below): its CTAs may become resident
+// while the previous kernel of the stream is still draining, run their prologue (barrier init, TMEM
+// allocation, descriptor prefetch, index math) and then block in pdl_wait() until the previous grid
+// has completed and its writes are visible.  NOTHING may touch global memory before pdl_wait().
+// pdl_launch_dependents() right after it lets the next kernel do the same behind this one.  The
+// ~270 launches of a window (and the ~300 single-tile launches of a streaming frame) then no longer
+// pay launch latency + prologue one after the other.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_sync() {
+  pdl_wait();
+  pdl_launch_dependents();
+}
+
+bool pdl_enabled();  // api.cu: VDA_PDL=0 turns the launch attribute off (A/B knob)
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid, cfg.blockDim = block, cfg.dynamicSmemBytes = smem, cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr, cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // ---------------------------------------------------------------- mbarrier
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));

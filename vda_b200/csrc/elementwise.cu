@@ -46,6 +46,7 @@ __global__ void layernorm_kernel(const TIn* __restrict__ x, const float* __restr
                                  const float* __restrict__ beta, bf16* __restrict__ out, bf16* __restrict__ out_nope,
                                  const float* __restrict__ pe, int rows, int C, float eps, int S, int skip,
                                  int pe_rows_per_t, int pe_T, int split) {
+  pdl_sync();  // launched with programmatic stream serialization (common.cuh)
   // each lane owns MAXV/2 groups of 4 consecutive channels: 16-byte fp32 loads, 8-byte bf16 stores
   constexpr int kQ = MAXV / 2;
   const int warps_per_block = blockDim.x >> 5;
@@ -151,6 +152,7 @@ __global__ void groupnorm_stats_kernel(const bf16* __restrict__ x, double* __res
 // divisions per element pair, which made it 6x slower than its HBM time).
 __global__ void groupnorm_finalize_kernel(const double* __restrict__ stats, float2* __restrict__ mr, int total, int hw,
                                           int C, float eps) {
+  pdl_sync();  // launched with programmatic stream serialization (common.cuh)
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
   const double n = static_cast<double>(hw) * (C / 32);
@@ -164,6 +166,7 @@ __global__ void groupnorm_finalize_kernel(const double* __restrict__ stats, floa
 __global__ void groupnorm_apply_kernel(const bf16* __restrict__ x, const float2* __restrict__ mr,
                                        const float* __restrict__ gamma, const float* __restrict__ beta,
                                        bf16* __restrict__ out, int hw, int C, int ldx, long long total_oct, int split) {
+  pdl_sync();  // launched with programmatic stream serialization (common.cuh)
   const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= total_oct) return;
   const int c8 = C >> 3;
@@ -211,6 +214,7 @@ __global__ void groupnorm_apply_kernel(const bf16* __restrict__ x, const float2*
 // x fp32 NCHW [frames,3,H,W] -> A bf16 [frames*gh*gw, ldk] with k = (c, kh, kw) (patch_embed.py:66).
 __global__ void patch_im2col_kernel(const float* __restrict__ x, bf16* __restrict__ a, int H, int W, int gh, int gw,
                                     int ldk, int split) {
+  pdl_sync();  // launched with programmatic stream serialization (common.cuh)
   const long long row = blockIdx.x;
   const int f = static_cast<int>(row / (gh * gw));
   const int p = static_cast<int>(row - static_cast<long long>(f) * gh * gw);
@@ -236,6 +240,7 @@ __global__ void patch_im2col_kernel(const float* __restrict__ x, bf16* __restric
 __global__ void add_cls_pos_kernel(const float* __restrict__ patch, const float* __restrict__ cls,
                                    const float* __restrict__ pos, float* __restrict__ tokens, int hw, int D,
                                    long long total4) {
+  pdl_sync();  // launched with programmatic stream serialization (common.cuh)
   const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= total4) return;
   const int d4 = D / 4;
@@ -280,6 +285,7 @@ __device__ __forceinline__ uint4 bil_mix(const uint4& a, const uint4& b, const u
 
 __global__ void __launch_bounds__(256) bilinear_nhwc_kernel(const bf16* __restrict__ x, bf16* __restrict__ out, int h, int w,
                                                             int H, int W, int C, int ldx, int ldo, float sy, float sx) {
+  pdl_sync();  // launched with programmatic stream serialization (common.cuh)
   const int c8 = C >> 3;
   const int px = threadIdx.x / c8;
   const int c = (threadIdx.x - px * c8) << 3;
@@ -374,6 +380,7 @@ __global__ void __launch_bounds__(256) bilinear_split_kernel(const bf16* __restr
 // fp32 single-channel bilinear (video_depth.py:66,111-112), optional ReLU.
 __global__ void bilinear_f32_kernel(const float* __restrict__ x, float* __restrict__ out, int h, int w, int H, int W,
                                     float sy, float sx, int relu, long long total) {
+  pdl_sync();  // launched with programmatic stream serialization (common.cuh)
   const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= total) return;
   const int X = static_cast<int>(idx % W);
@@ -394,6 +401,7 @@ __global__ void bilinear_f32_kernel(const float* __restrict__ x, float* __restri
 // 3x3 stride-2 pad-1 im2col for dpt.py:85-90: x NHWC [n,h,w,C] -> A [n*ho*wo, 9*C], k = (kh,kw,c)
 __global__ void im2col_s2_kernel(const bf16* __restrict__ x, bf16* __restrict__ a, int h, int w, int ho, int wo, int C,
                                  long long total) {
+  pdl_sync();  // launched with programmatic stream serialization (common.cuh)
   const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= total) return;
   const int c8 = C / 8;
@@ -423,16 +431,17 @@ static int launch_ln(const void* x, const float* gamma, const float* beta, void*
                      int rows, int C, float eps, int S, int skip, int pe_rows_per_t, int pe_T, int split, cudaStream_t st) {
   const int warps = 8;
   dim3 grid((rows + warps - 1) / warps), block(warps * 32);
+  cudaError_t le = cudaSuccess;
 #define VDA_LN(MAXV)                                                                                              \
-  layernorm_kernel<TIn, MAXV><<<grid, block, 0, st>>>(static_cast<const TIn*>(x), gamma, beta, static_cast<bf16*>(out), \
-                                                      static_cast<bf16*>(out_nope), pe, rows, C, eps, S, skip,  \
-                                                      pe_rows_per_t, pe_T, split ? C : 0)
+  le = launch_pdl(layernorm_kernel<TIn, MAXV>, grid, block, 0, st, static_cast<const TIn*>(x), gamma, beta,       \
+                  static_cast<bf16*>(out), static_cast<bf16*>(out_nope), pe, rows, C, eps, S, skip, pe_rows_per_t, \
+                  pe_T, split ? C : 0)
   if (C <= 256) VDA_LN(4);
   else if (C <= 512) VDA_LN(8);
   else if (C <= 1024) VDA_LN(16);
   else return set_error(-1, "layernorm: C=%d > 1024 unsupported", C);
 #undef VDA_LN
-  return check_cuda(cudaGetLastError(), "layernorm launch");
+  return check_cuda(le, "layernorm launch");
 }
 
 extern "C" {
@@ -462,28 +471,33 @@ int vda_groupnorm_nhwc(const void* x, int ldx, const float* gamma, const float* 
   groupnorm_stats_kernel<<<grid, threads, 0, st>>>(static_cast<const bf16*>(x), stats_ws, hw, C, ldx, rows_per_block, split);
   // stats_ws: 64*n doubles of sums, reused in place for the 32*n float2 (mean, rstd) pairs behind them
   float2* mr = reinterpret_cast<float2*>(stats_ws + 64 * n) ;
-  groupnorm_finalize_kernel<<<(32 * n + 127) / 128, 128, 0, st>>>(stats_ws, mr, 32 * n, hw, C, eps);
+  rc = check_cuda(cudaGetLastError(), "groupnorm stats launch");  // plain launch: it follows a memset node
+  if (rc) return rc;
+  rc = check_cuda(launch_pdl(groupnorm_finalize_kernel, dim3((32 * n + 127) / 128), dim3(128), 0, st, stats_ws, mr, 32 * n, hw,
+                             C, eps),
+                  "groupnorm finalize launch");
+  if (rc) return rc;
   const long long total = static_cast<long long>(n) * hw * (C / 8);
-  groupnorm_apply_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(
-      static_cast<const bf16*>(x), mr, gamma, beta, static_cast<bf16*>(out), hw, C, ldx, total, split);
-  return check_cuda(cudaGetLastError(), "groupnorm launch");
+  return check_cuda(launch_pdl(groupnorm_apply_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), 0, st,
+                               static_cast<const bf16*>(x), mr, gamma, beta, static_cast<bf16*>(out), hw, C, ldx, total, split),
+                    "groupnorm launch");
 }
 
 int vda_patch_im2col(const float* x, void* a, int frames, int H, int W, int ldk, int split, void* stream) {
   if (!x || !a || H % 14 || W % 14 || ldk < 588 || ldk % 8) return set_error(-1, "vda_patch_im2col: bad arguments");
   const int gh = H / 14, gw = W / 14;
-  patch_im2col_kernel<<<frames * gh * gw, 160, 0, static_cast<cudaStream_t>(stream)>>>(x, static_cast<bf16*>(a), H, W,
-                                                                                       gh, gw, ldk, split);
-  return check_cuda(cudaGetLastError(), "patch_im2col launch");
+  return check_cuda(launch_pdl(patch_im2col_kernel, dim3(frames * gh * gw), dim3(160), 0, static_cast<cudaStream_t>(stream), x,
+                               static_cast<bf16*>(a), H, W, gh, gw, ldk, split),
+                    "patch_im2col launch");
 }
 
 int vda_add_cls_pos(const float* patch, const float* cls, const float* pos, float* tokens, int frames, int hw, int D,
                     void* stream) {
   if (!patch || !cls || !pos || !tokens || D % 4) return set_error(-1, "vda_add_cls_pos: bad arguments");
   const long long total = static_cast<long long>(frames) * (hw + 1) * (D / 4);
-  add_cls_pos_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      patch, cls, pos, tokens, hw, D, total);
-  return check_cuda(cudaGetLastError(), "add_cls_pos launch");
+  return check_cuda(launch_pdl(add_cls_pos_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), 0,
+                               static_cast<cudaStream_t>(stream), patch, cls, pos, tokens, hw, D, total),
+                    "add_cls_pos launch");
 }
 
 int vda_bilinear_nhwc(const void* x, int ldx, void* out, int ldo, int n, int h, int w, int H, int W, int C,
@@ -502,9 +516,9 @@ int vda_bilinear_nhwc(const void* x, int ldx, void* out, int ldo, int n, int h, 
     return check_cuda(cudaGetLastError(), "bilinear_split launch");
   }
   const dim3 grid((W + ppb - 1) / ppb, (H + kBilRows - 1) / kBilRows, n);
-  bilinear_nhwc_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const bf16*>(x), static_cast<bf16*>(out), h, w, H, W, C, ldx, ldo, sy, sx);
-  return check_cuda(cudaGetLastError(), "bilinear_nhwc launch");
+  return check_cuda(launch_pdl(bilinear_nhwc_kernel, grid, dim3(256), 0, static_cast<cudaStream_t>(stream),
+                               static_cast<const bf16*>(x), static_cast<bf16*>(out), h, w, H, W, C, ldx, ldo, sy, sx),
+                    "bilinear_nhwc launch");
 }
 
 int vda_bilinear_f32(const float* x, float* out, int n, int h, int w, int H, int W, int relu, void* stream) {
@@ -512,18 +526,19 @@ int vda_bilinear_f32(const float* x, float* out, int n, int h, int w, int H, int
   const float sy = H > 1 ? static_cast<float>(h - 1) / (H - 1) : 0.f;
   const float sx = W > 1 ? static_cast<float>(w - 1) / (W - 1) : 0.f;
   const long long total = static_cast<long long>(n) * H * W;
-  bilinear_f32_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      x, out, h, w, H, W, sy, sx, relu, total);
-  return check_cuda(cudaGetLastError(), "bilinear_f32 launch");
+  return check_cuda(launch_pdl(bilinear_f32_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), 0,
+                               static_cast<cudaStream_t>(stream), x, out, h, w, H, W, sy, sx, relu, total),
+                    "bilinear_f32 launch");
 }
 
 int vda_im2col_s2(const void* x, void* a, int n, int h, int w, int C, void* stream) {
   if (!x || !a || C % 8) return set_error(-1, "vda_im2col_s2: bad arguments");
   const int ho = (h - 1) / 2 + 1, wo = (w - 1) / 2 + 1;
   const long long total = static_cast<long long>(n) * ho * wo * 9 * (C / 8);
-  im2col_s2_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const bf16*>(x), static_cast<bf16*>(a), h, w, ho, wo, C, total);
-  return check_cuda(cudaGetLastError(), "im2col_s2 launch");
+  return check_cuda(launch_pdl(im2col_s2_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), 0,
+                               static_cast<cudaStream_t>(stream), static_cast<const bf16*>(x), static_cast<bf16*>(a), h, w, ho, wo, C,
+                               total),
+                    "im2col_s2 launch");
 }
 
 }  // extern "C"

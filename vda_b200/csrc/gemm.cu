@@ -122,6 +122,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_sync();  // everything above overlapped the previous kernel's tail; global memory from here on
 
   // ---- halo mode (3x3 convs with few output channels).  Fetching every (tap, channel block) A tile
   // separately pulls each input pixel through L2 nine times; with BN <= 64 there is too little math
@@ -330,6 +331,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
   const int tile_begin = chunked ? cluster_id * chunk : cluster_id;
   const int tile_end = chunked ? min(num_tiles, tile_begin + chunk) : num_tiles;
   const int tile_step = chunked ? 1 : num_clusters;
+  // work units: tiles, with the tiles of the partial last wave cut into ksplit K ranges (round-robin only)
+  const int unit_end = (p.ksplit > 1 && !chunked) ? num_tiles + (num_tiles - p.tail_begin) * (p.ksplit - 1) : tile_end;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmA);
@@ -354,12 +357,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
   cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_sync();  // everything above overlapped the previous kernel's tail; global memory from here on
 
   if (warp == 0) {
     int stage = 0;
     uint32_t phase = 0;
     const int cblocks = (p.a_mode == A_CONV3X3) ? (p.C / kBlockK) : 1;
-    for (int tile = tile_begin; tile < tile_end; tile += tile_step) {
+    for (int v = tile_begin; v < unit_end; v += tile_step) {
+      const WorkUnit u = decode_unit(p, v);
+      const int tile = u.tile;
       const int m2 = tile / p.n_tiles, n_t = tile - m2 * p.n_tiles;
       const int m_t = 2 * m2 + static_cast<int>(rank);
       TileCoord tc = {0, 0, 0};
@@ -368,7 +374,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
         for (int kb = 0; kb < p.num_k_blocks; ++kb) tma_prefetch_2d(&p.tmA, kb * kBlockK, (m_t + 2) * kBlockM);
       }
       __syncwarp();
-      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+      for (int kb = u.kb0; kb < u.kb1; ++kb) {
         mbar_wait(&empty_bar[stage], phase ^ 1);
         uint8_t* sa = smem + stage * Cfg::kStageBytes;
         uint8_t* sb = sa + Cfg::kABytes;
@@ -393,13 +399,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
+      for (int v = tile_begin; v < unit_end; v += tile_step, ++it) {
+        const WorkUnit u = decode_unit(p, v);
         const int as = it & 1;
         const uint32_t aphase = (it >> 1) & 1;
         mbar_wait(&tempty_bar[as], aphase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        for (int kb = u.kb0; kb < u.kb1; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
@@ -408,9 +415,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
           if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < kBlockK / 16; ++k)
-              umma_f16_ss_2cta(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+              umma_f16_ss_2cta(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, ((kb - u.kb0) | k) != 0);
             umma_commit_2cta(&empty_bar[stage]);
-            if (kb == p.num_k_blocks - 1) umma_commit_2cta(&tfull_bar[as]);
+            if (kb == u.kb1 - 1) umma_commit_2cta(&tfull_bar[as]);
           }
           __syncwarp();
           if (++stage == p.stages) stage = 0, phase ^= 1;
@@ -431,14 +438,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
     const bool red_issuer = (et & 127) == 0;
     int box_ctr = 0;
     int it = 0;
-    for (int tile = tile_begin; tile < tile_end; tile += tile_step, ++it) {
+    for (int v = tile_begin; v < unit_end; v += tile_step, ++it) {
+      const WorkUnit u = decode_unit(p, v);
+      const int tile = u.tile;
       const int m2 = tile / p.n_tiles, n_t = tile - m2 * p.n_tiles;
       const int m_t = 2 * m2 + static_cast<int>(rank);
       const int as = it & 1;
       const uint32_t aphase = (it >> 1) & 1;
       float* s_bias = s_epi + as * 2 * BN;
       float* s_scale = s_bias + BN;
-      stage_bias_scale<BN>(p, n_t, et, s_bias, s_scale);
+      stage_bias_scale<BN>(p, n_t, et, s_bias, s_scale, u.kb0 == 0);  // the bias rides with the first K range only
       if (tile + tile_step < tile_end)
         epilogue_prefetch<BN>(p, 2 * ((tile + tile_step) / p.n_tiles) + static_cast<int>(rank),
                               (tile + tile_step) % p.n_tiles, r, half);
@@ -481,8 +490,7 @@ static cudaError_t launch_bn(const GemmParams& p, int num_sms, cudaStream_t stre
   }
   const int tiles = p.m_tiles * p.n_tiles;
   const int grid = tiles < num_sms ? tiles : num_sms;
-  gemm_tc_kernel<BN><<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(p);
-  return cudaGetLastError();
+  return launch_pdl(gemm_tc_kernel<BN>, dim3(grid), dim3(kGemmThreads), Cfg::kSmemBytes, stream, p);
 }
 
 template <int BN>
@@ -497,8 +505,7 @@ static cudaError_t launch2_bn(const GemmParams& p, int num_sms, cudaStream_t str
   const int pairs = ((p.m_tiles + 1) / 2) * p.n_tiles;
   const int max_pairs = num_sms / 2;
   const int grid = 2 * (pairs < max_pairs ? pairs : max_pairs);
-  gemm_tc2_kernel<BN><<<grid, kGemmThreads, Cfg::kSmemBytes, stream>>>(p);  // cluster dims are compiled in
-  return cudaGetLastError();
+  return launch_pdl(gemm_tc2_kernel<BN>, dim3(grid), dim3(kGemmThreads), Cfg::kSmemBytes, stream, p);  // cluster dims are compiled in
 }
 
 cudaError_t launch_gemm(const GemmParams& p, int block_n, bool two_cta, int num_sms, cudaStream_t stream) {

@@ -124,11 +124,12 @@ __device__ __forceinline__ void prefetch_l2(const void* p) {
 // Stage bias/scale of the tile's BN columns into shared memory (called by all 256 epilogue threads,
 // et = 0..255).  s_bias/s_scale: BN floats each, double-buffered by the caller per tile parity.
 template <int BN>
-__device__ __forceinline__ void stage_bias_scale(const GemmParams& p, int n_t, int et, float* s_bias, float* s_scale) {
+__device__ __forceinline__ void stage_bias_scale(const GemmParams& p, int n_t, int et, float* s_bias, float* s_scale,
+                                                 bool with_bias = true) {
   if (et < BN) {
     const int col = n_t * BN + et;
     const bool in = col < p.N;
-    s_bias[et] = (p.bias && in) ? __ldg(p.bias + col) : 0.f;
+    s_bias[et] = (p.bias && in && with_bias) ? __ldg(p.bias + col) : 0.f;
     s_scale[et] = (p.scale && in) ? __ldg(p.scale + col) : 1.f;
   }
   named_bar_sync(1, kEpiThreads);
@@ -245,6 +246,24 @@ __device__ __forceinline__ void epilogue_prefetch(const GemmParams& p, int m_til
 // its residual segments through a private ring of shared-memory slots with cp.async, kRing-1 groups
 // (and across tile boundaries) ahead of their use; slots are thread-private, so no barrier is needed.
 // The ring lives in the smem of GEMM stages that this launch leaves unused (GemmParams::stages).
+// A work unit of the persistent loop: a whole tile, or one K range of a tail tile (GemmParams::ksplit).
+struct WorkUnit {
+  int tile, kb0, kb1;
+};
+__device__ __forceinline__ WorkUnit decode_unit(const GemmParams& p, int v) {
+  WorkUnit u;
+  if (p.ksplit <= 1 || v < p.tail_begin) {
+    u.tile = v, u.kb0 = 0, u.kb1 = p.num_k_blocks;
+  } else {
+    const int t = v - p.tail_begin;
+    const int q = t / p.ksplit, part = t - q * p.ksplit;
+    u.tile = p.tail_begin + q;
+    u.kb0 = part * p.num_k_blocks / p.ksplit;
+    u.kb1 = (part + 1) * p.num_k_blocks / p.ksplit;
+  }
+  return u;
+}
+
 struct TileSched {
   int begin, step, end;  // this CTA's tile sequence
   int m_mul, m_add;      // m_tile = m_mul * (tile / n_tiles) + m_add  (2, rank for CTA pairs)

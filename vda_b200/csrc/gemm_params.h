@@ -33,6 +33,10 @@ struct alignas(64) GemmParams {
   int split;   // > 0: bf16 outputs / residuals are split tensors [hi | lo | hi], parts `split` elements apart
   int stages;  // smem ring depth used by this launch (<= compiled maximum); freed stages hold the residual ring
   int sched;  // tile order: 0 = auto, 1 = round-robin, 2 = contiguous run per CTA (see gemm.cu)
+  // Tail split-K (2-CTA kernel, reduce-add epilogue only): the tiles of the last, partial wave
+  // [tail_begin, tiles) are each cut into `ksplit` K ranges handled by different CTA pairs, whose
+  // partial sums meet in the fp32 residual through the TMA reduce-add.  ksplit <= 1 = off.
+  int ksplit, tail_begin;
   // conv geometry (a_mode == A_CONV3X3): stride 1, pad 1, output map = input map
   int H, W, C;
   int tw_log2;           // spatial tile is TH x TW pixels with TW = 1<<tw_log2, TH = 128/TW

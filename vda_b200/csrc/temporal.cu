@@ -162,6 +162,7 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 
 template <int HDP>  // head_dim rounded up to a multiple of 16
 __global__ void __launch_bounds__(kTWarps * 32) temporal_attn_mma_kernel(const TemporalParams p) {
+  pdl_sync();  // launched with programmatic stream serialization (common.cuh)
   constexpr int kStride = HDP * 2 + 16;  // bytes per staged row
   constexpr int kMat = 32 * kStride;
   constexpr int kChunks = HDP / 8;       // 16-byte chunks per staged row
@@ -316,8 +317,9 @@ static int launch_temporal_mma(const TemporalParams& p, cudaStream_t stream) {
     configured = true;
   }
   const int units = p.hw * p.heads;
-  temporal_attn_mma_kernel<HDP><<<(units + kTWarps - 1) / kTWarps, kTWarps * 32, smem, stream>>>(p);
-  return check_cuda(cudaGetLastError(), "temporal_attn launch");
+  return check_cuda(launch_pdl(temporal_attn_mma_kernel<HDP>, dim3((units + kTWarps - 1) / kTWarps), dim3(kTWarps * 32), smem,
+                               stream, p),
+                    "temporal_attn launch");
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -379,6 +381,7 @@ __device__ __forceinline__ void st8(void* base, long long off, const float (&v)[
 
 template <bool F32>
 __global__ void __launch_bounds__(kTWarps * 32) temporal_attn_stream_kernel(const TemporalStreamParams p) {
+  pdl_sync();  // launched with programmatic stream serialization (common.cuh)
   extern __shared__ __align__(16) uint8_t tsm[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int unit = blockIdx.x * kTWarps + warp;
@@ -480,11 +483,10 @@ static int launch_temporal_stream(bool f32, const void* q, const void* knew, con
     configured = true;
   }
   const int units = hw * heads, grid = (units + kTWarps - 1) / kTWarps;
-  if (f32)
-    temporal_attn_stream_kernel<true><<<grid, kTWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(p);
-  else
-    temporal_attn_stream_kernel<false><<<grid, kTWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(p);
-  return check_cuda(cudaGetLastError(), "temporal_attn_stream launch");
+  const cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return check_cuda(f32 ? launch_pdl(temporal_attn_stream_kernel<true>, dim3(grid), dim3(kTWarps * 32), smem, st, p)
+                        : launch_pdl(temporal_attn_stream_kernel<false>, dim3(grid), dim3(kTWarps * 32), smem, st, p),
+                    "temporal_attn_stream launch");
 }
 
 extern "C" int vda_temporal_attn_stream(const void* q, const void* knew, const void* vnew, int ldn, void* kcache,
