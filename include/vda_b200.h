@@ -19,6 +19,9 @@ extern "C" {
 int vda_init(int device);            /* resolve driver entry points, query SM count; idempotent */
 const char* vda_last_error(void);    /* message of the last failing call on this thread */
 int vda_num_sms(void);
+/* Launch the following kernels with programmatic stream serialization (each kernel's prologue overlaps the
+ * previous kernel's tail; csrc/common.cuh).  Returns the previous setting.  Default 0. */
+int vda_set_pdl(int on);
 
 enum { VDA_ACT_NONE = 0, VDA_ACT_GELU = 1, VDA_ACT_RELU = 2, VDA_ACT_GEGLU = 3 };
 enum { VDA_ST_PLAIN = 0, VDA_ST_CONVT = 1, VDA_ST_QKV = 2, VDA_ST_HEADDOT = 3 };

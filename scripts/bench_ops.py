@@ -58,7 +58,19 @@ oc_x = r(T, 296, 296, 256).to(torch.bfloat16)
 oc_w, oc_b = _P.conv3x3(r(128, 256, 3, 3, sc=2304 ** -0.5), r(128), device=dev)
 oc_y = torch.empty(T, 296, 296, 128, device=dev, dtype=torch.bfloat16)
 
+# reassemble ConvTranspose k=s as GEMM + pixel-shuffle store (dpt.py:60-82): 37x37 tokens, 256 -> 256 x4x4 / 512 -> 512 x2x2
+ct_a0 = r(T * 1369, 256).to(torch.bfloat16)
+ct_w0, ct_b0 = r(16 * 256, 256, sc=1 / 16).to(torch.bfloat16), r(16 * 256)
+ct_o0 = torch.empty(T, 148, 148, 256, device=dev, dtype=torch.bfloat16)
+ct_a1 = r(T * 1369, 512).to(torch.bfloat16)
+ct_w1, ct_b1 = r(4 * 512, 512, sc=1 / 22).to(torch.bfloat16), r(4 * 512)
+ct_o1 = torch.empty(T, 74, 74, 512, device=dev, dtype=torch.bfloat16)
+
 ops = {
+    "ct0": (lambda: L.gemm(ct_a0, ct_w0, L.make_epilogue(bias=ct_b0, out=ct_o0, ldo=256, store_mode=L.ST_CONVT, ct=(4, 256, 37, 37))),
+            2 * T * 1369 * 4096 * 256),
+    "ct1": (lambda: L.gemm(ct_a1, ct_w1, L.make_epilogue(bias=ct_b1, out=ct_o1, ldo=512, store_mode=L.ST_CONVT, ct=(2, 512, 37, 37))),
+            2 * T * 1369 * 2048 * 512),
     "oc1": (lambda: L.conv3x3(oc_x, oc_w, L.make_epilogue(bias=oc_b, out=oc_y, ldo=128), T, 296, 296, 256, 128),
             2 * T * 296 * 296 * 128 * 2304),
     "oc1_1cta": (lambda: L.conv3x3(oc_x, oc_w, L.make_epilogue(bias=oc_b, out=oc_y, ldo=128, cta_pair=1), T, 296, 296, 256, 128),

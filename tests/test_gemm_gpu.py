@@ -129,7 +129,8 @@ def test_gemm_geglu(L):
     _close(out, want)
 
 
-@pytest.mark.parametrize("s,cin,cout,h,w", [(4, 64, 48, 5, 7), (2, 128, 96, 9, 4), (4, 256, 256, 37, 37)])
+@pytest.mark.parametrize("s,cin,cout,h,w", [(4, 64, 48, 5, 7), (2, 128, 96, 9, 4), (4, 256, 256, 37, 37), (2, 128, 64, 9, 4),
+                                             (2, 512, 512, 37, 66), (4, 64, 32, 19, 3)])
 def test_gemm_convtranspose_store(L, s, cin, cout, h, w):
     n = 3
     x = _rand(n, cin, h, w, seed=1).bfloat16()

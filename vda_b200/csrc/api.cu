@@ -32,12 +32,17 @@ int check_cuda(cudaError_t e, const char* what) {
   return set_error(static_cast<int>(e), "%s: %s", what, cudaGetErrorString(e));
 }
 int num_sms() { return g_num_sms; }
+// Programmatic dependent launch (common.cuh).  Measured on B200: inside the CUDA graph of a 32-frame window
+// it is 2 % SLOWER (596 -> 584 frames/s, two interleaved runs each), for the ~300 single-tile launches of a
+// streaming frame 2 % faster (2.215 -> 2.168 ms), so the host turns it on per launch sequence
+// (vda_set_pdl, default off); VDA_PDL=0/1 overrides both ways for A/B runs.
+static int g_pdl = 0;
 bool pdl_enabled() {
-  static const int on = [] {
+  static const int forced = [] {
     const char* v = getenv("VDA_PDL");
-    return (v && atoi(v) == 0) ? 0 : 1;
+    return v ? (atoi(v) != 0 ? 1 : 0) : -1;
   }();
-  return on != 0;
+  return forced >= 0 ? forced != 0 : g_pdl != 0;
 }
 
 static int encode_map(CUtensorMap* tm, CUtensorMapDataType dt, CUtensorMapSwizzle sw, const void* base, int rank,
@@ -125,6 +130,10 @@ static int pick_epi_tma(const vda_epilogue* e, bool conv) {
   if ((e->store_mode == ST_PLAIN || (!conv && e->store_mode == ST_QKV)) && e->out && !e->out_f32 && !e->res_f32 &&
       e->ldo % 8 == 0 && aligned(e->out) && off_lvl != 2)
     return 2;
+  // ConvTranspose pixel-shuffle store: box staging + cooperative scattered store (4 lanes per 64-byte row run)
+  if (!conv && e->store_mode == ST_CONVT && e->out && !e->out_f32 && !e->res_f32 && e->ct_cout % 32 == 0 && e->ldo % 8 == 0 &&
+      aligned(e->out) && off_lvl != 3)
+    return 3;
   return 0;
 }
 
@@ -210,6 +219,11 @@ int vda_init(int device) {
 
 const char* vda_last_error(void) { return g_err; }
 int vda_num_sms(void) { return g_num_sms; }
+int vda_set_pdl(int on) {
+  const int prev = g_pdl;
+  g_pdl = on != 0;
+  return prev;
+}
 
 int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, int K, const vda_epilogue* epi,
                   void* stream) {

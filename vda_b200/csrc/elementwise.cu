@@ -258,33 +258,14 @@ __global__ void add_cls_pos_kernel(const float* __restrict__ patch, const float*
 // ------------------------------------------------------------------ bilinear, align_corners=True, NHWC bf16
 // (util/blocks.py:156-158, dpt_temporal.py:116-118).  HBM-bound: algorithmic bytes = n*(h*w + H*W)*C*2.
 // grid = (x-segments, y-strips, n); a block covers 256/(C/8) consecutive output columns, one thread per
-// (column, 8 channels), and walks kBilRows output rows keeping its two source rows in registers: a
+// (column, 8 channels), and walks a strip of output rows keeping its two source rows in registers: a
 // source row is fetched once per strip instead of once per output row (the one-output-per-thread
 // version moved 4x the output bytes through L2 and ran at 2.4 TB/s).  32-bit index math only.
-constexpr int kBilRows = 8;
-
-__device__ __forceinline__ uint4 bil_mix(const uint4& a, const uint4& b, const uint4& c, const uint4& d, float w00, float w01,
-                                         float w10, float w11) {
-  const uint32_t* pa = &a.x;
-  const uint32_t* pb = &b.x;
-  const uint32_t* pc = &c.x;
-  const uint32_t* pd = &d.x;
-  uint32_t o[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const float2 fa = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(pa + i));
-    const float2 fb = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(pb + i));
-    const float2 fc = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(pc + i));
-    const float2 fd = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(pd + i));
-    const __nv_bfloat162 r = __floats2bfloat162_rn(w00 * fa.x + w01 * fb.x + w10 * fc.x + w11 * fd.x,
-                                                   w00 * fa.y + w01 * fb.y + w10 * fc.y + w11 * fd.y);
-    o[i] = *reinterpret_cast<const uint32_t*>(&r);
-  }
-  return make_uint4(o[0], o[1], o[2], o[3]);
-}
+// Strip height is chosen per launch (32 / 16 / 8 rows: longer strips re-read fewer boundary rows; measured
+// 148^2 -> 296^2 x 256: 359 / 335 / 328 us for 8 / 16 / 32), shorter when the grid would not fill the GPU.
 
 __global__ void __launch_bounds__(256) bilinear_nhwc_kernel(const bf16* __restrict__ x, bf16* __restrict__ out, int h, int w,
-                                                            int H, int W, int C, int ldx, int ldo, float sy, float sx) {
+                                                            int H, int W, int C, int ldx, int ldo, float sy, float sx, int strip) {
   pdl_sync();  // launched with programmatic stream serialization (common.cuh)
   const int c8 = C >> 3;
   const int px = threadIdx.x / c8;
@@ -299,9 +280,28 @@ __global__ void __launch_bounds__(256) bilinear_nhwc_kernel(const bf16* __restri
   const float lx = fx - x0;
   const bf16* base = x + static_cast<long long>(n) * h * w * ldx + c;
   const long long o0 = static_cast<long long>(x0) * ldx, o1 = static_cast<long long>(x1) * ldx;
-  uint4 a = make_uint4(0, 0, 0, 0), b = a, cc = a, d = a;
+  // Separable form: lx is fixed per thread, so each source row is reduced ONCE to its horizontal lerp
+  // h(y) = x[y][x0] + lx * (x[y][x1] - x[y][x0]) (8 channels, fp32 registers) when it is loaded, and an
+  // output row is one vertical lerp h0 + ly * (h1 - h0) of the two rows in registers.  The 4-tap form
+  // unpacked all four bf16 taps again for every output row (~80 instructions per 16-byte store, which made
+  // the kernel issue-bound at ~3.7 TB/s); this needs ~20 per store plus ~35 per source row.
+  float h0[8], h1[8];
+  auto load_row = [&](int y, float (&hh)[8]) {
+    const bf16* r = base + static_cast<long long>(y) * w * ldx;
+    const uint4 p = __ldg(reinterpret_cast<const uint4*>(r + o0));
+    const uint4 q = __ldg(reinterpret_cast<const uint4*>(r + o1));
+    const uint32_t* pp = &p.x;
+    const uint32_t* qq = &q.x;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 fp = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(pp + i));
+      const float2 fq = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(qq + i));
+      hh[2 * i] = fmaf(lx, fq.x - fp.x, fp.x);
+      hh[2 * i + 1] = fmaf(lx, fq.y - fp.y, fp.y);
+    }
+  };
   int cur0 = -1, cur1 = -1;
-  const int Yb = blockIdx.y * kBilRows, Ye = min(Yb + kBilRows, H);
+  const int Yb = blockIdx.y * strip, Ye = min(Yb + strip, H);
   bf16* orow = out + ((static_cast<long long>(n) * H + Yb) * W + X) * ldo + c;
   for (int Y = Yb; Y < Ye; ++Y, orow += static_cast<long long>(W) * ldo) {
     const float fy = sy * Y;
@@ -310,26 +310,30 @@ __global__ void __launch_bounds__(256) bilinear_nhwc_kernel(const bf16* __restri
     const float ly = fy - y0;
     if (y0 != cur0) {
       if (y0 == cur1) {
-        a = cc, b = d;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) h0[i] = h1[i];
       } else {
-        const bf16* r0 = base + static_cast<long long>(y0) * w * ldx;
-        a = __ldg(reinterpret_cast<const uint4*>(r0 + o0));
-        b = __ldg(reinterpret_cast<const uint4*>(r0 + o1));
+        load_row(y0, h0);
       }
       cur0 = y0;
     }
     if (y1 != cur1) {
       if (y1 == y0) {
-        cc = a, d = b;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) h1[i] = h0[i];
       } else {
-        const bf16* r1 = base + static_cast<long long>(y1) * w * ldx;
-        cc = __ldg(reinterpret_cast<const uint4*>(r1 + o0));
-        d = __ldg(reinterpret_cast<const uint4*>(r1 + o1));
+        load_row(y1, h1);
       }
       cur1 = y1;
     }
-    __stcs(reinterpret_cast<uint4*>(orow),
-           bil_mix(a, b, cc, d, (1.f - ly) * (1.f - lx), (1.f - ly) * lx, ly * (1.f - lx), ly * lx));
+    uint32_t o[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const __nv_bfloat162 r2 = __floats2bfloat162_rn(fmaf(ly, h1[2 * i] - h0[2 * i], h0[2 * i]),
+                                                      fmaf(ly, h1[2 * i + 1] - h0[2 * i + 1], h0[2 * i + 1]));
+      o[i] = *reinterpret_cast<const uint32_t*>(&r2);
+    }
+    __stcs(reinterpret_cast<uint4*>(orow), make_uint4(o[0], o[1], o[2], o[3]));
   }
 }
 
@@ -515,9 +519,11 @@ int vda_bilinear_nhwc(const void* x, int ldx, void* out, int ldo, int n, int h, 
         static_cast<const bf16*>(x), static_cast<bf16*>(out), h, w, H, W, C, ldx, ldo, split_in, split_out, sy, sx);
     return check_cuda(cudaGetLastError(), "bilinear_split launch");
   }
-  const dim3 grid((W + ppb - 1) / ppb, (H + kBilRows - 1) / kBilRows, n);
+  int strip = 32;
+  while (strip > 8 && static_cast<long long>((W + ppb - 1) / ppb) * ((H + strip - 1) / strip) * n < 2048) strip >>= 1;
+  const dim3 grid((W + ppb - 1) / ppb, (H + strip - 1) / strip, n);
   return check_cuda(launch_pdl(bilinear_nhwc_kernel, grid, dim3(256), 0, static_cast<cudaStream_t>(stream),
-                               static_cast<const bf16*>(x), static_cast<bf16*>(out), h, w, H, W, C, ldx, ldo, sy, sx),
+                               static_cast<const bf16*>(x), static_cast<bf16*>(out), h, w, H, W, C, ldx, ldo, sy, sx, strip),
                     "bilinear_nhwc launch");
 }
 

@@ -24,6 +24,7 @@
 namespace vda {
 
 constexpr int kGemmThreads = 128 + kEpiThreads;  // 4 control warps + epilogue warps
+constexpr int kRowOffBytes = 2 * kBlockM * 8;     // epilogue MODE 3: output row offsets x 2 tile parities
 
 template <int BN>
 struct GemmCfg {
@@ -37,7 +38,7 @@ struct GemmCfg {
   static constexpr int kHaloStageBytes = 23 * 1024 + 9 * BN * kBlockK * 2;
   static constexpr int kHaloStages = BN <= 32 ? 3 : (BN <= 64 ? 2 : 0);
   static constexpr int kRingBytes = (kStages * kStageBytes > kHaloStages * kHaloStageBytes) ? kStages * kStageBytes : kHaloStages * kHaloStageBytes;
-  static constexpr int kSmemBytes = kRingBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kBiasBytes;
+  static constexpr int kSmemBytes = kRingBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kBiasBytes + kRowOffBytes;
 };
 
 template <int BN>
@@ -48,7 +49,7 @@ struct Gemm2Cfg {
   static constexpr int kStages = (BN >= 256) ? 6 : 8;
   static constexpr int kTmemCols = GemmCfg<BN>::kTmemCols;
   static constexpr int kBiasBytes = 2 * 2 * BN * 4;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kBiasBytes;
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kBiasBytes + kRowOffBytes;
 };
 
 // halo mode of the 1-CTA kernel: patch of an 8 x 16-pixel tile plus a 1-pixel border, one 64-channel block
@@ -269,6 +270,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
       const uint32_t aphase = (it >> 1) & 1;
       float* s_bias = s_epi + as * 2 * BN;
       float* s_scale = s_bias + BN;
+      long long* s_rowoff = reinterpret_cast<long long*>(s_epi + 4 * BN) + as * kBlockM;
+      stage_row_offsets(p, m_t, et, s_rowoff);
       stage_bias_scale<BN>(p, n_t, et, s_bias, s_scale);
       if (tile + tile_step < tile_end)  // residual rows of the NEXT tile into L2: a whole tile of lead time
         epilogue_prefetch<BN>(p, (tile + tile_step) / p.n_tiles, (tile + tile_step) % p.n_tiles, r, half);
@@ -281,6 +284,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         epilogue_tile_box<BN, 1>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer);
       else if (p.epi_tma == 2 && !v_tile)
         epilogue_tile_box<BN, 2>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer);
+      else if (p.epi_tma == 3)
+        epilogue_tile_box<BN, 3>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer, s_rowoff);
       else
         epilogue_tile<BN>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, ts, rr, it);
       tc_fence_before();
@@ -447,6 +452,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
       const uint32_t aphase = (it >> 1) & 1;
       float* s_bias = s_epi + as * 2 * BN;
       float* s_scale = s_bias + BN;
+      long long* s_rowoff = reinterpret_cast<long long*>(s_epi + 4 * BN) + as * kBlockM;
+      stage_row_offsets(p, m_t, et, s_rowoff);
       stage_bias_scale<BN>(p, n_t, et, s_bias, s_scale, u.kb0 == 0);  // the bias rides with the first K range only
       if (tile + tile_step < tile_end)
         epilogue_prefetch<BN>(p, 2 * ((tile + tile_step) / p.n_tiles) + static_cast<int>(rank),
@@ -460,6 +467,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
         epilogue_tile_box<BN, 1>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer);
       else if (p.epi_tma == 2 && !v_tile)
         epilogue_tile_box<BN, 2>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer);
+      else if (p.epi_tma == 3)
+        epilogue_tile_box<BN, 3>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer, s_rowoff);
       else
         epilogue_tile<BN>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, ts, rr, it);
       tc_fence_before();

@@ -350,13 +350,33 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, uint32_t src_
                : "memory");
 }
 
+// Output element offset of every row of a tile for the scattered stores of MODE 3 (-1 = row not stored),
+// computed once per tile by the first 128 epilogue threads into a table double-buffered by tile parity.
+__device__ __forceinline__ void stage_row_offsets(const GemmParams& p, int m_tile, int et, long long* s_rowoff) {
+  if (p.epi_tma != 3 || et >= kBlockM) return;
+  const RowMap rm = map_row(p, m_tile, et);
+  long long off = -1;
+  if (rm.valid) {
+    // ST_CONVT: input pixel (n, ih, iw) -> output pixel (n, ih*s, iw*s); the tap (kh, kw) is added per box
+    const int hw = p.ct_h * p.ct_w;
+    const int m = static_cast<int>(rm.row);
+    const int n = m / hw, rem = m - n * hw;
+    const int ih = rem / p.ct_w, iw = rem - ih * p.ct_w;
+    off = ((static_cast<long long>(n) * p.ct_h * p.ct_s + ih * p.ct_s) * (p.ct_w * p.ct_s) + iw * p.ct_s) * p.ldo;
+  }
+  s_rowoff[et] = off;
+}
+
 // Box epilogues.  MODE 1: fp32 reduce-add, 16 columns per box.  MODE 2: bf16 store, 32 columns per
 // box (same 64-byte rows, SWIZZLE_64B; conv tiles use a 4-D map whose box is the tile's pixel patch).
+// MODE 3: bf16 box as MODE 2, but written out by the slice's 128 threads themselves, four lanes per
+// 64-byte row segment, to rows given by a per-tile offset table: for stores TMA cannot express as one box
+// (ConvTranspose pixel shuffle).  A warp store then touches 8 lines instead of 32 (thread = row).
 // `box_base`: shared address of this column slice's 3 boxes; `box_ctr`: running box counter of the slice.
 template <int BN, int MODE>
 __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_tile, int n_t, uint32_t t_acc, int r, int half,
                                                   const float* s_bias, const float* s_scale, uint32_t box_base, int& box_ctr,
-                                                  bool issuer) {
+                                                  bool issuer, const long long* s_rowoff = nullptr) {
   constexpr int kPer = EpiSlice<BN>::kPer;
   constexpr int kCols = MODE == 1 ? 16 : 32;
   const int cbeg = half * kPer;
@@ -413,6 +433,29 @@ __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_til
       asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(rowaddr + ((static_cast<uint32_t>(c) ^ sw) << 4)),
                    "r"(pk[4 * c]), "r"(pk[4 * c + 1]), "r"(pk[4 * c + 2]), "r"(pk[4 * c + 3])
                    : "memory");
+    if constexpr (MODE == 3) {
+      named_bar_sync(2 + half, 128);
+      if (col < p.N) {
+        const int gg = col / p.ct_cout, co = col - gg * p.ct_cout;
+        const int kh = gg / p.ct_s, kw = gg - kh * p.ct_s;
+        const long long tapoff = (static_cast<long long>(kh) * (p.ct_w * p.ct_s) + kw) * p.ldo + co;
+        const uint32_t chunk = static_cast<uint32_t>(r) & 3;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint32_t row = (static_cast<uint32_t>(r) >> 2) + 32 * i;
+          const long long ro = s_rowoff[row];
+          uint4 v;
+          asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                       : "r"(box + row * 64 + ((chunk ^ ((row >> 1) & 3)) << 4)));
+          if (ro >= 0) *reinterpret_cast<uint4*>(p.out + ro + tapoff + chunk * 8) = v;
+        }
+      }
+      // box reuse: a thread writes box k+3 only after the barrier of box k+2, which every thread joins
+      // after it has finished copying box k+1 (and k) out
+      ++box_ctr;
+      continue;
+    }
     fence_proxy_async_smem();
     named_bar_sync(2 + half, 128);
     if (issuer) {

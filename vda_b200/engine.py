@@ -412,8 +412,14 @@ class Engine:
     def _run(self, x, ws, stream_ctx):
         T, _, H, W = x.shape
         n0 = L.LAUNCHES
-        taps = self.encoder(x, ws)
-        out = self.head(taps, H // PATCH, W // PATCH, T, ws, stream_ctx=stream_ctx)
+        # Programmatic dependent launch only for the latency-bound single-frame sequence of the streaming mode
+        # (~300 launches of one tile each: -2 % per frame); on a full window it costs 2 % (csrc/api.cu).
+        prev = L.set_pdl(stream_ctx is not None)
+        try:
+            taps = self.encoder(x, ws)
+            out = self.head(taps, H // PATCH, W // PATCH, T, ws, stream_ctx=stream_ctx)
+        finally:
+            L.set_pdl(prev)
         self.launches_per_run[("win", T, H, W)] = L.LAUNCHES - n0
         return out
 

@@ -87,6 +87,7 @@ def _declare(lib):
     sig = {
         "vda_init": [i],
         "vda_num_sms": [],
+        "vda_set_pdl": [i],
         "vda_gemm_bf16": [vp, i, vp, i, i, i, i, ep, vp],
         "vda_conv3x3_nhwc": [vp, i, vp, i, i, i, i, i, ep, vp],
         "vda_flash_attn_fwd": [vp, vp, vp, i, i, i, i, vp],
@@ -118,6 +119,11 @@ def _declare(lib):
         fn.argtypes = args
         fn.restype = i
     return sig
+
+
+def set_pdl(on):
+    """Programmatic dependent launch for the launches that follow (csrc/common.cuh); returns the previous setting."""
+    return bool(load().vda_set_pdl(int(bool(on))))
 
 
 def exported_symbols():
