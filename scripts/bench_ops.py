@@ -66,7 +66,16 @@ ct_a1 = r(T * 1369, 512).to(torch.bfloat16)
 ct_w1, ct_b1 = r(4 * 512, 512, sc=1 / 22).to(torch.bfloat16), r(4 * 512)
 ct_o1 = torch.empty(T, 74, 74, 512, device=dev, dtype=torch.bfloat16)
 
+# motion module 3 (74x74 tokens, C=256): K = 256 GEMMs, epilogue-bound
+m3_a = r(T * 5476, 256).to(torch.bfloat16)
+m3_wqkv = r(768, 256, sc=1 / 16).to(torch.bfloat16)
+m3_qkv = torch.empty(T * 5476, 768, device=dev, dtype=torch.bfloat16)
+m3_wo, m3_bo = r(256, 256, sc=1 / 16).to(torch.bfloat16), r(256)
+m3_h = r(T * 5476, 256)
+
 ops = {
+    "mm3_qkv": (lambda: L.gemm(m3_a, m3_wqkv, L.make_epilogue(out=m3_qkv, ldo=768)), 2 * T * 5476 * 768 * 256),
+    "mm3_out": (lambda: L.gemm(m3_a, m3_wo, L.make_epilogue(bias=m3_bo, res_f32=m3_h, out_f32=m3_h, ldo=256)), 2 * T * 5476 * 256 * 256),
     "ct0": (lambda: L.gemm(ct_a0, ct_w0, L.make_epilogue(bias=ct_b0, out=ct_o0, ldo=256, store_mode=L.ST_CONVT, ct=(4, 256, 37, 37))),
             2 * T * 1369 * 4096 * 256),
     "ct1": (lambda: L.gemm(ct_a1, ct_w1, L.make_epilogue(bias=ct_b1, out=ct_o1, ldo=512, store_mode=L.ST_CONVT, ct=(2, 512, 37, 37))),

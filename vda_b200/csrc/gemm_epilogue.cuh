@@ -381,16 +381,19 @@ __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_til
   constexpr int kCols = MODE == 1 ? 16 : 32;
   const int cbeg = half * kPer;
   if (cbeg >= BN) return;
+  // The accumulator chunk of box k+1 is requested as soon as the registers of chunk k have been packed, so
+  // its TMEM latency runs under the shared-memory writes, the barrier and the TMA issue of box k (with a
+  // K = 256 GEMM the MMAs of a tile take 2048 clk and eight strictly serial boxes did not fit under them).
+  uint32_t raw[kCols];
+  __syncwarp();
+  if constexpr (MODE == 1) {
+    tmem_ld16(t_acc + cbeg, raw);
+  } else {
+    tmem_ld32(t_acc + cbeg, raw);
+  }
 #pragma unroll 1
   for (int c0 = cbeg; c0 < cbeg + kPer; c0 += kCols) {
     const int col = n_t * BN + c0;
-    uint32_t raw[kCols];
-    __syncwarp();
-    if constexpr (MODE == 1) {
-      tmem_ld16(t_acc + c0, raw);
-    } else {
-      tmem_ld32(t_acc + c0, raw);
-    }
     tmem_ld_wait();
     uint32_t pk[16];  // 64 bytes of this row: 16 fp32 or 32 bf16
 #pragma unroll
@@ -421,6 +424,14 @@ __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_til
           __nv_bfloat162 h2 = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
           pk[8 * g + i] = *reinterpret_cast<uint32_t*>(&h2);
         }
+      }
+    }
+    if (c0 + kCols < cbeg + kPer) {  // raw is dead: fetch the next chunk behind the rest of this box
+      __syncwarp();
+      if constexpr (MODE == 1) {
+        tmem_ld16(t_acc + c0 + kCols, raw);
+      } else {
+        tmem_ld32(t_acc + c0 + kCols, raw);
       }
     }
     // box (box_ctr % 3) is free: its previous store (3 boxes ago) was confirmed read by the issuer
