@@ -73,7 +73,11 @@ m3_qkv = torch.empty(T * 5476, 768, device=dev, dtype=torch.bfloat16)
 m3_wo, m3_bo = r(256, 256, sc=1 / 16).to(torch.bfloat16), r(256)
 m3_h = r(T * 5476, 256)
 
+m3_wg, m3_bg = r(2048, 256, sc=1 / 16).to(torch.bfloat16), r(2048)
+m3_g = torch.empty(T * 5476, 1024, device=dev, dtype=torch.bfloat16)
+
 ops = {
+    "mm3_geglu": (lambda: L.gemm(m3_a, m3_wg, L.make_epilogue(bias=m3_bg, out=m3_g, ldo=1024, act=L.ACT_GEGLU)), 2 * T * 5476 * 2048 * 256),
     "mm3_qkv": (lambda: L.gemm(m3_a, m3_wqkv, L.make_epilogue(out=m3_qkv, ldo=768)), 2 * T * 5476 * 768 * 256),
     "mm3_out": (lambda: L.gemm(m3_a, m3_wo, L.make_epilogue(bias=m3_bo, res_f32=m3_h, out_f32=m3_h, ldo=256)), 2 * T * 5476 * 256 * 256),
     "ct0": (lambda: L.gemm(ct_a0, ct_w0, L.make_epilogue(bias=ct_b0, out=ct_o0, ldo=256, store_mode=L.ST_CONVT, ct=(4, 256, 37, 37))),

@@ -115,8 +115,9 @@ def test_gemm_bf16_residuals_and_relu_copy(L):
     _close(out_relu, want.relu())
 
 
-def test_gemm_geglu(L):
-    M, C = 1500, 256
+@pytest.mark.parametrize("M,C", [(1500, 256), (256 * 80 + 5, 256), (5000, 64), (300, 1024)])
+def test_gemm_geglu(L, M, C):
+    """value * gelu(gate) epilogue: box path on the 1-CTA (BN=128) and CTA-pair (BN=256) kernels, generic path for BN=64."""
     a = _rand(M, C, seed=1).bfloat16()
     w = _rand(8 * C, C, scale=C ** -0.5, seed=2).bfloat16()
     b = _rand(8 * C, seed=3)
@@ -124,7 +125,7 @@ def test_gemm_geglu(L):
     want = want[:, :4 * C] * F.gelu(want[:, 4 * C:])
     # interleave value/gate rows in groups of 16 (what the weight repack does)
     idx = torch.arange(8 * C, device="cuda").view(2, 4 * C // 16, 16).permute(1, 0, 2).reshape(-1)
-    out = torch.empty(M, 4 * C, device="cuda", dtype=torch.bfloat16)
+    out = torch.full((M, 4 * C), float("nan"), device="cuda", dtype=torch.bfloat16)
     L.gemm(a, w[idx].contiguous(), L.make_epilogue(bias=b[idx].contiguous(), out=out, ldo=4 * C, act=L.ACT_GEGLU))
     _close(out, want)
 

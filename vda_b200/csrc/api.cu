@@ -121,7 +121,12 @@ static int pick_epi_tma(const vda_epilogue* e, bool conv) {
   const char* ev = getenv("VDA_GEMM_NO_TMA_EPI");  // A/B knob: 1 disables all, 2 disables the bf16 store flavour
   const int off_lvl = ev ? atoi(ev) : 0;
   const bool off = off_lvl == 1;
-  if (off || e->act == ACT_GEGLU || e->out_relu || e->res1 || e->res2 || e->split) return 0;
+  if (off || e->out_relu || e->res1 || e->res2 || e->split) return 0;
+  if (e->act == ACT_GEGLU) {  // value * gelu(gate) pairs -> bf16 boxes of 32 outputs (64 accumulator columns)
+    const bool ok = !conv && e->store_mode == ST_PLAIN && e->out && !e->out_f32 && !e->res_f32 && e->ldo % 8 == 0 &&
+                    (reinterpret_cast<uintptr_t>(e->out) & 15) == 0 && off_lvl != 4;
+    return ok ? 4 : 0;
+  }
   const auto aligned = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
   const int ldf = e->ld32 ? e->ld32 : e->ldo;
   if (!conv && e->store_mode == ST_PLAIN && e->out_f32 && !e->out && ldf % 4 == 0 && aligned(e->out_f32) &&
@@ -242,6 +247,7 @@ int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, 
   pick_tile(epi, N, p.m_tiles, &bn, &two);
   p.n_tiles = (N + bn - 1) / bn;
   p.epi_tma = pick_epi_tma(epi, false);
+  if (p.epi_tma == 4 && bn < 128) p.epi_tma = 0;  // a GEGLU box spans 64 accumulator columns of one column slice
   p.stages = pick_stages(bn, two, epi, p.epi_tma);
   if (p.epi_tma == 1) {
     const char* rs = getenv("VDA_GEMM_RED_AS_STORE");  // knob for timing experiments only (drops the residual)
@@ -267,9 +273,9 @@ int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, 
         if (ks >= 2) p.ksplit = ks, p.tail_begin = tiles - rem;
       }
     }
-  } else if (p.epi_tma == 2) {
-    // QKV: only the Q|K columns [0, 2D) are stored through the map
-    const uint64_t dims[2] = {(uint64_t)(epi->store_mode == ST_QKV ? 2 * epi->qkv_d : N), (uint64_t)M};
+  } else if (p.epi_tma == 2 || p.epi_tma == 4) {
+    // QKV: only the Q|K columns [0, 2D) are stored through the map; GEGLU: N/2 output columns
+    const uint64_t dims[2] = {(uint64_t)(epi->store_mode == ST_QKV ? 2 * epi->qkv_d : p.n_out), (uint64_t)M};
     const uint64_t str[1] = {(uint64_t)epi->ldo * 2};
     const uint32_t box[2] = {32, 128};
     if ((rc = encode_map(&p.tmD, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, CU_TENSOR_MAP_SWIZZLE_64B, epi->out, 2, dims, str, box)))

@@ -286,6 +286,8 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         epilogue_tile_box<BN, 2>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer);
       else if (p.epi_tma == 3)
         epilogue_tile_box<BN, 3>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer, s_rowoff);
+      else if (p.epi_tma == 4)
+        epilogue_tile_box<BN, 4>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer);
       else
         epilogue_tile<BN>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, ts, rr, it);
       tc_fence_before();
@@ -469,6 +471,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
         epilogue_tile_box<BN, 2>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer);
       else if (p.epi_tma == 3)
         epilogue_tile_box<BN, 3>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer, s_rowoff);
+      else if (p.epi_tma == 4)
+        epilogue_tile_box<BN, 4>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer);
       else
         epilogue_tile<BN>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, ts, rr, it);
       tc_fence_before();

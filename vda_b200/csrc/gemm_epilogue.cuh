@@ -378,13 +378,13 @@ __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_til
                                                   const float* s_bias, const float* s_scale, uint32_t box_base, int& box_ctr,
                                                   bool issuer, const long long* s_rowoff = nullptr) {
   constexpr int kPer = EpiSlice<BN>::kPer;
-  constexpr int kCols = MODE == 1 ? 16 : 32;
+  constexpr int kCols = MODE == 1 ? 16 : (MODE == 4 ? 64 : 32);  // accumulator columns per box
   const int cbeg = half * kPer;
   if (cbeg >= BN) return;
   // The accumulator chunk of box k+1 is requested as soon as the registers of chunk k have been packed, so
   // its TMEM latency runs under the shared-memory writes, the barrier and the TMA issue of box k (with a
   // K = 256 GEMM the MMAs of a tile take 2048 clk and eight strictly serial boxes did not fit under them).
-  uint32_t raw[kCols];
+  uint32_t raw[MODE == 4 ? 32 : kCols];
   __syncwarp();
   if constexpr (MODE == 1) {
     tmem_ld16(t_acc + cbeg, raw);
@@ -396,8 +396,32 @@ __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_til
     const int col = n_t * BN + c0;
     tmem_ld_wait();
     uint32_t pk[16];  // 64 bytes of this row: 16 fp32 or 32 bf16
+    if constexpr (MODE == 4) {
+      // GEGLU: accumulator columns [32j, 32j+16) = value, [32j+16, 32j+32) = gate -> 16 outputs; a box
+      // takes 64 accumulator columns = 32 bf16 outputs, at output column col / 2 (weight rows are packed
+      // in 16-row value / gate groups, vda_b200/packing.py)
 #pragma unroll
-    for (int g = 0; g < kCols / 16; ++g) {
+      for (int g = 0; g < 2; ++g) {
+        float b[16], bg[16];
+        lds_f32x16(s_bias + c0 + 32 * g, b);
+        lds_f32x16(s_bias + c0 + 32 * g + 16, bg);
+#pragma unroll
+        for (int i = 0; i < 16; i += 2) {
+          float g0 = __uint_as_float(raw[16 + i]) + bg[i], g1 = __uint_as_float(raw[16 + i + 1]) + bg[i + 1];
+          gelu_fast2(g0, g1);
+          __nv_bfloat162 h2 = __floats2bfloat162_rn((__uint_as_float(raw[i]) + b[i]) * g0,
+                                                    (__uint_as_float(raw[i + 1]) + b[i + 1]) * g1);
+          pk[8 * g + (i >> 1)] = *reinterpret_cast<uint32_t*>(&h2);
+        }
+        if (g == 0 || c0 + kCols < cbeg + kPer) {  // second half of this box / first half of the next
+          __syncwarp();
+          tmem_ld32(t_acc + c0 + 32 * (g + 1), raw);
+          if (g == 0) tmem_ld_wait();
+        }
+      }
+    }
+#pragma unroll
+    for (int g = 0; g < (MODE == 4 ? 0 : kCols / 16); ++g) {
       float b[16], v[16];
       lds_f32x16(s_bias + c0 + 16 * g, b);
 #pragma unroll
@@ -426,11 +450,11 @@ __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_til
         }
       }
     }
-    if (c0 + kCols < cbeg + kPer) {  // raw is dead: fetch the next chunk behind the rest of this box
+    if (MODE != 4 && c0 + kCols < cbeg + kPer) {  // raw is dead: fetch the next chunk behind the rest of this box
       __syncwarp();
       if constexpr (MODE == 1) {
         tmem_ld16(t_acc + c0 + kCols, raw);
-      } else {
+      } else if constexpr (MODE != 4) {
         tmem_ld32(t_acc + c0 + kCols, raw);
       }
     }
@@ -483,7 +507,7 @@ __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_til
           const int ty = t / p.tiles_w, tx = t - ty * p.tiles_w;
           tma_store_4d(&p.tmD, box, col, tx << p.tw_log2, ty * (kBlockM >> p.tw_log2), img);
         } else {
-          tma_store_2d(&p.tmD, box, col, m_tile * kBlockM);
+          tma_store_2d(&p.tmD, box, MODE == 4 ? (col >> 1) : col, m_tile * kBlockM);
         }
       }
       bulk_commit();
