@@ -29,6 +29,7 @@ if ROOT not in sys.path:
 
 METRIC = "frames/sec VDA-L 518x518 32-frame windows"
 UNIT = "frames/s"
+NCU_FC1 = "r01c_ncu_fc1.json"   # ncu --set full capture of the fc1 launch the roofline's `traffic` is read from
 
 
 def parse():
@@ -180,8 +181,16 @@ def ncu_traffic():
     """DRAM bytes (read + write) of the largest plain-GEMM launch (vitl fc1) from the committed
     `ncu --set full` capture under profiles/ -- a profiler artefact, not measured in this run."""
     try:
-        d = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_fc1_gemm_tc2.json")))
-        mb = lambda k: float(d[k].split()[0]) * 1e6
+        d = json.load(open(os.path.join(ROOT, "profiles", NCU_FC1)))
+
+        def mb(k):
+            v = d[k]
+            if isinstance(v, dict):
+                scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[v["unit"]]
+                return float(v["value"]) * scale
+            num, unit = v.split()
+            return float(num) * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[unit]
+
         alg = sum(d["algorithmic_bytes"].values())
         return mb("dram__bytes_read.sum") + mb("dram__bytes_write.sum"), alg
     except Exception:
@@ -308,7 +317,7 @@ def run_ours(a):
                      "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s", "frac": achieved / tf_peak,
                      "traffic": ncu_traffic()[0], "traffic_algorithmic_bytes": ncu_traffic()[1],
                      "traffic_note": "DRAM read+write bytes of one fc1 launch (M=43840,N=4096,K=1024), ncu --set full, "
-                                     "profiles/r01_ncu_fc1_gemm_tc2.json",
+                                     f"profiles/{NCU_FC1}",
                      "peak_source": peak_src, "launches": n_g,
                      "flops_per_launch": f_g / n_g, "ms_per_launch": t_g / n_g},
         "breakdown_ms_per_step": {k: v[2] / a.steps for k, v in kinds.items()},
