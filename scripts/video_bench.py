@@ -25,6 +25,7 @@ ap.add_argument("--width", type=int, default=518)
 ap.add_argument("--input-size", type=int, default=518)
 ap.add_argument("--metric", action="store_true")
 ap.add_argument("--reps", type=int, default=2)
+ap.add_argument("--result-rank", default="all", help="all: every rank returns the full result; 0: only rank 0 does; both: time one after the other")
 a = ap.parse_args()
 
 world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -45,23 +46,28 @@ for t in range(a.frames):
     base = 127 + 90 * np.sin((xx + 3 * t) / 37) * np.cos((yy - 2 * t) / 29)
     frames[t] = np.clip(base[..., None] + rng.integers(-12, 13, (a.height, a.width, 3)), 0, 255).astype(np.uint8)
 
-times = []
-for rep in range(a.reps + 1):
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    depth, _ = model.infer_video_depth(frames, 24, input_size=a.input_size, device="cuda")
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    times.append(time.perf_counter() - t0)
-best = min(times[1:])
-if rank == 0:
-    n_win = len(window_frame_indices(a.frames))
-    print(json.dumps({"workload": f"infer_video_depth {a.arch} {a.frames} frames {a.height}x{a.width} metric={a.metric}",
-                      "n_gpus": world, "windows": n_win, "seconds": best, "video_frames_per_s": a.frames / best,
-                      "window_frames_per_s": 32 * n_win / best, "all_runs_s": times,
-                      "depth_shape": list(depth.shape), "depth_range": [float(depth.min()), float(depth.max())]}), flush=True)
+from vda_b200 import parallel
+
+modes = ["all", "0"] if a.result_rank == "both" else [a.result_rank]
+for mode in modes:
+    parallel.set_result_rank(None if mode == "all" else int(mode))
+    times = []
+    for rep in range(a.reps + 1):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        depth, _ = model.infer_video_depth(frames, 24, input_size=a.input_size, device="cuda")
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        times.append(time.perf_counter() - t0)
+    best = min(times[1:])
+    if rank == 0:
+        n_win = len(window_frame_indices(a.frames))
+        print(json.dumps({"workload": f"infer_video_depth {a.arch} {a.frames} frames {a.height}x{a.width} metric={a.metric}",
+                          "n_gpus": world, "result_rank": mode, "windows": n_win, "seconds": best,
+                          "video_frames_per_s": a.frames / best, "window_frames_per_s": 32 * n_win / best, "all_runs_s": times,
+                          "depth_shape": list(depth.shape), "depth_range": [float(depth.min()), float(depth.max())]}), flush=True)
 if world > 1:
     dist.destroy_process_group()

@@ -71,3 +71,38 @@ def test_distributed_driver_equals_single_process(world, n_frames):
     for r in range(world):
         assert res[r].shape == want.shape
         np.testing.assert_array_equal(res[r], want)
+
+
+def _worker_rank0(rank, world, port, n_frames, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        prev = parallel.set_result_rank(0)
+        assert prev is None and parallel.wants_result() == (rank == 0)
+        got = parallel.distributed_infer(n_frames, window_frame_indices, lambda ids: _fake_raw(ids, n_frames), _align_cpu)
+        q.put((rank, None if got is None else got.numpy()))
+        parallel.set_result_rank(None)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_result_on_one_rank_only():
+    """set_result_rank(0): rank 0 gets the same aligned maps, the other ranks take part and return None."""
+    world, n_frames = 2, 60
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_rank0, args=(r, world, port, n_frames, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    n_win = len(window_frame_indices(n_frames))
+    want = _align_cpu(_fake_raw(list(range(n_win)), n_frames))[:n_frames].numpy()
+    np.testing.assert_array_equal(res[0], want)
+    assert res[1] is None

@@ -12,6 +12,27 @@ import torch.distributed as dist
 
 INFER_LEN = 32
 
+# Which ranks receive the aligned result.  None = every rank (SPMD callers: each process returns the full array, the
+# default).  An int = only that rank runs the alignment scan and downloads the maps; the others take part in the
+# exchange and return None.  With 8 ranks on one host, 8 copies of a GB-sized result through the same host memory
+# cost more than the 6 windows each rank computes (profiles/r01c_video_8gpu.jsonl).  Set with set_result_rank()
+# or the environment variable VDA_RESULT_RANK ("all" | rank number).
+import os as _os
+
+_RESULT_RANK = None if _os.environ.get("VDA_RESULT_RANK", "all") == "all" else int(_os.environ["VDA_RESULT_RANK"])
+
+
+def set_result_rank(rank):
+    """rank: None (every rank gets the result) or the one rank that does.  Returns the previous setting."""
+    global _RESULT_RANK
+    prev, _RESULT_RANK = _RESULT_RANK, (None if rank is None else int(rank))
+    return prev
+
+
+def wants_result(group=None):
+    """True if this rank returns the aligned result (always True outside a multi-rank group)."""
+    return _RESULT_RANK is None or not active(group) or dist.get_rank(group) == _RESULT_RANK
+
 
 def shard_windows(n_windows, world, rank):
     """Contiguous block of window ids owned by `rank`: ceil(n/world) per rank, trailing ranks may be
@@ -39,12 +60,15 @@ def gather_windows(local_raw, n_windows, group=None):
 def distributed_infer(n_frames, window_ids_fn, run_windows_fn, align_fn, group=None):
     """Generic sharded driver.
     window_ids_fn(n_frames) -> list of windows; run_windows_fn(ids) -> [len(ids)*32, H, W] raw depth;
-    align_fn(raw_all) -> aligned [>= n_frames, H, W].  Returns aligned[:n_frames] on every rank."""
+    align_fn(raw_all) -> aligned [>= n_frames, H, W].  Returns aligned[:n_frames] on every rank that wants the
+    result (see set_result_rank), None on the others."""
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     n_windows = len(window_ids_fn(n_frames))
     mine = shard_windows(n_windows, world, rank)
     raw = run_windows_fn(mine)
     raw_all = gather_windows(raw, n_windows, group)
+    if not wants_result(group):
+        return None
     return align_fn(raw_all)[:n_frames]
 
 

@@ -197,6 +197,10 @@ class VideoDepthAnything(nn.Module):
         frames = np.asarray(frames)
         n, h0, w0 = frames.shape[:3]
         up = (int(original_height), int(original_width)) if original_width is not None and original_height is not None else None
+        if parallel.active() and not parallel.wants_result():
+            # vda_b200.parallel.set_result_rank: this rank only computes its windows and joins the exchange
+            self.infer_video_depth_device(frames, input_size=input_size, device=device, fp32=fp32)
+            return None, target_fps
         out = np.empty((n,) + (up or (h0, w0)), np.float32)
         if parallel.active():
             # the result array is touched page by page on a helper thread while the GPUs work: first-touch
