@@ -9,11 +9,10 @@
 //
 // One CTA per (q-tile of 128 rows, head, frame), two CTAs resident per SM so that one CTA's
 // exp-bound softmax overlaps the other's MMAs:
-//   warp 0    TMA producer: Q once, then (K tile 128x64, V^T tile 64x128) per KV step, 2 stages
-//   warp 1    TMEM alloc + MMA issuer: S = Q K^T (M128 N128 K64) and O_j = P V (M128 N64 K128)
-//   warp 2-5  softmax: one thread per query row (tcgen05.ld 32x32b): running max/sum in registers,
-//             P written to shared memory as bf16 in the UMMA K-major 128B-swizzled layout,
-//             O accumulated in fp32 registers with the online-softmax rescale.
+//   warp 0    TMA producer: Q once, then K tiles (128x64) and V^T tiles (64x128) through separate 2-stage rings
+//   warp 1    TMEM alloc + MMA issuer: S = Q K^T (SS form, M128 N128 K64) and O += P V (TS form: P read from TMEM)
+//   warp 2-5  softmax: one thread per query row; the 128-column S row is pulled into registers with one burst of
+//             tcgen05.ld, P goes back to TMEM as packed bf16, O stays in TMEM (lazy rescale); see the kernel comment.
 #include <stdlib.h>
 #include <string.h>
 
@@ -88,10 +87,7 @@ constexpr int kAttThreads = 192;
 constexpr int kQBytes = 128 * 64 * 2;        // 16 KB
 constexpr int kKBytes = 128 * 64 * 2;        // 16 KB
 constexpr int kVBytes = 64 * 128 * 2;        // 16 KB (two 64x64 sub-tiles)
-constexpr int kKVStage = kKBytes + kVBytes;  // 32 KB
-constexpr int kPBytes = 128 * 128 * 2;       // 32 KB (two 128x64 sub-tiles)
-constexpr int kAttSmem = kQBytes + 2 * kKVStage + kPBytes + 256;
-constexpr int kAttTmemCols = 256;            // S: cols [0,128), O_j: cols [128,192)
+constexpr int kAttTmemCols = 256;            // S: cols [0,128), P: [128,192), O: [192,256)
 
 struct alignas(64) AttnParams {
   CUtensorMap tmQK;  // 3D (2D, S, frames), box (64, 128, 1)
@@ -102,202 +98,9 @@ struct alignas(64) AttnParams {
   float scale_log2;  // head_dim^-0.5 * log2(e)
 };
 
-__global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_kernel(const __grid_constant__ AttnParams p) {
-  extern __shared__ __align__(1024) uint8_t smem[];
-  if ((smem_u32(smem) & 1023u) != 0) __trap();  // 128B-swizzle atoms need a 1024 B aligned base
-  uint8_t* sQ = smem;
-  uint8_t* sKV = smem + kQBytes;
-  uint8_t* sP = sKV + 2 * kKVStage;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kPBytes);
-  uint64_t* q_full = bars;
-  uint64_t* kv_full = bars + 1;   // [2]
-  uint64_t* kv_empty = bars + 3;  // [2]
-  uint64_t* s_full = bars + 5;
-  uint64_t* p_full = bars + 6;
-  uint64_t* o_full = bars + 7;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int qt = blockIdx.x, head = blockIdx.y, frame = blockIdx.z;
-
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&p.tmQK);
-    tma_prefetch_desc(&p.tmV);
-    mbar_init(q_full, 1);
-    for (int s = 0; s < 2; ++s) mbar_init(&kv_full[s], 1), mbar_init(&kv_empty[s], 1);
-    mbar_init(s_full, 1);
-    mbar_init(p_full, 128);
-    mbar_init(o_full, 1);
-    fence_mbar_init();
-  }
-  if (warp == 1) {
-    tmem_alloc(tmem_slot, kAttTmemCols);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_S = tmem_base, tmem_O = tmem_base + 128;
-  pdl_sync();
-
-  // producer / MMA loops run warp-convergent with single-lane issue (see gemm.cu for why)
-  if (warp == 0) {
-    if (elect_one()) {
-      mbar_expect_tx(q_full, kQBytes);
-      tma_load_3d(sQ, &p.tmQK, q_full, head * 64, qt * 128, frame);
-    }
-    __syncwarp();
-    for (int j = 0; j < p.kv_tiles; ++j) {
-      const int st = j & 1;
-      mbar_wait(&kv_empty[st], ((j >> 1) & 1) ^ 1);
-      uint8_t* sk = sKV + st * kKVStage;
-      if (elect_one()) {
-        mbar_expect_tx(&kv_full[st], kKVStage);
-        tma_load_3d(sk, &p.tmQK, &kv_full[st], p.D + head * 64, j * 128, frame);
-        tma_load_3d(sk + kKBytes, &p.tmV, &kv_full[st], j * 128, 0, frame * p.heads + head);
-        tma_load_3d(sk + kKBytes + kVBytes / 2, &p.tmV, &kv_full[st], j * 128 + 64, 0, frame * p.heads + head);
-      }
-      __syncwarp();
-    }
-  } else if (warp == 1) {
-    constexpr uint32_t idesc_s = umma_idesc_f16(128, 128, true);
-    constexpr uint32_t idesc_o = umma_idesc_f16(128, 64, true);
-    const uint64_t qdesc = umma_desc_k_sw128(smem_u32(sQ));
-    const uint32_t p_addr = smem_u32(sP);
-    auto issue_s = [&](int j) {
-      const int st = j & 1;
-      mbar_wait(&kv_full[st], (j >> 1) & 1);
-      tc_fence_after();
-      const uint64_t kdesc = umma_desc_k_sw128(smem_u32(sKV + st * kKVStage));
-      if (elect_one()) {
-#pragma unroll
-        for (int k = 0; k < 4; ++k) umma_f16_ss(tmem_S, qdesc + 2 * k, kdesc + 2 * k, idesc_s, k != 0);
-        umma_commit(s_full);
-      }
-      __syncwarp();
-    };
-    mbar_wait(q_full, 0);
-    issue_s(0);
-    for (int j = 0; j < p.kv_tiles; ++j) {
-      const int st = j & 1;
-      mbar_wait(p_full, j & 1);
-      tc_fence_after();
-      const uint32_t v_addr = smem_u32(sKV + st * kKVStage + kKBytes);
-      if (elect_one()) {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          const uint64_t pdesc = umma_desc_k_sw128(p_addr + (k >> 2) * (128 * 128)) + 2 * (k & 3);
-          const uint64_t vdesc = umma_desc_k_sw128(v_addr + (k >> 2) * (64 * 128)) + 2 * (k & 3);
-          umma_f16_ss(tmem_O, pdesc, vdesc, idesc_o, k != 0);
-        }
-        umma_commit(o_full);
-        umma_commit(&kv_empty[st]);
-      }
-      __syncwarp();
-      if (j + 1 < p.kv_tiles) issue_s(j + 1);
-    }
-  } else {
-    // ------------------------------------------------------------- softmax warps
-    const int quad = warp & 3;
-    const int r = quad * 32 + lane;
-    const uint32_t lane_off = static_cast<uint32_t>(quad * 32) << 16;
-    const int q_idx = qt * 128 + r;
-    float acc[64];
-#pragma unroll
-    for (int i = 0; i < 64; ++i) acc[i] = 0.f;
-    float m_run = -INFINITY, l_run = 0.f;
-    uint8_t* p_row = sP + r * 128;
-    const int rx = r & 7;
-
-    for (int j = 0; j < p.kv_tiles; ++j) {
-      mbar_wait(s_full, j & 1);
-      tc_fence_after();
-      const int kv_left = p.S - j * 128;  // columns >= kv_left are padding
-      // pass 1: row max
-      float m_tile = -INFINITY;
-#pragma unroll
-      for (int c0 = 0; c0 < 128; c0 += 16) {
-        uint32_t raw[16];
-        tmem_ld16(tmem_S + lane_off + c0, raw);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const float s = (c0 + i < kv_left) ? __uint_as_float(raw[i]) : -INFINITY;
-          m_tile = fmaxf(m_tile, s);
-        }
-      }
-      const float m_new = fmaxf(m_run, m_tile * p.scale_log2);
-      const float alpha = fast_exp2(m_run - m_new);
-      float l_tile = 0.f;
-      // pass 2: p = exp2(s*scale - m), bf16 -> swizzled smem (A operand of the PV MMA)
-#pragma unroll
-      for (int c0 = 0; c0 < 128; c0 += 16) {
-        uint32_t raw[16];
-        tmem_ld16(tmem_S + lane_off + c0, raw);
-        tmem_ld_wait();
-        uint32_t packed[8];
-#pragma unroll
-        for (int i = 0; i < 16; i += 2) {
-          float p0 = (c0 + i < kv_left) ? fast_exp2(fmaf(__uint_as_float(raw[i]), p.scale_log2, -m_new)) : 0.f;
-          float p1 = (c0 + i + 1 < kv_left) ? fast_exp2(fmaf(__uint_as_float(raw[i + 1]), p.scale_log2, -m_new)) : 0.f;
-          l_tile += p0 + p1;
-          __nv_bfloat162 h = __floats2bfloat162_rn(p0, p1);
-          packed[i >> 1] = *reinterpret_cast<uint32_t*>(&h);
-        }
-        uint8_t* sub = p_row + (c0 >> 6) * (128 * 128);
-        const int cbase = (c0 & 63) >> 3;
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint4 v = make_uint4(packed[4 * c], packed[4 * c + 1], packed[4 * c + 2], packed[4 * c + 3]);
-          *reinterpret_cast<uint4*>(sub + (((cbase + c) ^ rx) << 4)) = v;
-        }
-      }
-      l_run = l_run * alpha + l_tile;
-      m_run = m_new;
-      fence_proxy_async_smem();
-      tc_fence_before();
-      mbar_arrive(p_full);
-      // rescale the running output while the PV MMA runs
-#pragma unroll
-      for (int i = 0; i < 64; ++i) acc[i] *= alpha;
-      mbar_wait(o_full, j & 1);
-      tc_fence_after();
-#pragma unroll
-      for (int c0 = 0; c0 < 64; c0 += 16) {
-        uint32_t raw[16];
-        tmem_ld16(tmem_O + lane_off + c0, raw);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 16; ++i) acc[c0 + i] += __uint_as_float(raw[i]);
-      }
-    }
-    if (q_idx < p.S) {
-      const float inv = 1.0f / l_run;
-      bf16* dst = p.out + (static_cast<long long>(frame) * p.S + q_idx) * p.D + head * 64;
-#pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        uint32_t w[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          __nv_bfloat162 h = __floats2bfloat162_rn(acc[8 * c + 2 * i] * inv, acc[8 * c + 2 * i + 1] * inv);
-          w[i] = *reinterpret_cast<uint32_t*>(&h);
-        }
-        reinterpret_cast<uint4*>(dst)[c] = make_uint4(w[0], w[1], w[2], w[3]);
-      }
-    }
-  }
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) {
-    tc_fence_after();
-    tmem_dealloc(tmem_base, kAttTmemCols);
-  }
-}
-
 // =============================================================================================
-// v2: S row in registers, P and O in TMEM.
+// S row in registers, P and O in TMEM (the first-generation kernel staged P through shared memory and kept O in
+// registers: 587 us per vitl block against 340 us; removed).
 //   * the softmax thread pulls its whole 128-column S row into registers with one burst of
 //     tcgen05.ld and immediately frees the S buffer, so S_{j+1} = Q K_{j+1}^T runs on the tensor pipe
 //     while the exponentials of tile j are still being computed;
@@ -634,51 +437,25 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
   p.q_tiles = (S + 127) / 128;
   p.kv_tiles = (S + 127) / 128;
   p.scale_log2 = 0.125f * 1.4426950408889634f;
+  // A/B knob: VDA_ATTN_POLY = 0 / 4 / 8 (default): one score pair in N evaluated with the packed polynomial exp2
+  const char* ep = getenv("VDA_ATTN_POLY");
+  const int poly = ep ? atoi(ep) : 8;
   static bool configured = false;
   if (!configured) {
-    int rc = check_cuda(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttSmem),
-                        "attn smem attribute");
-    if (rc) return rc;
-    rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
-    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
-    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
-    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
-    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<4, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
-    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<8, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
-    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<2, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
-    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<6, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
-    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<16, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn v2");
+    int rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<8, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn smem");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<4, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn smem");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn smem");
     if (rc) return rc;
     configured = true;
   }
-  // A/B knobs: VDA_ATTN_VARIANT=1 first-generation kernel (P via smem); VDA_ATTN_POLY=4 a quarter of the
-  // exponentials on the FMA pipe; VDA_ATTN_LATE=0/1 position of the PV_{j-1} wait
-  const char* ev = getenv("VDA_ATTN_VARIANT");
-  const char* ep = getenv("VDA_ATTN_POLY");
-  const char* el = getenv("VDA_ATTN_LATE");
-  const char* ek = getenv("VDA_ATTN_PK");  // packed f32x2 softmax arithmetic
-  const int variant = (ev && ev[0] == '1') ? 1 : 2, poly = ep ? atoi(ep) : 8, late = el ? atoi(el) : 1, pk = ek ? atoi(ek) : 1;
-  dim3 grid(p.q_tiles, heads, frames);
-  cudaError_t le = cudaSuccess;
-  if (variant == 1)
-    le = launch_pdl(attn_fwd_kernel, grid, dim3(kAttThreads), kAttSmem, static_cast<cudaStream_t>(stream), p);
-  else if (pk && late && poly == 8)
-    le = launch_pdl(attn_fwd_v2_kernel<8, true, true>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
-  else if (pk && late && poly == 6)
-    le = launch_pdl(attn_fwd_v2_kernel<6, true, true>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
-  else if (pk && late && poly == 16)
-    le = launch_pdl(attn_fwd_v2_kernel<16, true, true>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
-  else if (pk && late && poly == 2)
-    le = launch_pdl(attn_fwd_v2_kernel<2, true, true>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
-  else if (pk && late && poly != 0)
-    le = launch_pdl(attn_fwd_v2_kernel<4, true, true>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
-  else if (pk && late)
-    le = launch_pdl(attn_fwd_v2_kernel<0, true, true>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
-  else if (poly != 0)
-    le = launch_pdl(attn_fwd_v2_kernel<4, false>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
-  else if (late)
-    le = launch_pdl(attn_fwd_v2_kernel<0, true>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
+  const dim3 grid(p.q_tiles, heads, frames);
+  const cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaError_t le;
+  if (poly == 8)
+    le = launch_pdl(attn_fwd_v2_kernel<8, true, true>, grid, dim3(kAttThreads), kA2Smem, st, p);
+  else if (poly == 4)
+    le = launch_pdl(attn_fwd_v2_kernel<4, true, true>, grid, dim3(kAttThreads), kA2Smem, st, p);
   else
-    le = launch_pdl(attn_fwd_v2_kernel<0, false>, grid, dim3(kAttThreads), kA2Smem, static_cast<cudaStream_t>(stream), p);
+    le = launch_pdl(attn_fwd_v2_kernel<0, true, true>, grid, dim3(kAttThreads), kA2Smem, st, p);
   return check_cuda(le, "attn launch");
 }
