@@ -144,11 +144,18 @@ def test_gemm_convtranspose_store(L, s, cin, cout, h, w):
     bk = torch.zeros(s, s, cp, device="cuda")
     bk[:, :, :cout] = b
     a = x.permute(0, 2, 3, 1).reshape(n * h * w, cin).contiguous()
-    out = torch.zeros(n, h * s, w * s, cp, device="cuda", dtype=torch.bfloat16)
+    # guard bands of a sentinel value on both sides of the output: the scattered (pixel-shuffle) stores must not leave it
+    numel, guard = n * h * s * w * s * cp, 4096
+    buf = torch.full((numel + 2 * guard,), 7.0, device="cuda", dtype=torch.bfloat16)
+    out = buf[guard:guard + numel].view(n, h * s, w * s, cp)
+    out.fill_(float("nan"))
     L.gemm(a, wk.view(-1, cin), L.make_epilogue(bias=bk.view(-1), out=out, ldo=cp, store_mode=L.ST_CONVT,
                                                  ct=(s, cp, h, w)))
+    torch.cuda.synchronize()
+    assert not torch.isnan(out).any(), "some output pixels were never written"
     _close(out[..., :cout].permute(0, 3, 1, 2), want)
     assert out[..., cout:].abs().max().item() == 0 if cp > cout else True
+    assert (buf[:guard] == 7.0).all() and (buf[guard + numel:] == 7.0).all(), "store outside the output tensor"
 
 
 def test_gemm_qkv_store(L):
