@@ -41,8 +41,13 @@ __device__ __forceinline__ void st_pair(bf16* p, float a, float b, int split) {
 // Output row remap: input rows are [frames, S] tokens; the first `skip` tokens of every frame are
 // dropped (cls token for the DPT taps, dinov2.py:311-312).  Optional positional-encoding add
 // (motion_module.py:207-209) after normalisation: pe[(row / pe_rows_per_t) % pe_T][c].
+// 4 blocks of 8 warps per SM (64 registers, a 16-byte spill) instead of the 3 that 70 registers allowed: C = 1024 rows
+// 54 -> 49 us (5.5 TB/s = 83 % of the measured HBM peak); 5 blocks spill more and are slower (54.5 us).
+#ifndef VDA_LN_MINBLOCKS
+#define VDA_LN_MINBLOCKS 4
+#endif
 template <typename TIn, int MAXV>
-__global__ void layernorm_kernel(const TIn* __restrict__ x, const float* __restrict__ gamma,
+__global__ void __launch_bounds__(256, VDA_LN_MINBLOCKS) layernorm_kernel(const TIn* __restrict__ x, const float* __restrict__ gamma,
                                  const float* __restrict__ beta, bf16* __restrict__ out, bf16* __restrict__ out_nope,
                                  const float* __restrict__ pe, int rows, int C, float eps, int S, int skip,
                                  int pe_rows_per_t, int pe_T, int split) {

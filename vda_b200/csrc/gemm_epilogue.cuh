@@ -20,6 +20,7 @@ constexpr int kBlockK = 64;
 #define VDA_EPI_WARPS 8  // measured: 16 warps (96 regs) is not faster than 8 (126 regs)
 #endif
 constexpr int kEpiWarps = VDA_EPI_WARPS;  // 4 TMEM lane quadrants x kEpiParts column slices
+static_assert(VDA_EPI_WARPS == 8, "the box epilogues (3 boxes x 2 column slices in 48 KB, named barriers 2/3) are laid out for 8 epilogue warps");
 constexpr int kEpiParts = kEpiWarps / 4;
 constexpr int kEpiThreads = kEpiWarps * 32;
 
