@@ -149,7 +149,8 @@ static int pick_stages(int bn, bool two, const vda_epilogue* e, int epi_tma) {
   const bool staged = epi_tma || (e->res_f32 && e->store_mode == ST_PLAIN && e->act != ACT_GEGLU);
   if (!staged) return max_stages;
   const int stage_bytes = 128 * 64 * 2 + (two ? bn / 2 : bn) * 64 * 2;
-  const int freed = (48 * 1024 + stage_bytes - 1) / stage_bytes;
+  const int need = epi_tma ? epi_box_area_bytes(epi_tma) : 48 * 1024;  // TMA boxes, or the 3-4 slot fp32-residual staging ring
+  const int freed = (need + stage_bytes - 1) / stage_bytes;
   return max_stages - freed;
 }
 

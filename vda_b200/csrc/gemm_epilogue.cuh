@@ -20,7 +20,7 @@ constexpr int kBlockK = 64;
 #define VDA_EPI_WARPS 8  // measured: 16 warps (96 regs) is not faster than 8 (126 regs)
 #endif
 constexpr int kEpiWarps = VDA_EPI_WARPS;  // 4 TMEM lane quadrants x kEpiParts column slices
-static_assert(VDA_EPI_WARPS == 8, "the box epilogues (3 boxes x 2 column slices in 48 KB, named barriers 2/3) are laid out for 8 epilogue warps");
+static_assert(VDA_EPI_WARPS == 8, "the box epilogues (kRedBoxes boxes x 2 column slices, named barriers 2/3) are laid out for 8 epilogue warps");
 constexpr int kEpiParts = kEpiWarps / 4;
 constexpr int kEpiThreads = kEpiWarps * 32;
 
@@ -326,7 +326,6 @@ __device__ __forceinline__ ResRing make_res_ring(const GemmParams& p, const Tile
 // residual in L2 (cp.reduce.async.bulk.tensor .add).  The SM never reads the residual at all.
 // Three boxes per column slice rotate; one named barrier per box (see the ordering argument inline).
 constexpr int kRedBoxBytes = 16 * 4 * kBlockM;  // 8 KB
-constexpr int kRedBoxes = 3;
 
 __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, uint32_t src_smem, int c0, int c1) {
   asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
@@ -335,6 +334,7 @@ __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, uint32_t
                : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read_1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
@@ -379,6 +379,7 @@ __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_til
                                                   const float* s_bias, const float* s_scale, uint32_t box_base, int& box_ctr,
                                                   bool issuer, const long long* s_rowoff = nullptr) {
   constexpr int kPer = EpiSlice<BN>::kPer;
+  constexpr int kRedBoxes = epi_boxes(MODE);
   constexpr int kCols = MODE == 1 ? 16 : (MODE == 4 ? 64 : 32);  // accumulator columns per box
   const int cbeg = half * kPer;
   if (cbeg >= BN) return;
@@ -459,8 +460,8 @@ __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_til
         tmem_ld32(t_acc + c0 + kCols, raw);
       }
     }
-    // box (box_ctr % 3) is free: its previous store (3 boxes ago) was confirmed read by the issuer
-    // before the issuer joined the barrier of the previous box, which every thread has passed.
+    // box (box_ctr % kRedBoxes) is free: the store that last used it was confirmed read by the issuer before the
+    // issuer joined the barrier of the previous box, which every thread has passed.
     const uint32_t box = box_base + static_cast<uint32_t>(box_ctr % kRedBoxes) * kRedBoxBytes;
     const uint32_t rowaddr = box + static_cast<uint32_t>(r) * 64;
     const uint32_t sw = (static_cast<uint32_t>(r) >> 1) & 3;
@@ -487,12 +488,13 @@ __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_til
           if (ro >= 0) *reinterpret_cast<uint4*>(p.out + ro + tapoff + chunk * 8) = v;
         }
       }
-      // box reuse: a thread writes box k+3 only after the barrier of box k+2, which every thread joins
-      // after it has finished copying box k+1 (and k) out
+      // box reuse: a thread writes box k+2 only after the barrier of box k+1, which every thread joins
+      // after it has finished copying box k out
       ++box_ctr;
       continue;
     }
     fence_proxy_async_smem();
+    if (kRedBoxes == 2 && issuer) bulk_wait_read_all();  // box k-1 has left shared memory: whoever passes the barrier may reuse it
     named_bar_sync(2 + half, 128);
     if (issuer) {
       if (col < p.N) {  // rows >= M / cols >= N / pixels outside the map are clipped by TMA
@@ -512,7 +514,7 @@ __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_til
         }
       }
       bulk_commit();
-      bulk_wait_read_1();  // the previous box of this slice has been read out of shared memory
+      if (kRedBoxes != 2) bulk_wait_read_1();  // 3 boxes: the previous box of this slice has been read out of shared memory
     }
     ++box_ctr;
   }

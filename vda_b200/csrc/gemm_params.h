@@ -6,6 +6,20 @@
 
 namespace vda {
 
+// Shared-memory boxes per column slice of the TMA epilogues (gemm_epilogue.cuh), 8 KB each, two slices.
+// fp32 reduce-add flavour (epi_tma 1): 2 boxes -- the issuing thread confirms that the previous box has been read
+// (cp.async.bulk.wait_group.read 0) BEFORE it joins the barrier of the current box, so every thread that passes that
+// barrier may overwrite the previous box; one store is still in flight while the next box is computed.  32 KB instead
+// of 48 KB leave the 256-wide CTA-pair tile a fifth pipeline stage: proj 99 -> 92 us, fc2 298 -> 279 us.
+// bf16 store flavours (2, 3, 4): 3 boxes with the wait after the commit; with 2 they were 2-3 % slower (fc1, K = 256).
+#ifdef __CUDACC__
+#define VDA_HD __host__ __device__
+#else
+#define VDA_HD
+#endif
+VDA_HD constexpr int epi_boxes(int epi_tma) { return epi_tma == 1 ? 2 : 3; }
+VDA_HD constexpr int epi_box_area_bytes(int epi_tma) { return 2 * epi_boxes(epi_tma) * 8 * 1024; }
+
 // A-operand addressing
 enum : int { A_PLAIN = 0, A_CONV3X3 = 1 };
 // output-row addressing
