@@ -259,7 +259,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
     const int et = threadIdx.x - 128;
     const TileSched ts = {tile_begin, tile_step, tile_end, 1, 0};
     ResRing rr = make_res_ring<BN>(p, ts, smem + ring_used, Cfg::kRingBytes - ring_used, et, r, half);
-    // TMA reduce-add epilogue: 3 boxes per column slice in the freed stages; thread 0 of each slice issues
+    // box epilogues: epi_boxes(mode) boxes per column slice in the freed stages; thread 0 of each slice issues the TMA
     const uint32_t red_base = smem_u32(smem + ring_used) + static_cast<uint32_t>(half) * epi_boxes(p.epi_tma) * kRedBoxBytes;
     const bool red_issuer = (et & 127) == 0;
     int box_ctr = 0;
@@ -440,7 +440,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
     const TileSched ts = {tile_begin, tile_step, tile_end, 2, static_cast<int>(rank)};
     ResRing rr = make_res_ring<BN>(p, ts, smem + p.stages * Cfg::kStageBytes, (Cfg::kStages - p.stages) * Cfg::kStageBytes, et,
                                    r, half);
-    // TMA reduce-add epilogue: 3 boxes per column slice in the freed stages; thread 0 of each slice issues
+    // box epilogues: epi_boxes(mode) boxes per column slice in the freed stages; thread 0 of each slice issues the TMA
     const uint32_t red_base = smem_u32(smem + p.stages * Cfg::kStageBytes) + static_cast<uint32_t>(half) * epi_boxes(p.epi_tma) * kRedBoxBytes;
     const bool red_issuer = (et & 127) == 0;
     int box_ctr = 0;

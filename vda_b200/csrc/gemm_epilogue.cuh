@@ -324,7 +324,7 @@ __device__ __forceinline__ ResRing make_res_ring(const GemmParams& p, const Tile
 // the threads only write their delta rows into a swizzled shared-memory box (16 fp32 columns x 128
 // rows); one elected thread per column slice hands the box to the TMA unit, which adds it onto the
 // residual in L2 (cp.reduce.async.bulk.tensor .add).  The SM never reads the residual at all.
-// Three boxes per column slice rotate; one named barrier per box (see the ordering argument inline).
+// epi_boxes(MODE) boxes per column slice rotate (gemm_params.h); one named barrier per box (ordering argument inline).
 constexpr int kRedBoxBytes = 16 * 4 * kBlockM;  // 8 KB
 
 __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, uint32_t src_smem, int c0, int c1) {
@@ -373,7 +373,7 @@ __device__ __forceinline__ void stage_row_offsets(const GemmParams& p, int m_til
 // MODE 3: bf16 box as MODE 2, but written out by the slice's 128 threads themselves, four lanes per
 // 64-byte row segment, to rows given by a per-tile offset table: for stores TMA cannot express as one box
 // (ConvTranspose pixel shuffle).  A warp store then touches 8 lines instead of 32 (thread = row).
-// `box_base`: shared address of this column slice's 3 boxes; `box_ctr`: running box counter of the slice.
+// `box_base`: shared address of this column slice's boxes; `box_ctr`: running box counter of the slice.
 template <int BN, int MODE>
 __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_tile, int n_t, uint32_t t_acc, int r, int half,
                                                   const float* s_bias, const float* s_scale, uint32_t box_base, int& box_ctr,
