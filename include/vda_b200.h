@@ -18,7 +18,8 @@ extern "C" {
 
 int vda_init(int device);            /* resolve driver entry points, query SM count; idempotent */
 const char* vda_last_error(void);    /* message of the last failing call on this thread */
-int vda_num_sms(void);
+int vda_num_sms(void);             /* SM count of the current device */
+const char* vda_build_digest(void);  /* sha256 of the sources + flags this binary was built from */
 /* Launch the following kernels with programmatic stream serialization (each kernel's prologue overlaps the
  * previous kernel's tail; csrc/common.cuh).  Returns the previous setting.  Default 0. */
 int vda_set_pdl(int on);
@@ -141,27 +142,27 @@ int vda_temporal_attn_stream_f32(const float* q, const float* knew, const float*
 int vda_depth_tail(const void* x, int ldx, const void* w3, const float* b3, const float* w1, float b1, float* out,
                    int n, int h, int w, int H, int W, int C, void* stream);
 
-/* Depth visualisation (utils/dc_utils.py:72-86): minmax2 = {min, max} of max(x, 0) as two fp32 words;
- * colorize: q = uint8((d - min) / (max - min) * 255), out = lut_rgb[q] (3 bytes per pixel) or q if grey. */
+/* Depth visualisation (utils/dc_utils.py:72-86): minmax2 = {min, max} of x as two fp32 words (any sign);
+ * colorize: q = ((d - min) / (max - min) * 255).astype(uint8) evaluated with numpy's three fp32 roundings and
+ * truncating cast (bit-exact), out = lut_rgb[q] (3 bytes per pixel) or q if grey. */
 int vda_minmax_f32(const float* x, long long n, void* minmax2, void* stream);
 int vda_depth_colorize(const float* depth, long long n, const void* minmax2, const void* lut_rgb, void* out, int grey,
                        void* stream);
-
-/* Debug probe (tests only): D f32 [128,32] = A[128,64] * W[32,64]^T where A's row 8g+i is row
- * g*(sbo/128) + row0 + i of the bf16 source G [320,64], read through a tap-shifted tcgen05 descriptor. */
-int vda_debug_umma_shift(const void* G, const void* W, float* D, int row0, int sbo, int base_offset, void* stream);
-/* Debug probe: `ctas` x `threads` threads each issue iters*8 mma.sync.m16n8k16 bf16 (no memory traffic). */
-int vda_debug_mma_rate(float* out, int ctas, int threads, int iters, void* stream);
+/* Near/far depth normalisation of the fork's job engine (external_engine/engine.py:1099-1141), per frame:
+ * t = (d - min_f) / (max_f - min_f); out = near + (far-near)*t if far > near else far + (near-far)*t; constant
+ * frames -> near; invert: out = far - (out - near).  fp32 roundings as numpy's (bit-exact).
+ * minmax_ws: 2*frames fp32 words of scratch (receives each frame's {min, max}). */
+int vda_depth_normalize(const float* depth, float* out, long long per_frame, int frames, double near_value,
+                        double far_value, int invert, void* minmax_ws, void* stream);
 
 /* Frame pre-processing (util/transform.py:51-157 via video_depth.py:77-89): frames uint8 RGB [n,H0,W0,3]
  * -> out f32 [n,3,nh,nw] = ((cv2-compatible INTER_CUBIC resize of frame/255) - mean) / std. */
 int vda_preprocess_u8(const void* frames, int n, int H0, int W0, float* out, int nh, int nw, void* stream);
 
-/* FP32-accuracy mode attention (fp32=True of infer_video_depth, video_depth.py:108).  Inputs are the
- * fp32 q/k/v written by the projection GEMM, outputs are split tensors (vda_epilogue::split).
- * vda_attn_f32: q | k | v (dinov2_layers/attention.py:51-59) either as f32 [frames*S, ld >= 3*heads*64]
- * (in_split = 0) or as a split bf16 tensor [frames*S, ld] with hi at column c and lo at c + in_split
- * (in_split >= 3*heads*64; the fast path: the projection GEMM writes it with vda_epilogue::split);
+/* FP32-accuracy mode attention (fp32=True of infer_video_depth, video_depth.py:108); outputs are split
+ * tensors (vda_epilogue::split).
+ * vda_attn_f32: q | k | v (dinov2_layers/attention.py:51-59) as a split bf16 tensor [frames*S, ld] with hi at
+ * column c and lo at c + in_split (in_split >= 3*heads*64; the projection GEMM writes it with vda_epilogue::split);
  * out [frames*S, ldo] with parts `split` apart.  vda_temporal_attn_f32: as vda_temporal_attn. */
 int vda_attn_f32(const void* qkv, int ld, int in_split, void* out, int ldo, int split, int frames, int S, int heads,
                  void* stream);
@@ -171,7 +172,13 @@ int vda_temporal_attn_f32(const float* q, const float* k, const float* v, int ld
 /* Alignment (utils/util.py:40-74, video_depth.py:120-160).  sums5 = {sum p*p, sum p, n, sum p*t,
  * sum t} accumulated in FP64 (caller zeroes it); solve writes {scale, shift} (metric: {1,0}). */
 int vda_lsq_accum(const float* pred, const float* target, long long n, double* sums5, void* stream);
-int vda_lsq_solve(const double* sums5, float* scale_shift, int metric, void* stream);
+/* the same with a per-element fp32 weight (utils/util.py:16-62 with a non-trivial mask); mask NULL = all ones */
+int vda_lsq_accum_masked(const float* pred, const float* target, const float* mask, long long n, double* sums5,
+                         void* stream);
+/* flags: bit 0 = metric model (scale 1, shift 0: video_depth.py:135-136), bit 1 = zero sums5 afterwards */
+int vda_lsq_solve(double* sums5, float* scale_shift, int flags, void* stream);
+/* out[f] = pre[f]*(1-w_f) + post[f]*w_f, w_f = f/(frames-1) (utils/util.py:65-74), fp32 roundings as numpy's */
+int vda_blend_frames(const float* pre, const float* post, float* out, long long per_frame, int frames, void* stream);
 int vda_affine_clamp(const float* src, float* dst, long long n, const float* scale_shift, void* stream);
 int vda_affine_clamp_blend(float* pre, const float* post, long long per_frame, int frames, const float* scale_shift,
                            void* stream);

@@ -42,8 +42,44 @@ def video_frames(n, h, w, seed=0):
     return out
 
 
+UTIL_SHAPE = (2, 37, 53)
+NORMALIZE_CASES = [(0.0, 1.0, False), (0.1, 10.0, True), (5.0, 0.5, False), (2.0, 2.0, True)]  # near, far, invert
+
+
+def util_inputs(seed=0):
+    """pred, target, mask (float32 [2,37,53]; mask has fractional weights and zeros) and 8+8 frames to cross-fade."""
+    rng = np.random.default_rng(seed)
+    pred = rng.uniform(0.2, 7.5, UTIL_SHAPE).astype(np.float32)
+    target = (1.7 * pred - 0.3 + rng.normal(0, 0.05, UTIL_SHAPE)).astype(np.float32)
+    mask = (rng.uniform(0, 1, UTIL_SHAPE) > 0.3).astype(np.float32) * rng.choice([1.0, 0.5], UTIL_SHAPE).astype(np.float32)
+    pre = [rng.normal(0, 2, UTIL_SHAPE[1:]).astype(np.float32) for _ in range(8)]
+    post = [rng.normal(0, 2, UTIL_SHAPE[1:]).astype(np.float32) for _ in range(8)]
+    depth = rng.uniform(0.0, 80.0, (3,) + UTIL_SHAPE[1:]).astype(np.float32)
+    depth[2] = 4.25   # constant frame (engine.py:1123-1124)
+    return pred, target, mask, pre, post, depth
+
+
+def make_util_golden():
+    """utils/util.py:16-74 and external_engine/engine.py:1099-1141 outputs of the unmodified reference."""
+    csas, gif, nd = refload.import_reference_utils()
+    pred, target, mask, pre, post, depth = util_inputs()
+    out = {}
+    out["full"] = np.array(csas(pred, target, mask), np.float64)
+    out["full_ones"] = np.array(csas(pred, target, np.ones_like(mask)), np.float64)
+    out["scale_only"] = np.array(csas(pred, target, mask, scale_only=True), np.float64)
+    out["blend"] = np.stack(gif(pre, post)).astype(np.float32)
+    for i, (near, far, inv) in enumerate(NORMALIZE_CASES):
+        out[f"norm{i}"] = np.stack([nd(depth[f], near, far, inv) for f in range(depth.shape[0])]).astype(np.float32)
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "util_cases.npz"), **out)
+    print("util", {k: v.shape for k, v in out.items()})
+
+
 def main():
     assert refload.reference_available(), "needs /root/reference (build container)"
+    os.makedirs(GOLDEN_DIR, exist_ok=True)
+    make_util_golden()
+    if os.environ.get("VDA_GOLDEN_ONLY") == "util":
+        return
     Offline, Stream = refload.import_reference()
     os.makedirs(GOLDEN_DIR, exist_ok=True)
     torch.set_grad_enabled(False)

@@ -55,6 +55,27 @@ def import_reference():
     return Offline, Stream
 
 
+def import_reference_utils():
+    """(compute_scale_and_shift, get_interpolate_frames, normalize_depth) of the unmodified reference.
+    utils/util.py is loaded by file path (this repo has a `utils` package of its own); normalize_depth is a method
+    of the job engine class (external_engine/engine.py:1099-1141) whose module needs a GUI / job stack to import,
+    so the method's own source is compiled by itself and called with self = None."""
+    import ast
+    import importlib.util
+    import logging
+
+    import numpy as np
+
+    spec = importlib.util.spec_from_file_location("_vda_reference_utils_util", os.path.join(REF_ROOT, "utils", "util.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    src = open(os.path.join(REF_ROOT, "external_engine", "engine.py")).read()
+    fn = next(n for n in ast.walk(ast.parse(src)) if isinstance(n, ast.FunctionDef) and n.name == "normalize_depth")
+    ns = {"np": np, "logger": logging.getLogger("reference"), "print": lambda *a, **k: None}
+    exec(compile(ast.Module(body=[fn], type_ignores=[]), "engine.py:normalize_depth", "exec"), ns)
+    return mod.compute_scale_and_shift, mod.get_interpolate_frames, lambda *a: ns["normalize_depth"](None, *a)
+
+
 def state_dict_shapes(arch):
     """Key -> shape of the reference state_dict, derived from the architecture table (no reference needed)."""
     from .vda_oracle import ARCH

@@ -263,6 +263,52 @@ def scale_and_shift(pred, target):
     return 1, 0
 
 
+def scale_and_shift_masked(prediction, target, mask, scale_only=False):
+    """utils/util.py:16-62 as written (float32 sums over mask * ...): `compute_scale_and_shift`."""
+    prediction, target, mask = (a.astype(np.float32) for a in (prediction, target, mask))
+    a00 = np.sum(mask * prediction * prediction)
+    a01 = np.sum(mask * prediction)
+    a11 = np.sum(mask)
+    b0 = np.sum(mask * prediction * target)
+    if scale_only:                      # util.py:23-38
+        return b0 / (a00 + 1e-6), 0
+    b1 = np.sum(mask * target)
+    det = a00 * a11 - a01 * a01
+    if det != 0:
+        return (a11 * b0 - a01 * b1) / det, (-a01 * b0 + a00 * b1) / det
+    return 1, 0
+
+
+def interpolate_frames(pre, post):
+    """utils/util.py:65-74: linear cross-fade of two equally long frame lists."""
+    n = len(pre)
+    step = (1.0 - 0.0) / (n - 1)
+    w = [0.0] + [i * step for i in range(1, n - 1)] + [1.0]
+    return [pre[i] * (1 - w[i]) + post[i] * w[i] for i in range(n)]
+
+
+def depth_to_uint8(frames):
+    """utils/dc_utils.py:75-79: clip-global min/max, float32 arithmetic, truncating cast."""
+    d_min, d_max = frames.min(), frames.max()
+    return ((frames - d_min) / (d_max - d_min) * 255).astype(np.uint8)
+
+
+def normalize_depth(depth, near_value, far_value, invert_depth):
+    """external_engine/engine.py:1099-1141 for one frame (the engine calls it per frame, :402 / :785)."""
+    lo, hi = depth.min(), depth.max()
+    if hi > lo:
+        out = (depth - lo) / (hi - lo)
+        if far_value > near_value:
+            out = near_value + (far_value - near_value) * out
+        else:
+            out = far_value + (near_value - far_value) * out
+    else:
+        out = np.full_like(depth, near_value)
+    if invert_depth:
+        out = far_value - (out - near_value)
+    return out
+
+
 def align_windows(depth_list, metric=False):
     """video_depth.py:120-160: sequential scale/shift alignment + 8-frame cross-fade."""
     aligned, ref = [], []

@@ -3,10 +3,18 @@
 // read by an MMA whose 8-row groups start at an arbitrary row (start address offset by s*128 bytes,
 // "matrix base offset" = s) and lie `sbo` bytes apart?  D[128,32] = A_shifted[128,64] * W[32,64]^T.
 // Row r = 8g + i of the A operand is expected to be source row  g*(sbo/128) + row0 + i.
-// Debug/test entry point only (tests/test_umma_probe_gpu.py); not on the product path.
-#include "common.cuh"
-#include "api_internal.h"
-#include "../../include/vda_b200.h"
+// Measurement probes, NOT part of libvda_b200.so: built on demand into scripts/probes/libvda_probes.so
+// (scripts/probes/probes.py) and linked against the product library for its TMA-descriptor helper.
+#include "../../vda_b200/csrc/common.cuh"
+#include "../../vda_b200/csrc/api_internal.h"
+
+extern "C" {
+/* D f32 [128,32] = A[128,64] * W[32,64]^T where A's row 8g+i is row g*(sbo/128) + row0 + i of the bf16 source
+ * G [320,64], read through a tap-shifted tcgen05 descriptor. */
+int vda_debug_umma_shift(const void* G, const void* W, float* D, int row0, int sbo, int base_offset, void* stream);
+/* `ctas` x `threads` threads each issue iters*8 mma.sync.m16n8k16 bf16 (no memory traffic). */
+int vda_debug_mma_rate(float* out, int ctas, int threads, int iters, void* stream);
+}
 
 namespace vda {
 
@@ -116,12 +124,8 @@ extern "C" int vda_debug_umma_shift(const void* G, const void* W, float* D, int 
     if ((rc = encode_bf16_map(&tmW, W, 2, dims, str, box))) return rc;
   }
   const int smem = kProbeRows * 128 + 32 * 128 + 64 + 1024;
-  static bool configured = false;
-  if (!configured) {
-    rc = check_cuda(cudaFuncSetAttribute(umma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem), "probe smem");
-    if (rc) return rc;
-    configured = true;
-  }
+  rc = check_cuda(cudaFuncSetAttribute(umma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem), "probe smem");
+  if (rc) return rc;
   umma_probe_kernel<<<1, 128, smem, static_cast<cudaStream_t>(stream)>>>(tmG, tmW, D, row0, sbo, base_offset);
   return check_cuda(cudaGetLastError(), "umma probe launch");
 }

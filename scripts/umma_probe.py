@@ -3,11 +3,14 @@ import os
 import sys
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 import torch
 
 import vda_b200.lib as L
+from probes.probes import load as load_probes
 
 L.init()
+PROBES = load_probes()
 g = torch.Generator(device="cuda").manual_seed(0)
 G = torch.randn(320, 64, device="cuda", generator=g).bfloat16()
 W = torch.randn(32, 64, device="cuda", generator=g).bfloat16()
@@ -17,7 +20,7 @@ for sbo in (1024, 2048, 1280):
         res = []
         for bo in sorted({0, row0 & 7}):
             D.fill_(float("nan"))
-            L.check(L.load().vda_debug_umma_shift(L.ptr(G), L.ptr(W), L.ptr(D), row0, sbo, bo, L.stream_ptr()))
+            L.check(PROBES.vda_debug_umma_shift(L.ptr(G), L.ptr(W), L.ptr(D), row0, sbo, bo, L.stream_ptr()))
             torch.cuda.synchronize()
             rows = torch.tensor([gidx * (sbo // 128) + row0 + i for gidx in range(16) for i in range(8)], device="cuda")
             ok = bool((rows < 320).all())

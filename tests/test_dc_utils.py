@@ -28,3 +28,12 @@ def test_read_video_frames_stride_length_and_max_res(tmp_path):
     assert frames.shape == (3, 24, 32, 3) and fps == 12
     lut = inferno_lut()
     assert lut.shape == (256, 3) and lut.dtype == np.uint8 and lut[0].sum() < 10 and lut[-1][0] > 240
+
+
+def test_inferno_table_is_pinned():
+    """The colour table is OpenCV's COLORMAP_INFERNO, committed as a fixture so a cv2 upgrade cannot change the
+    product's bytes silently (matplotlib, the reference's source of the table, is unavailable on this image)."""
+    from utils.dc_utils import inferno_lut
+
+    gold = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "inferno_lut_cv2.npy"))
+    np.testing.assert_array_equal(inferno_lut(), gold)

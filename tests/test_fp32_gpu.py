@@ -148,18 +148,13 @@ def test_split_elementwise_kernels(L):
     assert unsplit(a)[:, 588:].abs().max().item() == 0
 
 
-@pytest.mark.parametrize("presplit", [True, False])
 @pytest.mark.parametrize("frames,S,heads", [(2, 1370, 6), (3, 131, 2), (1, 64, 1), (1, 7, 1)])
-def test_attn_f32(L, frames, S, heads, presplit):
-    """presplit: q/k/v arrive as the split tensor the projection GEMM writes (cp.async-pipelined kernel);
-    otherwise as f32 (split on the fly)."""
+def test_attn_f32(L, frames, S, heads):
+    """q/k/v arrive as the split tensor the projection GEMM writes."""
     D = heads * 64
     qkv = _rand(frames * S, 3 * D, seed=1)
     out = torch.full((frames * S, 3 * D), float("nan"), device="cuda", dtype=torch.bfloat16)
-    if presplit:
-        L.attn_f32(split3(qkv), out, D, frames, S, heads, in_split=3 * D)
-    else:
-        L.attn_f32(qkv, out, D, frames, S, heads)
+    L.attn_f32(split3(qkv), out, D, frames, S, heads, in_split=3 * D)
     f = qkv.double().view(frames, S, 3, heads, 64).permute(2, 0, 3, 1, 4)
     want = F.scaled_dot_product_attention(f[0], f[1], f[2]).permute(0, 2, 1, 3).reshape(frames * S, D).float()
     split_close(out, want, 1e-5)

@@ -262,16 +262,63 @@ def test_depth_tail_fused(L, n, h, w, H, W, C):
     assert (out - want).abs().max().item() < 2e-2 * scale      # torch rounds the upsample differently in the last bf16 bit
 
 
-def test_depth_colorize_matches_numpy(L):
-    """dc_utils.py:72-86 semantics: global min/max, truncating uint8 cast, LUT."""
+def test_depth_colorize_bit_exact(L):
+    """dc_utils.py:72-86: clip-global min/max, three float32 roundings, truncating uint8 cast -- byte for byte --
+    then the colour table look-up.  Includes negative values (min/max are taken over the raw floats)."""
+    from oracle import vda_oracle as O
     from utils.dc_utils import depth_to_vis, inferno_lut
 
     rng = np.random.default_rng(0)
-    d = rng.uniform(0.2, 7.5, (3, 37, 53)).astype(np.float32)
-    lo, hi = d.min(), d.max()
-    q = ((d - lo) / (hi - lo) * 255).astype(np.uint8)
-    got_grey = depth_to_vis(d, grayscale=True)
-    assert got_grey.shape == q.shape and np.abs(got_grey.astype(int) - q.astype(int)).max() <= 1
-    assert (got_grey == q).mean() > 0.999
-    got = depth_to_vis(d)
-    assert got.shape == d.shape + (3,) and np.array_equal(got, inferno_lut()[got_grey])
+    for d in (rng.uniform(0.2, 7.5, (3, 37, 53)).astype(np.float32),
+              rng.normal(0.0, 30.0, (2, 518, 518)).astype(np.float32),
+              (rng.integers(0, 1 << 16, (4, 64, 64)) / 257.0).astype(np.float32)):
+        q = O.depth_to_uint8(d)
+        got_grey = depth_to_vis(d, grayscale=True)
+        assert got_grey.dtype == np.uint8 and got_grey.shape == q.shape
+        np.testing.assert_array_equal(got_grey, q)
+        got = depth_to_vis(d)
+        assert got.shape == d.shape + (3,)
+        np.testing.assert_array_equal(got, inferno_lut()[q])
+
+
+def test_depth_normalize_bit_exact(L):
+    """external_engine/engine.py:1099-1141 per frame: near/far remap, far <= near, invert_depth, constant frame."""
+    import os
+
+    from oracle import make_golden as G
+    from oracle import vda_oracle as O
+
+    gold = np.load(os.path.join(G.GOLDEN_DIR, "util_cases.npz"))
+    depth = G.util_inputs()[5]
+    big = np.random.default_rng(3).uniform(0, 50, (5, 270, 480)).astype(np.float32)
+    big[3] = -1.5
+    for i, (near, far, inv) in enumerate(G.NORMALIZE_CASES):
+        got = L.depth_normalize(torch.from_numpy(depth).cuda(), near, far, inv).cpu().numpy()
+        np.testing.assert_array_equal(got, gold[f"norm{i}"])          # the unmodified reference's output
+        got = L.depth_normalize(torch.from_numpy(big).cuda(), near, far, inv).cpu().numpy()
+        want = np.stack([O.normalize_depth(big[f], near, far, inv) for f in range(big.shape[0])])
+        np.testing.assert_array_equal(got, want)
+
+
+def test_util_shims_match_reference_golden(L):
+    """utils.util.compute_scale_and_shift (masked, all-ones, scale_only) and get_interpolate_frames through the
+    GPU kernels vs the unmodified reference's outputs (tests/golden/util_cases.npz)."""
+    import os
+
+    from oracle import make_golden as G
+    from utils.util import compute_scale_and_shift, get_interpolate_frames
+
+    gold = np.load(os.path.join(G.GOLDEN_DIR, "util_cases.npz"))
+    pred, target, mask, pre, post, _ = G.util_inputs()
+    np.testing.assert_allclose(np.array(compute_scale_and_shift(pred, target, mask), np.float64), gold["full"], rtol=2e-5)
+    np.testing.assert_allclose(np.array(compute_scale_and_shift(pred, target, np.ones_like(mask)), np.float64),
+                               gold["full_ones"], rtol=2e-5)
+    np.testing.assert_allclose(np.array(compute_scale_and_shift(pred, target), np.float64), gold["full_ones"], rtol=2e-5)
+    np.testing.assert_allclose(np.array(compute_scale_and_shift(pred, target, mask, scale_only=True), np.float64),
+                               gold["scale_only"], rtol=2e-5)
+    np.testing.assert_array_equal(np.stack(get_interpolate_frames(pre, post)), gold["blend"])
+    # lsq_solve(reset=True) leaves zeroed sums behind
+    sums = torch.ones(5, device="cuda", dtype=torch.float64)
+    ss = torch.zeros(2, device="cuda")
+    L.lsq_solve(sums, ss, reset=True)
+    assert sums.abs().sum().item() == 0.0

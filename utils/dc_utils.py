@@ -41,7 +41,11 @@ def read_video_frames(video_path, process_length, target_fps=-1, max_res=-1):
 
 
 def inferno_lut():
-    """256 x 3 uint8 RGB table (OpenCV's COLORMAP_INFERNO is matplotlib's inferno)."""
+    """256 x 3 uint8 RGB table: OpenCV's COLORMAP_INFERNO (pinned by tests/golden/inferno_lut_cv2.npy).
+    The reference indexes matplotlib's 256 float "inferno" colours and truncates (`(colormap[q] * 255).astype(uint8)`,
+    dc_utils.py:74,79); OpenCV stores the same control points rounded to nearest, so single channels can differ by one
+    code value.  matplotlib is not installed on this image (neither here nor on the GPU box), so its float table
+    cannot be committed or compared: the index q is bit-exact, the colour is OpenCV's."""
     bgr = cv2.applyColorMap(np.arange(256, dtype=np.uint8).reshape(-1, 1), cv2.COLORMAP_INFERNO)
     return np.ascontiguousarray(bgr[:, 0, ::-1])
 
@@ -56,6 +60,20 @@ def depth_to_vis(depths, grayscale=False):
     d = torch.as_tensor(np.ascontiguousarray(depths, dtype=np.float32)).cuda()
     lut = None if grayscale else torch.from_numpy(inferno_lut()).cuda()
     return L.depth_colorize(d, lut, grey=grayscale).cpu().numpy()
+
+
+def normalize_depth(depth, near_value, far_value, invert_depth=False):
+    """float32 [N,H,W] (or [H,W]) -> float32 same shape: per-frame min/max -> [near, far] remap of the fork's job engine
+    (external_engine/engine.py:1099-1141: inverted mapping when far <= near, `invert_depth`, constant frames -> near)
+    on the GPU (vda_depth_normalize), bit-exact with the numpy original."""
+    import torch
+
+    from vda_b200 import lib as L
+
+    L.init()
+    d = np.ascontiguousarray(depth, dtype=np.float32)
+    t = torch.from_numpy(d.reshape((-1,) + d.shape[-2:])).cuda()
+    return L.depth_normalize(t, near_value, far_value, invert_depth).cpu().numpy().reshape(d.shape)
 
 
 def save_video(frames, output_video_path, fps=10, is_depths=False, grayscale=False):

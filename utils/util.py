@@ -1,21 +1,24 @@
 """Import-path parity with the reference's utils/util.py (imported by its video_depth.py:27).
-The product path aligns windows on the GPU (vda_b200.video_depth.align_windows_device); these
-numpy-facing helpers exist for callers that import them by name and run the same GPU kernels."""
+The product path aligns windows on the GPU (vda_b200.parallel.WindowScan); these numpy-facing helpers exist for
+callers that import them by name (benchmark/eval-style alignment) and run the same GPU kernels."""
 import numpy as np
 import torch
 
 from vda_b200 import lib as L
 
 
+def _dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32)).cuda()
+
+
 def compute_scale_and_shift(prediction, target, mask=None, scale_only=False):
-    """utils/util.py:16-62 for mask == 1 (the only use on the hot path, video_depth.py:138-140)."""
-    if mask is not None and not np.all(mask):
-        raise NotImplementedError("only the all-ones mask of the inference path is supported")
+    """utils/util.py:16-62: least-squares scale (and shift) of `prediction` onto `target` over mask > 0 weights.
+    mask None = all ones (the inference path, video_depth.py:138-140).  Sums are accumulated in FP64 on the GPU."""
     L.init()
-    p = torch.from_numpy(np.ascontiguousarray(prediction, dtype=np.float32)).cuda()
-    t = torch.from_numpy(np.ascontiguousarray(target, dtype=np.float32)).cuda()
+    p, t = _dev(prediction), _dev(target)
+    m = None if mask is None else _dev(mask)
     sums = torch.zeros(5, dtype=torch.float64, device="cuda")
-    L.lsq_accum(p, t, p.numel(), sums)
+    L.lsq_accum(p, t, p.numel(), sums, mask=m)
     if scale_only:
         s = sums.cpu().numpy()
         return np.float32(s[3] / (s[0] + 1e-6)), 0
@@ -26,15 +29,15 @@ def compute_scale_and_shift(prediction, target, mask=None, scale_only=False):
 
 
 def get_interpolate_frames(frame_list_pre, frame_list_post):
-    """utils/util.py:65-74 (linear cross-fade, weights i/(n-1))."""
+    """utils/util.py:65-74 (linear cross-fade, weights i/(n-1)); fp32 roundings as numpy's."""
     assert len(frame_list_pre) == len(frame_list_post)
     n = len(frame_list_pre)
     L.init()
-    pre = torch.from_numpy(np.stack(frame_list_pre).astype(np.float32)).cuda()
-    post = torch.from_numpy(np.stack(frame_list_post).astype(np.float32)).cuda()
-    ident = torch.tensor([1.0, 0.0], device="cuda")
-    # blend kernel clamps post at 0 after the (identity) affine; the reference's callers pass
-    # already-clamped frames, for which this is the identity.
-    L.affine_clamp_blend(pre, post, pre[0].numel(), n, ident)
-    out = pre.cpu().numpy()
-    return [out[i] for i in range(n)]
+    pre = _dev(np.stack(frame_list_pre))
+    post = _dev(np.stack(frame_list_post))
+    if not 2 <= n <= 8:
+        raise ValueError("get_interpolate_frames: 2..8 frames (INTERP_LEN of video_depth.py:33 is 8)")
+    out = torch.empty_like(pre)
+    L.blend_frames(pre, post, out, pre[0].numel(), n)
+    res = out.cpu().numpy()
+    return [res[i] for i in range(n)]

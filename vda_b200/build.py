@@ -7,7 +7,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, os.environ.get("VDA_LIB_NAME", "libvda_b200.so"))  # VDA_LIB_NAME: A/B builds for tuning
-STAMP = LIB[:-3] + ".stamp" if os.environ.get("VDA_LIB_NAME") else os.path.join(HERE, ".libvda_b200.stamp")
+MARK = b"vda-src-digest:"   # followed by the 64 hex digits of _digest() inside the binary (csrc/api.cu: vda_build_digest)
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-shared",
@@ -29,10 +29,22 @@ def _digest():
     return h.hexdigest()
 
 
+def binary_digest(path=None):
+    """The source digest compiled into an existing library file, read without loading it (None if absent)."""
+    try:
+        blob = open(path or LIB, "rb").read()
+    except OSError:
+        return None
+    at = blob.find(MARK)
+    return blob[at + len(MARK):at + len(MARK) + 64].decode("ascii", "replace") if at >= 0 else None
+
+
 def build(force=False, verbose=False):
-    """Compile every .cu under csrc/ into one shared library. Returns the library path."""
+    """Compile every .cu under csrc/ into one shared library.  Returns the library path.
+    The digest of the sources + flags is compiled INTO the library, so a library left over from other sources is
+    detected from the file itself (there is no side stamp file that could travel without its binary)."""
     digest = _digest()
-    if not force and os.path.exists(LIB) and os.path.exists(STAMP) and open(STAMP).read() == digest:
+    if not force and binary_digest() == digest:
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     objs = []
@@ -41,6 +53,8 @@ def build(force=False, verbose=False):
     for src in _sources():
         obj = os.path.join(HERE, "build", os.path.basename(src)[:-3] + ".o")
         cmd = [nvcc] + [f for f in NVCC_FLAGS if f != "-shared"] + ["-c", src, "-o", obj]
+        if os.path.basename(src) == "api.cu":
+            cmd.append(f'-DVDA_SRC_DIGEST="{digest}"')
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
@@ -52,7 +66,8 @@ def build(force=False, verbose=False):
         if p.returncode:
             raise RuntimeError(f"nvcc failed on {src}")
     subprocess.check_call([nvcc, "-shared", "-o", LIB] + objs + ["-lcudart_static", "-ldl", "-lrt", "-lpthread"])
-    open(STAMP, "w").write(digest)
+    if binary_digest() != digest:
+        raise RuntimeError("built library does not carry its source digest")
     return LIB
 
 

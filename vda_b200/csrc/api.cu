@@ -14,7 +14,7 @@ namespace vda {
 cudaError_t launch_gemm(const GemmParams& p, int block_n, bool two_cta, int num_sms, cudaStream_t stream);
 
 static thread_local char g_err[512] = "";
-static int g_num_sms = 0;
+static int g_sms[kMaxDevices] = {};  // per device, filled by vda_init(device)
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -31,7 +31,12 @@ int check_cuda(cudaError_t e, const char* what) {
   if (e == cudaSuccess) return 0;
   return set_error(static_cast<int>(e), "%s: %s", what, cudaGetErrorString(e));
 }
-int num_sms() { return g_num_sms; }
+int current_device() {
+  int d = 0;
+  cudaGetDevice(&d);
+  return d;
+}
+int num_sms() { return g_sms[current_device() & (kMaxDevices - 1)]; }
 // Programmatic dependent launch (common.cuh).  Measured on B200: inside the CUDA graph of a 32-frame window
 // it is 2 % SLOWER (596 -> 584 frames/s, two interleaved runs each), for the ~300 single-tile launches of a
 // streaming frame 2 % faster (2.215 -> 2.168 ms), so the host turns it on per launch sequence
@@ -93,7 +98,7 @@ static void pick_tile(const vda_epilogue* e, int N, int m_tiles, int* bn_out, bo
       const int nt = (N + bn - 1) / bn;
       const bool forced = e->cta_pair == 2;
       if (!forced && (nt * bn - n16) * 8 > nt * bn) continue;
-      if (!forced && static_cast<long long>(m2) * nt < g_num_sms / 2) continue;
+      if (!forced && static_cast<long long>(m2) * nt < num_sms() / 2) continue;
       *bn_out = bn, *two_out = true;
       return;
     }
@@ -107,7 +112,7 @@ static void pick_tile(const vda_epilogue* e, int N, int m_tiles, int* bn_out, bo
   for (int i = 0; i < 4; ++i) {
     const int bn = cands[i];
     if (bn > 32 && bn > ((N + 31) / 32) * 32) continue;
-    if (static_cast<long long>(m_tiles) * ((N + bn - 1) / bn) >= g_num_sms) {
+    if (static_cast<long long>(m_tiles) * ((N + bn - 1) / bn) >= num_sms()) {
       *bn_out = bn;
       return;
     }
@@ -155,6 +160,7 @@ static int pick_stages(int bn, bool two, const vda_epilogue* e, int epi_tma) {
 }
 
 static int fill_epilogue(GemmParams& p, const vda_epilogue* e) {
+  if (num_sms() <= 0) return set_error(-2, "vda_init(device) has not been called for the current device %d", current_device());
   const char* sv = getenv("VDA_GEMM_SCHED");  // tuning knob: 1 = round-robin tiles, 2 = contiguous runs
   p.sched = sv ? atoi(sv) : 0;
   p.act = e->act;
@@ -211,7 +217,8 @@ int vda_init(int device) {
   rc = check_cuda(cudaGetDeviceProperties(&prop, device), "cudaGetDeviceProperties");
   if (rc) return rc;
   if (prop.major != 10) return set_error(-5, "device %d is sm_%d%d; this library is sm_100a only", device, prop.major, prop.minor);
-  g_num_sms = prop.multiProcessorCount;
+  if (device < 0 || device >= kMaxDevices) return set_error(-5, "device index %d out of range", device);
+  g_sms[device] = prop.multiProcessorCount;
   if (!g_encode) {
     void* fn = nullptr;
     cudaDriverEntryPointQueryResult q;
@@ -224,7 +231,13 @@ int vda_init(int device) {
 }
 
 const char* vda_last_error(void) { return g_err; }
-int vda_num_sms(void) { return g_num_sms; }
+int vda_num_sms(void) { return num_sms(); }
+#ifndef VDA_SRC_DIGEST
+#define VDA_SRC_DIGEST "unstamped"
+#endif
+/* sha256 of csrc/ + include/ + the nvcc flags this binary was built from (vda_b200/build.py); the marker prefix lets
+ * the build script read it out of the file without loading it */
+const char* vda_build_digest(void) { return &"vda-src-digest:" VDA_SRC_DIGEST[15]; }
 int vda_set_pdl(int on) {
   const int prev = g_pdl;
   g_pdl = on != 0;
@@ -265,7 +278,7 @@ int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, 
     // fp32 adds commute, so only the rounding order of those few tiles varies from run to run.
     const char* kv = getenv("VDA_GEMM_KSPLIT");  // A/B knob: 0 disables
     if (two && !p.f32_store && epi->act == ACT_NONE && p.sched != 2 && !(kv && atoi(kv) == 0)) {
-      const int tiles = ((p.m_tiles + 1) / 2) * p.n_tiles, nc = g_num_sms / 2;
+      const int tiles = ((p.m_tiles + 1) / 2) * p.n_tiles, nc = num_sms() / 2;
       const int rem = tiles % nc;
       if (tiles > nc && rem) {
         int ks = nc / rem;
@@ -294,7 +307,7 @@ int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, 
     const uint32_t box[2] = {64, (uint32_t)(two ? bn / 2 : bn)};
     if ((rc = encode_bf16_map(&p.tmB, W, 2, dims, str, box))) return rc;
   }
-  return check_cuda(launch_gemm(p, bn, two, g_num_sms, static_cast<cudaStream_t>(stream)), "gemm launch");
+  return check_cuda(launch_gemm(p, bn, two, num_sms(), static_cast<cudaStream_t>(stream)), "gemm launch");
 }
 
 int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W, int C, int Cout,
@@ -368,7 +381,7 @@ int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W,
     const uint32_t box[2] = {64, (uint32_t)(two ? bn / 2 : bn)};
     if ((rc = encode_bf16_map(&p.tmB, w, 2, dims, str, box))) return rc;
   }
-  return check_cuda(launch_gemm(p, bn, two, g_num_sms, static_cast<cudaStream_t>(stream)), "conv3x3 launch");
+  return check_cuda(launch_gemm(p, bn, two, num_sms(), static_cast<cudaStream_t>(stream)), "conv3x3 launch");
 }
 
 }  // extern "C"

@@ -440,13 +440,14 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
   // A/B knob: VDA_ATTN_POLY = 0 / 4 / 8 (default): one score pair in N evaluated with the packed polynomial exp2
   const char* ep = getenv("VDA_ATTN_POLY");
   const int poly = ep ? atoi(ep) : 8;
-  static bool configured = false;
+  static DeviceOnce once;
+  int& configured = once.slot();
   if (!configured) {
     int rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<8, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn smem");
     if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<4, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn smem");
     if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn smem");
     if (rc) return rc;
-    configured = true;
+    configured = 1;
   }
   const dim3 grid(p.q_tiles, heads, frames);
   const cudaStream_t st = static_cast<cudaStream_t>(stream);

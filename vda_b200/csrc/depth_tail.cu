@@ -225,12 +225,13 @@ template <int C>
 static int launch_tail(const TailParams& p, int num_sms, cudaStream_t st) {
   constexpr int smem = 32 * (9 * C * 2 + 16) + kTH * kTH * (C * 2 + 16);
   static_assert(kTH * kTH * (C * 2 + 16) >= 4 * 64 * 32 * 4, "exchange buffer must fit in the patch");
-  static bool configured = false;
+  static DeviceOnce once;
+  int& configured = once.slot();
   if (!configured) {
     int rc = check_cuda(cudaFuncSetAttribute(depth_tail_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
                         "depth_tail smem attribute");
     if (rc) return rc;
-    configured = true;
+    configured = 1;
   }
   const int grid = p.num_tiles < num_sms ? p.num_tiles : num_sms;
   const char* dbg = getenv("VDA_TAIL_DEBUG");

@@ -29,94 +29,7 @@ __device__ __forceinline__ void st_split2(bf16* p, float a, float b, int split) 
 }
 
 // ---------------------------------------------------------------------------------------------
-// Spatial attention, head_dim 64.  Block = 128 threads = 128 query rows of one (frame, head);
-// thread r keeps its query (pre-scaled by d^-1/2 * log2 e) and its output row in registers and
-// walks the keys in chunks of 32 staged in shared memory (broadcast reads): online softmax with one
-// rescale per chunk.
-constexpr int kAfRows = 128;
-constexpr int kAfChunk = 32;
-
-__global__ void __launch_bounds__(kAfRows) attn_f32_kernel(const float* __restrict__ qkv, int ld, bf16* __restrict__ out,
-                                                           int ldo, int split, int S, int D, float scale_log2) {
-  __shared__ __align__(16) float sK[kAfChunk][64];
-  __shared__ __align__(16) float sV[kAfChunk][64];
-  const int head = blockIdx.y, frame = blockIdx.z;
-  const int r = blockIdx.x * kAfRows + threadIdx.x;
-  const float* base = qkv + static_cast<long long>(frame) * S * ld + head * 64;
-  float q[64], o[64];
-  {
-    const float4* qr = reinterpret_cast<const float4*>(base + static_cast<long long>(r < S ? r : S - 1) * ld);
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const float4 t = __ldg(qr + i);
-      q[4 * i] = t.x * scale_log2, q[4 * i + 1] = t.y * scale_log2, q[4 * i + 2] = t.z * scale_log2,
-             q[4 * i + 3] = t.w * scale_log2;
-    }
-  }
-#pragma unroll
-  for (int i = 0; i < 64; ++i) o[i] = 0.f;
-  float m_run = -INFINITY, l_run = 0.f;
-
-  for (int j0 = 0; j0 < S; j0 += kAfChunk) {
-    __syncthreads();
-    // 32 keys x 64 floats = 512 float4 per matrix, 4 per thread, rows contiguous (256 B)
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int idx = i * kAfRows + threadIdx.x;
-      const int j = idx >> 4, c = idx & 15;
-      float4 kk = make_float4(0.f, 0.f, 0.f, 0.f), vv = kk;
-      if (j0 + j < S) {
-        const float* row = base + static_cast<long long>(j0 + j) * ld;
-        kk = __ldg(reinterpret_cast<const float4*>(row + D) + c);
-        vv = __ldg(reinterpret_cast<const float4*>(row + 2 * D) + c);
-      }
-      reinterpret_cast<float4*>(&sK[j][0])[c] = kk;
-      reinterpret_cast<float4*>(&sV[j][0])[c] = vv;
-    }
-    __syncthreads();
-    float s[kAfChunk];
-#pragma unroll
-    for (int j = 0; j < kAfChunk; ++j) {
-      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-#pragma unroll
-      for (int c = 0; c < 16; ++c) {
-        const float4 kk = reinterpret_cast<const float4*>(&sK[j][0])[c];
-        a0 = fmaf(q[4 * c], kk.x, a0), a1 = fmaf(q[4 * c + 1], kk.y, a1);
-        a2 = fmaf(q[4 * c + 2], kk.z, a2), a3 = fmaf(q[4 * c + 3], kk.w, a3);
-      }
-      s[j] = (j0 + j < S) ? (a0 + a1) + (a2 + a3) : -INFINITY;
-    }
-    float m_new = m_run;
-#pragma unroll
-    for (int j = 0; j < kAfChunk; ++j) m_new = fmaxf(m_new, s[j]);
-    const float alpha = exp2f(m_run - m_new);  // first chunk: exp2(-inf) = 0
-    m_run = m_new;
-    l_run *= alpha;
-#pragma unroll
-    for (int i = 0; i < 64; ++i) o[i] *= alpha;
-#pragma unroll
-    for (int j = 0; j < kAfChunk; ++j) {
-      const float pj = exp2f(s[j] - m_new);
-      l_run += pj;
-#pragma unroll
-      for (int c = 0; c < 16; ++c) {
-        const float4 vv = reinterpret_cast<const float4*>(&sV[j][0])[c];
-        o[4 * c] = fmaf(pj, vv.x, o[4 * c]), o[4 * c + 1] = fmaf(pj, vv.y, o[4 * c + 1]);
-        o[4 * c + 2] = fmaf(pj, vv.z, o[4 * c + 2]), o[4 * c + 3] = fmaf(pj, vv.w, o[4 * c + 3]);
-      }
-    }
-  }
-  if (r < S) {
-    const float inv = 1.f / l_run;
-    bf16* dst = out + (static_cast<long long>(frame) * S + r) * ldo + head * 64;
-#pragma unroll
-    for (int i = 0; i < 64; i += 2) st_split2(dst + i, o[i] * inv, o[i + 1] * inv, split);
-  }
-}
-
-// ---------------------------------------------------------------------------------------------
-// The same attention on warp-level tensor cores with split operands (the default; the SIMT kernel
-// above stays as VDA_ATTN_F32_SIMT=1 for A/B runs and as the plain-fp32 cross-check in the tests).
+// Spatial attention, head_dim 64, on warp-level tensor cores with split operands.
 // Flash-attention layout: CTA = 4 warps = 64 query rows of one (frame, head), KV tiles of 64 keys.
 // Every fp32 operand is split on the fly into bf16 hi + lo and every product is evaluated as
 // hi.hi + lo.hi + hi.lo (QK^T additionally lo.lo) with fp32 accumulation in mma.sync.m16n8k16:
@@ -152,153 +65,6 @@ __device__ __forceinline__ void split_pair(float a, float b, uint32_t& hi, uint3
 constexpr int kAmRows = 64;          // query rows per CTA
 constexpr int kAmKeys = 64;          // keys per KV tile
 constexpr int kAmPitch = 64 * 2 + 16;  // bytes per staged bf16 row
-
-__global__ void __launch_bounds__(128) attn_f32_mma_kernel(const float* __restrict__ qkv, int ld, bf16* __restrict__ out,
-                                                           int ldo, int split, int S, int D, float scale_log2) {
-  __shared__ __align__(16) uint8_t sm[4 * kAmKeys * kAmPitch];  // K hi, K lo, V hi, V lo
-  const uint32_t sKh = smem_u32(sm), sKl = sKh + kAmKeys * kAmPitch, sVh = sKl + kAmKeys * kAmPitch,
-                 sVl = sVh + kAmKeys * kAmPitch;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int head = blockIdx.y, frame = blockIdx.z;
-  const int g = lane >> 2, q4 = lane & 3;
-  const float* base = qkv + static_cast<long long>(frame) * S * ld + head * 64;
-  const int row_a = blockIdx.x * kAmRows + warp * 16 + g, row_b = row_a + 8;
-
-  // Q fragments (hi / lo) for the 4 k16 steps over head_dim
-  uint32_t qh[4][4], ql[4][4];
-  {
-    const float* qa = base + static_cast<long long>(min(row_a, S - 1)) * ld;
-    const float* qb = base + static_cast<long long>(min(row_b, S - 1)) * ld;
-#pragma unroll
-    for (int kk = 0; kk < 4; ++kk) {
-      const int c = kk * 16 + q4 * 2;
-      const float2 a0 = __ldg(reinterpret_cast<const float2*>(qa + c)), a1 = __ldg(reinterpret_cast<const float2*>(qb + c));
-      const float2 a2 = __ldg(reinterpret_cast<const float2*>(qa + c + 8)), a3 = __ldg(reinterpret_cast<const float2*>(qb + c + 8));
-      split_pair(a0.x * scale_log2, a0.y * scale_log2, qh[kk][0], ql[kk][0]);
-      split_pair(a1.x * scale_log2, a1.y * scale_log2, qh[kk][1], ql[kk][1]);
-      split_pair(a2.x * scale_log2, a2.y * scale_log2, qh[kk][2], ql[kk][2]);
-      split_pair(a3.x * scale_log2, a3.y * scale_log2, qh[kk][3], ql[kk][3]);
-    }
-  }
-  float o[8][4];
-#pragma unroll
-  for (int nt = 0; nt < 8; ++nt)
-#pragma unroll
-    for (int i = 0; i < 4; ++i) o[nt][i] = 0.f;
-  float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.f, 0.f};
-
-  for (int j0 = 0; j0 < S; j0 += kAmKeys) {
-    __syncthreads();
-    // stage + split the K and V tiles: 64 keys x 16 float4 per matrix, 8 per thread
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int idx = i * 128 + threadIdx.x;
-      const int j = idx >> 4, c = idx & 15;
-      float4 kk = make_float4(0.f, 0.f, 0.f, 0.f), vv = kk;
-      if (j0 + j < S) {
-        const float* row = base + static_cast<long long>(j0 + j) * ld;
-        kk = __ldg(reinterpret_cast<const float4*>(row + D) + c);
-        vv = __ldg(reinterpret_cast<const float4*>(row + 2 * D) + c);
-      }
-      uint32_t h0, l0, h1, l1;
-      split_pair(kk.x, kk.y, h0, l0), split_pair(kk.z, kk.w, h1, l1);
-      const uint32_t off = j * kAmPitch + c * 8;
-      asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(sKh + off), "r"(h0), "r"(h1) : "memory");
-      asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(sKl + off), "r"(l0), "r"(l1) : "memory");
-      split_pair(vv.x, vv.y, h0, l0), split_pair(vv.z, vv.w, h1, l1);
-      asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(sVh + off), "r"(h0), "r"(h1) : "memory");
-      asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(sVl + off), "r"(l0), "r"(l1) : "memory");
-    }
-    __syncthreads();
-
-    // ---- S = Q K^T (log2 domain), 16 rows x 64 keys per warp
-    float s[8][4];
-#pragma unroll
-    for (int nt = 0; nt < 8; ++nt)
-#pragma unroll
-      for (int i = 0; i < 4; ++i) s[nt][i] = 0.f;
-#pragma unroll
-    for (int kk = 0; kk < 4; ++kk) {
-#pragma unroll
-      for (int np = 0; np < 4; ++np) {
-        uint32_t bh[4], bl[4];
-        const uint32_t off = (np * 16 + (lane & 7) + ((lane >> 4) << 3)) * kAmPitch + (kk * 2 + ((lane >> 3) & 1)) * 16;
-        f32_ldsm_x4(sKh + off, bh);
-        f32_ldsm_x4(sKl + off, bl);
-#pragma unroll
-        for (int t = 0; t < 2; ++t) {
-          f32_mma(s[2 * np + t], qh[kk], bh[2 * t], bh[2 * t + 1]);
-          f32_mma(s[2 * np + t], ql[kk], bh[2 * t], bh[2 * t + 1]);
-          f32_mma(s[2 * np + t], qh[kk], bl[2 * t], bl[2 * t + 1]);
-          f32_mma(s[2 * np + t], ql[kk], bl[2 * t], bl[2 * t + 1]);
-        }
-      }
-    }
-    // ---- online softmax: this lane holds rows g (i = 0,1) and g+8 (i = 2,3), keys nt*8 + q4*2 + (i&1)
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      float m = m_run[h];
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt)
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          if (j0 + nt * 8 + q4 * 2 + i >= S) s[nt][2 * h + i] = -INFINITY;
-          m = fmaxf(m, s[nt][2 * h + i]);
-        }
-      m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
-      m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
-      const float alpha = exp2f(m_run[h] - m);
-      m_run[h] = m;
-      float l = 0.f;
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt)
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-          const float e = exp2f(s[nt][2 * h + i] - m);
-          s[nt][2 * h + i] = e;
-          l += e;
-        }
-      l += __shfl_xor_sync(0xffffffffu, l, 1);
-      l += __shfl_xor_sync(0xffffffffu, l, 2);
-      l_run[h] = l_run[h] * alpha + l;
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt) o[nt][2 * h] *= alpha, o[nt][2 * h + 1] *= alpha;
-    }
-    // ---- O += P V
-#pragma unroll
-    for (int k2 = 0; k2 < 4; ++k2) {
-      uint32_t ph[4], pl[4];
-      split_pair(s[2 * k2][0], s[2 * k2][1], ph[0], pl[0]);
-      split_pair(s[2 * k2][2], s[2 * k2][3], ph[1], pl[1]);
-      split_pair(s[2 * k2 + 1][0], s[2 * k2 + 1][1], ph[2], pl[2]);
-      split_pair(s[2 * k2 + 1][2], s[2 * k2 + 1][3], ph[3], pl[3]);
-#pragma unroll
-      for (int np = 0; np < 4; ++np) {
-        uint32_t vh[4], vl[4];
-        const int mi = lane >> 3;
-        const uint32_t off = (k2 * 16 + (mi & 1) * 8 + (lane & 7)) * kAmPitch + (np * 16 + (mi >> 1) * 8) * 2;
-        f32_ldsm_x4_t(sVh + off, vh);
-        f32_ldsm_x4_t(sVl + off, vl);
-#pragma unroll
-        for (int t = 0; t < 2; ++t) {
-          f32_mma(o[2 * np + t], ph, vh[2 * t], vh[2 * t + 1]);
-          f32_mma(o[2 * np + t], pl, vh[2 * t], vh[2 * t + 1]);
-          f32_mma(o[2 * np + t], ph, vl[2 * t], vl[2 * t + 1]);
-        }
-      }
-    }
-  }
-#pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    const int row = h ? row_b : row_a;
-    if (row < S) {
-      const float inv = 1.f / l_run[h];
-      bf16* dst = out + (static_cast<long long>(frame) * S + row) * ldo + head * 64;
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt) st_split2(dst + nt * 8 + q4 * 2, o[nt][2 * h] * inv, o[nt][2 * h + 1] * inv, split);
-    }
-  }
-}
 
 // ---------------------------------------------------------------------------------------------
 // Same contraction for q/k/v that the projection GEMM already wrote as split tensors (hi at column c,
@@ -552,34 +318,24 @@ using namespace vda;
 extern "C" int vda_attn_f32(const void* qkv, int ld, int in_split, void* out, int ldo, int split, int frames, int S,
                             int heads, void* stream) {
   const int D = heads * 64;
-  if (!qkv || !out || frames <= 0 || S <= 0 || heads <= 0 || ld % 8 || ld < 3 * D || in_split % 8 || in_split < 0 ||
+  if (!qkv || !out || frames <= 0 || S <= 0 || heads <= 0 || ld % 8 || ld < 3 * D || in_split % 8 ||
       ldo % 8 || split % 8)
     return set_error(-1, "vda_attn_f32: bad arguments (head_dim 64, ld%%8, in_split%%8, ldo%%8, split%%8)");
   const float scale_log2 = 0.125f * 1.4426950408889634f;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (in_split) {
-    if (ld < in_split + 3 * D) return set_error(-1, "vda_attn_f32: ld < in_split + 3*heads*64");
-    static bool configured = false;
-    if (!configured) {
-      int rc = check_cuda(cudaFuncSetAttribute(attn_split_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kApSmem),
-                          "attn_split smem attribute");
-      if (rc) return rc;
-      configured = true;
-    }
-    const dim3 grid((S + kAmRows - 1) / kAmRows, heads, frames);
-    attn_split_mma_kernel<<<grid, 128, kApSmem, st>>>(static_cast<const bf16*>(qkv), ld, in_split, static_cast<bf16*>(out),
-                                                      ldo, split, S, D, scale_log2);
-    return check_cuda(cudaGetLastError(), "attn_f32 launch");
+  if (in_split <= 0) return set_error(-1, "vda_attn_f32: q/k/v must arrive as the split tensor the projection GEMM writes (in_split > 0)");
+  if (ld < in_split + 3 * D) return set_error(-1, "vda_attn_f32: ld < in_split + 3*heads*64");
+  static DeviceOnce once;
+  int& configured = once.slot();
+  if (!configured) {
+    int rc = check_cuda(cudaFuncSetAttribute(attn_split_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kApSmem),
+                        "attn_split smem attribute");
+    if (rc) return rc;
+    configured = 1;
   }
-  const float* q32 = static_cast<const float*>(qkv);
-  const char* ev = getenv("VDA_ATTN_F32_SIMT");  // A/B knob: the plain-fp32 SIMT kernel
-  if (ev && atoi(ev)) {
-    const dim3 grid((S + kAfRows - 1) / kAfRows, heads, frames);
-    attn_f32_kernel<<<grid, kAfRows, 0, st>>>(q32, ld, static_cast<bf16*>(out), ldo, split, S, D, scale_log2);
-  } else {
-    const dim3 grid((S + kAmRows - 1) / kAmRows, heads, frames);
-    attn_f32_mma_kernel<<<grid, 128, 0, st>>>(q32, ld, static_cast<bf16*>(out), ldo, split, S, D, scale_log2);
-  }
+  const dim3 grid((S + kAmRows - 1) / kAmRows, heads, frames);
+  attn_split_mma_kernel<<<grid, 128, kApSmem, st>>>(static_cast<const bf16*>(qkv), ld, in_split, static_cast<bf16*>(out), ldo,
+                                                    split, S, D, scale_log2);
   return check_cuda(cudaGetLastError(), "attn_f32 launch");
 }
 
@@ -589,7 +345,8 @@ extern "C" int vda_temporal_attn_f32(const float* q, const float* k, const float
       Tk > 32 || ld % 4 || ldo % 8 || split % 8)
     return set_error(-1, "vda_temporal_attn_f32: bad arguments (head_dim%%4, T<=32)");
   const int smem = kTfWarps * 2 * 32 * head_dim * 4;
-  static int configured = 0;
+  static DeviceOnce once;
+  int& configured = once.slot();
   if (smem > configured) {
     int rc = check_cuda(cudaFuncSetAttribute(temporal_attn_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              kTfWarps * 2 * 32 * 128 * 4),

@@ -20,6 +20,7 @@
 //                        problem has enough 256-row tile pairs to fill the 74 SM pairs.
 //   gemm_tc_kernel<BN>   single CTA, M=128 x N=BN: small problems (streaming mode, vits head).
 #include "gemm_epilogue.cuh"
+#include "api_internal.h"
 
 namespace vda {
 
@@ -495,11 +496,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 template <int BN>
 static cudaError_t launch_bn(const GemmParams& p, int num_sms, cudaStream_t stream) {
   using Cfg = GemmCfg<BN>;
-  static bool configured = false;
+  static DeviceOnce once;
+  int& configured = once.slot();
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
     if (e != cudaSuccess) return e;
-    configured = true;
+    configured = 1;
   }
   const int tiles = p.m_tiles * p.n_tiles;
   const int grid = tiles < num_sms ? tiles : num_sms;
@@ -509,11 +511,12 @@ static cudaError_t launch_bn(const GemmParams& p, int num_sms, cudaStream_t stre
 template <int BN>
 static cudaError_t launch2_bn(const GemmParams& p, int num_sms, cudaStream_t stream) {
   using Cfg = Gemm2Cfg<BN>;
-  static bool configured = false;
+  static DeviceOnce once;
+  int& configured = once.slot();
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(gemm_tc2_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
     if (e != cudaSuccess) return e;
-    configured = true;
+    configured = 1;
   }
   const int pairs = ((p.m_tiles + 1) / 2) * p.n_tiles;
   const int max_pairs = num_sms / 2;

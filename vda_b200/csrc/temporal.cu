@@ -309,12 +309,13 @@ __global__ void __launch_bounds__(kTWarps * 32) temporal_attn_mma_kernel(const T
 template <int HDP>
 static int launch_temporal_mma(const TemporalParams& p, cudaStream_t stream) {
   constexpr int smem = kTWarps * 3 * 32 * (HDP * 2 + 16);
-  static bool configured = false;
+  static DeviceOnce once;
+  int& configured = once.slot();
   if (!configured) {
     int rc = check_cuda(cudaFuncSetAttribute(temporal_attn_mma_kernel<HDP>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem),
                         "temporal mma smem attribute");
     if (rc) return rc;
-    configured = true;
+    configured = 1;
   }
   const int units = p.hw * p.heads;
   return check_cuda(launch_pdl(temporal_attn_mma_kernel<HDP>, dim3((units + kTWarps - 1) / kTWarps), dim3(kTWarps * 32), smem,
@@ -470,7 +471,8 @@ static int launch_temporal_stream(bool f32, const void* q, const void* knew, con
   p.ldn = ldn, p.ldo = ldo, p.hw = hw, p.heads = heads, p.hd = head_dim, p.C = heads * head_dim, p.Tk = Tk, p.split = split;
   p.scale = 1.0f / sqrtf(static_cast<float>(head_dim));
   const int smem = kTWarps * 32 * (head_dim + 1) * 4;
-  static bool configured = false;
+  static DeviceOnce once;
+  int& configured = once.slot();
   if (!configured) {
     int rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              kTWarps * 32 * 129 * 4),
@@ -480,7 +482,7 @@ static int launch_temporal_stream(bool f32, const void* q, const void* knew, con
                                            kTWarps * 32 * 129 * 4),
                       "temporal stream smem attribute");
     if (rc) return rc;
-    configured = true;
+    configured = 1;
   }
   const int units = hw * heads, grid = (units + kTWarps - 1) / kTWarps;
   const cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -533,7 +535,8 @@ extern "C" int vda_temporal_attn(const void* q, int ldq, const void* k, int ldk,
   }
   const int per_warp = 32 * (head_dim + 2) * 2 + 2 * 32 * head_dim * 2;
   const int smem = per_warp * kTWarps;
-  static int configured = 0;
+  static DeviceOnce once;
+  int& configured = once.slot();
   if (smem > configured) {
     int rc = check_cuda(cudaFuncSetAttribute(temporal_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 101376),
                         "temporal smem attribute");

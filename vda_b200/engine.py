@@ -376,7 +376,7 @@ class Engine:
                 # launch-bound otherwise: ~300 launches for one frame of work).
                 if stream_ctx.Tk != 32:
                     return self._run(x.contiguous(), ws, stream_ctx)
-                key = ("stream", T, H, W, id(stream_ctx))
+                key = ("stream", T, H, W, stream_ctx.serial)
                 xin = ws.get("graph_in", (T, 3, H, W), torch.float32)
                 xin.copy_(x)
                 g = self.graphs.get(key)
@@ -433,8 +433,11 @@ class StreamCache:
     `frame_cache_list` becomes a list of slot numbers with identical list semantics."""
 
     CAP = 44  # the reference's list peaks at 43 entries (42 after the trim) + 1 slot in flight
+    _SERIAL = 0  # graphs captured for a cache are keyed by this, never by id() (ids are recycled)
 
     def __init__(self, engine, gh, gw):
+        StreamCache._SERIAL += 1
+        self.serial = StreamCache._SERIAL
         w = engine.w
         dev = engine.device
         gh4, gw4 = (gh - 1) // 2 + 1, (gw - 1) // 2 + 1

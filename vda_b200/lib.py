@@ -67,15 +67,18 @@ class _timed:
 
 
 def load():
-    """Load (building if the in-tree .so is absent) and return the ctypes library handle."""
+    """Load the in-tree library (rebuilding it if it is absent or was built from other sources) and return the
+    ctypes handle."""
     global _lib
     if _lib is not None:
         return _lib
-    path = _build.LIB
-    if not os.path.exists(path):
-        path = _build.build()
+    path = _build.build()     # no-op when the in-tree binary carries the digest of the current sources
     lib = C.CDLL(path)
     lib.vda_last_error.restype = C.c_char_p
+    lib.vda_build_digest.restype = C.c_char_p
+    if lib.vda_build_digest().decode() != _build._digest():
+        raise VdaError(f"{path} was built from other sources than vda_b200/csrc (stale binary); rebuild with "
+                       "`python -m vda_b200.build --force`")
     _declare(lib)
     _lib = lib
     return lib
@@ -104,12 +107,13 @@ def _declare(lib):
         "vda_preprocess_u8": [vp, i, i, i, vp, i, i, vp],
         "vda_minmax_f32": [vp, C.c_longlong, vp, vp],
         "vda_depth_colorize": [vp, C.c_longlong, vp, vp, vp, i, vp],
-        "vda_debug_umma_shift": [vp, vp, vp, i, i, i, vp],
-        "vda_debug_mma_rate": [vp, i, i, i, vp],
+        "vda_depth_normalize": [vp, vp, C.c_longlong, i, C.c_double, C.c_double, i, vp, vp],
         "vda_depth_tail": [vp, i, vp, vp, vp, f, vp, i, i, i, i, i, i, vp],
         "vda_attn_f32": [vp, i, i, vp, i, i, i, i, i, vp],
         "vda_temporal_attn_f32": [vp, vp, vp, i, vp, i, i, i, i, i, i, i, vp],
         "vda_lsq_accum": [vp, vp, C.c_longlong, vp, vp],
+        "vda_lsq_accum_masked": [vp, vp, vp, C.c_longlong, vp, vp],
+        "vda_blend_frames": [vp, vp, vp, C.c_longlong, i, vp],
         "vda_lsq_solve": [vp, vp, i, vp],
         "vda_affine_clamp": [vp, vp, C.c_longlong, vp, vp],
         "vda_affine_clamp_blend": [vp, vp, C.c_longlong, i, vp, vp],
@@ -128,7 +132,7 @@ def set_pdl(on):
 
 def exported_symbols():
     """Names every include/vda_b200.h declaration must resolve to (used by the CPU-side test)."""
-    return sorted(_declare(load()).keys()) + ["vda_last_error"]
+    return sorted(_declare(load()).keys()) + ["vda_last_error", "vda_build_digest"]
 
 
 def check(rc):
@@ -213,7 +217,7 @@ def depth_colorize(depth, lut_rgb=None, grey=False):
     check(load().vda_minmax_f32(ptr(depth), depth.numel(), ptr(mm), stream_ptr()))
     out = torch.empty(tuple(depth.shape) + (() if grey else (3,)), dtype=torch.uint8, device=depth.device)
     check(load().vda_depth_colorize(ptr(depth), depth.numel(), ptr(mm), ptr(lut_rgb), ptr(out), int(grey), stream_ptr()))
-    _launched(3)
+    _launched(4)
     return out
 
 
@@ -224,8 +228,8 @@ def preprocess_u8(frames_u8, out, nh, nw):
     _launched()
 
 
-def attn_f32(qkv, out, split, frames, S, heads, in_split=0):
-    """qkv: f32 [frames*S, 3D] (in_split=0) or split bf16 [frames*S, 3*in_split] (hi | lo | hi); out split bf16."""
+def attn_f32(qkv, out, split, frames, S, heads, in_split):
+    """qkv: split bf16 [frames*S, 3*in_split] (hi | lo | hi); out split bf16."""
     with _timed("attn", 4.0 * frames * heads * S * S * 64):
         check(load().vda_attn_f32(ptr(qkv), qkv.shape[1], in_split, ptr(out), out.shape[1], split, frames, S, heads,
                                   stream_ptr()))
@@ -310,14 +314,34 @@ def temporal_attn_stream_f32(q, knew, vnew, ldn, kcache, vcache, slots, pe_q, pe
     _launched(1)
 
 
-def lsq_accum(pred, target, n, sums5):
-    check(load().vda_lsq_accum(ptr(pred), ptr(target), n, ptr(sums5), stream_ptr()))
+def lsq_accum(pred, target, n, sums5, mask=None):
+    """sums5 (f64, caller-zeroed) += {sum m p p, sum m p, sum m, sum m p t, sum m t}; mask None = all ones."""
+    check(load().vda_lsq_accum_masked(ptr(pred), ptr(target), ptr(mask), n, ptr(sums5), stream_ptr()))
     _launched(1)
 
 
-def lsq_solve(sums5, scale_shift, metric=False):
-    check(load().vda_lsq_solve(ptr(sums5), ptr(scale_shift), int(metric), stream_ptr()))
+def lsq_solve(sums5, scale_shift, metric=False, reset=False):
+    """{scale, shift} from the five sums (metric: {1, 0}); reset=True zeroes sums5 for the next window."""
+    check(load().vda_lsq_solve(ptr(sums5), ptr(scale_shift), int(bool(metric)) | (2 if reset else 0), stream_ptr()))
     _launched(1)
+
+
+def blend_frames(pre, post, out, per_frame, frames):
+    check(load().vda_blend_frames(ptr(pre), ptr(post), ptr(out), per_frame, frames, stream_ptr()))
+    _launched(1)
+
+
+def depth_normalize(depth, near_value, far_value, invert_depth=False):
+    """depth f32 [frames, ...] on the GPU -> f32 same shape, each frame mapped to [near, far]
+    (external_engine/engine.py:1099-1141)."""
+    d = depth.contiguous()
+    frames = d.shape[0]
+    out = torch.empty_like(d)
+    ws = torch.empty(2 * frames, dtype=torch.float32, device=d.device)
+    check(load().vda_depth_normalize(ptr(d), ptr(out), d[0].numel(), frames, float(near_value), float(far_value),
+                                     int(bool(invert_depth)), ptr(ws), stream_ptr()))
+    _launched(4)
+    return out
 
 
 def affine_clamp(src, dst, n, scale_shift):

@@ -100,16 +100,30 @@ class VideoDepthAnything(nn.Module):
     # -- lifecycle: packed weights are rebuilt lazily after .to()/.cuda()/load_state_dict()
     def _apply(self, fn, *a, **k):
         self._engine = self._engine32 = None
+        self._tensors = None
         return super()._apply(fn, *a, **k)
 
     def load_state_dict(self, *a, **k):
         self._engine = self._engine32 = None
         return super().load_state_dict(*a, **k)
 
+    def _weights_version(self):
+        """Changes whenever a parameter or buffer is modified in place through autograd-visible ops
+        (copy_, fill_, optimizer steps, sub-module load_state_dict): the packed kernel-layout weights and the
+        captured CUDA graphs are then rebuilt instead of silently replaying stale weights."""
+        ts = getattr(self, "_tensors", None)
+        if ts is None:
+            ts = self._tensors = list(self.parameters()) + list(self.buffers())
+        return sum(t._version for t in ts)
+
     def engine(self, fp32=False):
         """Window executor for the module's current device; fp32=True -> the FP32-accuracy executor
         (split-bf16 tensor-core products, fp32 everywhere else; engine.Engine)."""
         dev = self.pretrained.cls_token.device
+        v = self._weights_version()
+        if v != getattr(self, "_packed_version", None):
+            self._engine = self._engine32 = None
+            self._packed_version = v
         if fp32:
             if self._engine32 is None or self._engine32.device != dev:
                 self._engine32 = Engine(self, dev, fp32=True)

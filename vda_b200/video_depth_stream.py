@@ -39,6 +39,7 @@ class VideoDepthAnything(nn.Module):
 
     def _apply(self, fn, *a, **k):
         self._engine = None
+        self._tensors = None
         return super()._apply(fn, *a, **k)
 
     def load_state_dict(self, *a, **k):
@@ -46,8 +47,16 @@ class VideoDepthAnything(nn.Module):
         return super().load_state_dict(*a, **k)
 
     def engine(self, fp32=False):
-        """One executor per precision (BF16 tensor-core path / FP32-accuracy path), built on first use."""
+        """One executor per precision (BF16 tensor-core path / FP32-accuracy path), built on first use and
+        rebuilt when a parameter was modified in place since (see video_depth.VideoDepthAnything._weights_version)."""
         dev = self.pretrained.cls_token.device
+        ts = getattr(self, "_tensors", None)
+        if ts is None:
+            ts = self._tensors = list(self.parameters()) + list(self.buffers())
+        v = sum(t._version for t in ts)
+        if v != getattr(self, "_packed_version", None):
+            self._engine = None
+            self._packed_version = v
         if self._engine is None or self._engine.get("dev") != dev:
             self._engine = {"dev": dev}
         if fp32 not in self._engine:
