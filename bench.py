@@ -1,6 +1,6 @@
 """Headline benchmark (BASELINE.json): frames/s of VDA-L 518x518 32-frame windows on N B200s.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--arch vitl]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--arch vitl] [--no-extras]
 
 A "step" is one pass of the hot path (VideoDepthAnything.forward, video_depth.py:61-68) over one
 synthetic 32-frame window per rank.  N>1 is launched by torchrun, one rank per GPU; windows are
@@ -8,14 +8,23 @@ independent so ranks share nothing on the data path ("scaling": 
   value : 32*K*N / max-over-ranks device time, the window already resident in HBM.
   e2e   : the same through the public module call with HOST buffers: pinned fp32 window -> H2D ->
           forward -> D2H of the fp32 depth, all inside the timed region.
+  p50_window_latency_ms : median of >= 20 individually event-timed window forwards (BASELINE.json's second metric).
   roofline : the tcgen05 GEMM kernel (gemm_tc_kernel, A_PLAIN launches) timed per launch with CUDA
           events on the launching stream over a second pass of the same K steps launched eagerly
           (the timed pass replays a CUDA graph, which cannot hold events); FLOPs = 2*M*N*K per launch.
-  cpu_baseline : the oracle (CPU restatement of the reference forward) on the host cores, on a
-          bounded sample (a T=--cpu-frames window of the same architecture and resolution).
---impl reference runs only that CPU arm (rank 0) with all host threads.
+  cpu_baseline : the oracle (CPU restatement of the reference forward) on ALL host cores, on a bounded sample of the
+          same workload (the largest T <= 32 whose pass fits the time budget); N=1 only.
+  extra : the other BASELINE.json configs, each through the public API with host buffers in and out:
+          video_1024f_vitl (config 3: infer_video_depth, windows sharded round-robin over the N ranks, the NCCL
+          exchange + alignment + downloads inside the timed region), and at N=1 video_512f_vitb_metric_720p
+          (config 4), stream_vits_518 / stream_vitl_518 (config 5, per-frame latency), cpu_config1_vits_fp32
+          (config 1: the reference's CPU-runnable case on the host cores) and torch_eager_same_gpu (the
+          reference's op sequence as eager PyTorch on this GPU: fp32, autocast fp16/bf16, and autocast fp16 with
+          F.scaled_dot_product_attention in place of attention.py:53-59).
+--impl reference runs only the CPU arm (rank 0) with all host threads.
 """
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -29,7 +38,7 @@ if ROOT not in sys.path:
 
 METRIC = "frames/sec VDA-L 518x518 32-frame windows"
 UNIT = "frames/s"
-NCU_FC1 = "r01c_ncu_fc1.json"   # ncu --set full capture of the fc1 launch the roofline's `traffic` is read from
+NCU_FC1 = "r02_ncu_fc1.json"   # ncu --set full capture of the fc1 launch the roofline's `traffic` is read from
 
 
 def parse():
@@ -41,11 +50,11 @@ def parse():
     ap.add_argument("--arch", default="vitl", choices=["vits", "vitb", "vitl"])
     ap.add_argument("--frames", type=int, default=32)
     ap.add_argument("--size", type=int, default=518)
-    ap.add_argument("--cpu-frames", type=int, default=2, help="frames of the CPU-baseline sample window")
+    ap.add_argument("--cpu-frames", type=int, default=0, help="frames of the CPU-baseline sample window (0 = largest that fits --cpu-budget)")
+    ap.add_argument("--cpu-budget", type=float, default=45.0, help="seconds one CPU-baseline pass may take")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--torch-eager-gpu", action="store_true",
-                    help="also time the oracle (plain torch ops, the reference's own op sequence) on this GPU: fp32 and "
-                         "autocast bf16 -- SURVEY.md 8(d)'s second comparand; reported, never the measured product")
+    ap.add_argument("--no-extras", action="store_true", help="headline line only (profiling runs)")
+    ap.add_argument("--video-frames", type=int, default=1024)
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"],
                     help="fp32 = the FP32-accuracy mode (split-bf16 products, DESIGN.md 4b); not the headline config")
     return ap.parse_args()
@@ -60,34 +69,89 @@ def config_of(a):
             "l2": "per-step working set (several GB of activations) is larger than the 126 MB L2; no explicit flush"}
 
 
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+# ----------------------------------------------------------------------------- synthetic video
+def synth_video(n, h, w, seed=0):
+    """uint8 RGB [n,h,w,3]: a smooth pattern translating over time + uniform noise (so the alignment sees
+    correlated frames).  Cheap: crops of one periodic canvas plus a cycled noise tile."""
+    import numpy as np
+
+    rng = np.random.default_rng(seed)
+    px, py = 128, 96                                   # periods of the pattern in x / y
+    yy, xx = np.mgrid[0:h + py, 0:w + px].astype(np.float32)
+    canvas = np.stack([127 + 90 * np.sin(2 * np.pi * xx / px + c) * np.cos(2 * np.pi * yy / py - 0.5 * c) for c in range(3)], -1)
+    noise = rng.integers(-12, 13, (8, h, w, 3)).astype(np.float32)
+    out = np.empty((n, h, w, 3), np.uint8)
+    buf = np.empty((h, w, 3), np.float32)
+    for t in range(n):
+        dx, dy = (3 * t) % px, (2 * t) % py
+        np.add(canvas[dy:dy + h, dx:dx + w], noise[t & 7], out=buf)
+        np.clip(buf, 0, 255, out=buf)
+        out[t] = buf                       # truncating cast on assignment
+    return out
+
+
 # ----------------------------------------------------------------------------- CPU arm (oracle)
-def cpu_arm(a, steps, warmup):
-    """Times the oracle forward (fp32, torch CPU, all host threads) on a T=cpu_frames window."""
+def _cpu_pass(sd, arch, T, size, O, torch):
+    x = torch.randn(1, T, 3, size, size, generator=torch.Generator().manual_seed(0))
+    t0 = time.perf_counter()
+    O.forward(sd, x, arch)
+    return time.perf_counter() - t0
+
+
+def cpu_arm(a, steps=1, with_config1=True):
+    """Times the oracle forward (fp32, torch CPU, every host core) on the headline architecture: a short T=2 pass
+    warms the thread pool and calibrates, then the largest T in {32,16,8,4,2} whose pass fits --cpu-budget is timed
+    `steps` times.  with_config1: also BASELINE configs[0] exactly (vits, T=32, 518x518, fp32), one pass."""
     import torch
 
     from oracle import refload
     from oracle import vda_oracle as O
 
     torch.set_grad_enabled(False)
+    cores = host_cores()
+    torch.set_num_threads(cores)       # torchrun exports OMP_NUM_THREADS=1: without this the arm runs on one core
     cores = torch.get_num_threads()
     sd = refload.seeded_state_dict(a.arch, 0)
-    T = a.cpu_frames
-    x = torch.randn(1, T, 3, a.size, a.size, generator=torch.Generator().manual_seed(0))
-    for _ in range(warmup):
-        O.forward(sd, x, a.arch)
-    t0 = time.perf_counter()
-    for _ in range(steps):
-        O.forward(sd, x, a.arch)
-    dt = (time.perf_counter() - t0) / steps
-    return {"value": T / dt, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"oracle forward on a {T}-frame {a.size}x{a.size} {a.arch} window, fp32 torch CPU, "
-                      f"{steps} timed pass(es) of {dt:.2f} s"}, dt
+    t2 = _cpu_pass(sd, a.arch, 2, a.size, O, torch)
+    t2 = min(t2, _cpu_pass(sd, a.arch, 2, a.size, O, torch))
+    if a.cpu_frames:
+        T = a.cpu_frames
+    else:
+        T = 2
+        for cand in (32, 16, 8, 4):
+            if cand <= a.frames and t2 * cand / 2 * 1.15 <= a.cpu_budget:
+                T = cand
+                break
+    times = [t2] if T == 2 else [_cpu_pass(sd, a.arch, T, a.size, O, torch) for _ in range(max(1, steps))]
+    dt = sorted(times)[len(times) // 2]
+    out = {"value": T / dt, "unit": UNIT, "cores": cores, "kind": "port",
+           "sample": f"oracle forward (CPU restatement of video_depth.py:61-68) on a {T}-frame {a.size}x{a.size} {a.arch} window, "
+                     f"fp32 torch CPU on {cores} threads, {len(times)} timed pass(es), median {dt:.2f} s "
+                     f"(T=2 calibration pass {t2:.2f} s)",
+           "sample_frames": T, "same_frames_as_gpu_arm": T == a.frames, "seconds_per_pass": dt}
+    c1 = None
+    if with_config1:
+        sd1 = refload.seeded_state_dict("vits", 0)
+        t = _cpu_pass(sd1, "vits", 32, 518, O, torch)
+        c1 = {"workload": "BASELINE configs[0]: vits random-init, 1x32x3x518x518 fp32 forward on the host cores (oracle port)",
+              "seconds_per_window": t, "frames_per_s": 32 / t, "cores": cores, "passes": 1}
+    return out, dt, c1
 
 
-def torch_eager_gpu_arm(a, steps=3, warmup=2):
+def torch_eager_gpu_arm(a, steps=2, warmup=1):
     """The oracle's op sequence (what the reference executes: F.linear / naive softmax attention / conv2d /
-    interpolate ...) as eager PyTorch on the same B200, full window, fp32 and autocast(bf16)."""
+    interpolate ...) as eager PyTorch on the same B200, full window: fp32, autocast bf16 / fp16 (the reference's
+    default, video_depth.py:108) and autocast fp16 with F.scaled_dot_product_attention in place of the naive
+    attention of dinov2_layers/attention.py:53-59 (mathematically identical; the fair bar)."""
     import torch
+    import torch.nn.functional as F
 
     from oracle import refload
     from oracle import vda_oracle as O
@@ -95,24 +159,52 @@ def torch_eager_gpu_arm(a, steps=3, warmup=2):
     torch.set_grad_enabled(False)
     sd = {k: v.cuda() for k, v in refload.seeded_state_dict(a.arch, 0).items()}
     x = torch.randn(1, a.frames, 3, a.size, a.size, generator=torch.Generator().manual_seed(0)).cuda()
+    heads = O.ARCH[a.arch]["heads"]
+
+    def vit_block_sdpa(sd_, pre, t, heads_):
+        B, N, C = t.shape
+        h = F.layer_norm(t, (C,), sd_[pre + "norm1.weight"], sd_[pre + "norm1.bias"], 1e-6)
+        qkv = F.linear(h, sd_[pre + "attn.qkv.weight"], sd_[pre + "attn.qkv.bias"]).reshape(B, N, 3, heads_, C // heads_)
+        q, k, v = qkv.permute(2, 0, 3, 1, 4)
+        o = F.scaled_dot_product_attention(q, k, v).transpose(1, 2).reshape(B, N, C)
+        t = t + sd_[pre + "ls1.gamma"] * F.linear(o, sd_[pre + "attn.proj.weight"], sd_[pre + "attn.proj.bias"])
+        h = F.layer_norm(t, (C,), sd_[pre + "norm2.weight"], sd_[pre + "norm2.bias"], 1e-6)
+        h = F.linear(F.gelu(F.linear(h, sd_[pre + "mlp.fc1.weight"], sd_[pre + "mlp.fc1.bias"])), sd_[pre + "mlp.fc2.weight"],
+                     sd_[pre + "mlp.fc2.bias"])
+        return t + sd_[pre + "ls2.gamma"] * h
+
     out = {}
-    for name, ctx in (("fp32", torch.autocast("cuda", enabled=False)),
-                      ("autocast_bf16", torch.autocast("cuda", dtype=torch.bfloat16)),
-                      ("autocast_fp16", torch.autocast("cuda", dtype=torch.float16))):
-        with ctx:
-            for _ in range(warmup):
-                O.forward(sd, x, a.arch)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            torch.cuda.synchronize()
-            e0.record()
-            for _ in range(steps):
-                O.forward(sd, x, a.arch)
-            e1.record()
-            torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / steps
-        out[name] = {"frames_per_s": a.frames / ms * 1e3, "ms_per_window": ms}
-    out["note"] = (f"oracle forward (eager torch {torch.__version__}, naive attention as attention.py:53-59, TF32 off), "
-                   f"{a.frames}-frame {a.size}x{a.size} {a.arch} window, {steps} timed passes")
+    naive_block = O.vit_block
+    cases = (("fp32", torch.autocast("cuda", enabled=False), False),
+             ("autocast_bf16", torch.autocast("cuda", dtype=torch.bfloat16), False),
+             ("autocast_fp16", torch.autocast("cuda", dtype=torch.float16), False),
+             ("autocast_fp16_sdpa", torch.autocast("cuda", dtype=torch.float16), True))
+    ref_out = None
+    for name, ctx, sdpa in cases:
+        O.vit_block = vit_block_sdpa if sdpa else naive_block
+        try:
+            with ctx:
+                for _ in range(warmup):
+                    y = O.forward(sd, x, a.arch)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                torch.cuda.synchronize()
+                e0.record()
+                for _ in range(steps):
+                    y = O.forward(sd, x, a.arch)
+                e1.record()
+                torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / steps
+            out[name] = {"frames_per_s": a.frames / ms * 1e3, "ms_per_window": ms}
+            if name == "fp32":
+                ref_out = y.float()
+            elif ref_out is not None:
+                m = ref_out > 1e-6
+                out[name]["absrel_vs_eager_fp32"] = float(((y.float() - ref_out).abs()[m] / ref_out[m]).mean())
+        finally:
+            O.vit_block = naive_block
+    out["note"] = (f"oracle forward (eager torch {torch.__version__}, TF32 off), {a.frames}-frame {a.size}x{a.size} {a.arch} "
+                   f"window, {steps} timed passes after {warmup} warm-up; *_sdpa swaps the naive attention for "
+                   f"F.scaled_dot_product_attention")
     return out
 
 
@@ -120,13 +212,14 @@ def run_reference(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    steps, warmup = max(1, min(a.steps, 3)), 1 if a.warmup > 0 else 0
-    cb, dt = cpu_arm(a, steps, warmup)
+    steps = max(1, min(a.steps, 2))
+    cb, dt, c1 = cpu_arm(a, steps, with_config1=True)
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": a.gpus,
-            "steps": steps, "warmup": warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+            "steps": steps, "warmup": 2, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_of(a),
             "cpu_baseline": cb, "gpu_launches": 0,
-            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "extra": {"cpu_config1_vits_fp32": c1}}
     print(json.dumps(line), flush=True)
 
 
@@ -177,11 +270,22 @@ def peaks():
         return 1400.0, 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def gemm_source_digest():
+    """Digest of the sources the GEMM kernel is compiled from; an ncu capture is only quoted while it matches."""
+    h = hashlib.sha256()
+    for f in ("gemm.cu", "gemm_epilogue.cuh", "gemm_params.h", "common.cuh"):
+        h.update(open(os.path.join(ROOT, "vda_b200", "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
+
+
 def ncu_traffic():
     """DRAM bytes (read + write) of the largest plain-GEMM launch (vitl fc1) from the committed
-    `ncu --set full` capture under profiles/ -- a profiler artefact, not measured in this run."""
+    `ncu --set full` capture under profiles/ -- a profiler artefact, not measured in this run; dropped (None) when
+    the capture was taken from other GEMM sources than the ones in the tree."""
     try:
         d = json.load(open(os.path.join(ROOT, "profiles", NCU_FC1)))
+        if d.get("gemm_source_digest") != gemm_source_digest():
+            return None, None, "capture is stale (GEMM sources changed since); not quoted"
 
         def mb(k):
             v = d[k]
@@ -192,12 +296,88 @@ def ncu_traffic():
             return float(num) * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[unit]
 
         alg = sum(d["algorithmic_bytes"].values())
-        return mb("dram__bytes_read.sum") + mb("dram__bytes_write.sum"), alg
-    except Exception:
-        return None, None
+        return mb("dram__bytes_read.sum") + mb("dram__bytes_write.sum"), alg, f"profiles/{NCU_FC1}"
+    except Exception as exc:
+        return None, None, f"no capture ({type(exc).__name__})"
+
+
+def _guard(fn):
+    """Extras must never take the headline line down with them; a failure is reported in place."""
+    try:
+        return fn()
+    except Exception as exc:  # noqa: BLE001
+        import traceback
+
+        return {"error": f"{type(exc).__name__}: {exc}", "trace": traceback.format_exc()[-800:]}
+
+
+def video_extra(model, frames, world, rank, dist, torch, dev, mode, reps=1):
+    """Whole-video throughput through infer_video_depth (uint8 host frames in, float32 host maps out); under
+    torchrun the windows are dealt round-robin over the ranks (vda_b200.parallel).  Timed wall-clock between two
+    barriers, max over ranks."""
+    from vda_b200 import parallel
+    from vda_b200.video_depth import window_frame_indices
+
+    if mode == "sharded":
+        parallel.set_result_sharded()
+    else:
+        parallel.set_result_rank(0 if world > 1 else None)
+    best, timing, depth = None, None, None
+    for rep in range(reps + 1):            # first call: pinned rings, graphs, NCCL buffers
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        depth, _ = model.infer_video_depth(frames, 24, input_size=518, device="cuda")
+        torch.cuda.synchronize()
+        dt_local = time.perf_counter() - t0
+        tl = dict(model.last_timing)
+        if world > 1:
+            t = torch.tensor([dt_local, dt_local - tl["seconds_to_last_forward"]], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt, tail = float(t[0]), float(t[1])
+        else:
+            dt, tail = dt_local, dt_local - tl["seconds_to_last_forward"]
+        if rep > 0 and (best is None or dt < best):
+            best, timing = dt, dict(tl, seconds_after_last_forward=tail)
+    parallel.set_result_rank(None)
+    n = len(frames)
+    n_win = len(window_frame_indices(n))
+    out = {"video_frames_per_s": n / best, "window_frames_per_s": 32 * n_win / best, "seconds": best, "frames": n,
+           "windows": n_win, "rounds": timing["rounds"], "n_gpus": world,
+           "result": {"sharded": "each rank keeps the frames of its own windows", "rank0": "rank 0 receives every frame"}[
+               "sharded" if mode == "sharded" else "rank0"] if world > 1 else "single process",
+           "seconds_after_last_forward_max_over_ranks": timing["seconds_after_last_forward"],
+           "share_after_last_forward": timing["seconds_after_last_forward"] / best,
+           "h2d_bytes": int(frames[0].nbytes) * 32 * timing["rounds"], "d2h_bytes": int(n) * frames.shape[1] * frames.shape[2] * 4}
+    if rank == 0 and depth is not None and mode != "sharded":
+        out["depth_min_max"] = [float(depth.min()), float(depth.max())]
+    return out
+
+
+def stream_extra(arch, torch, n_frames=150, size=518):
+    """Config 5: per-frame wall time of infer_video_depth_one (uint8 frame in, float32 depth on the host)."""
+    import numpy as np
+
+    from vda_b200.video_depth import MODEL_CONFIGS, randomize_zero_init_
+    from video_depth_anything.video_depth_stream import VideoDepthAnything as Stream
+
+    torch.manual_seed(0)
+    model = randomize_zero_init_(Stream(**MODEL_CONFIGS[arch])).cuda().eval()
+    frames = synth_video(n_frames, size, size, seed=1)
+    lat = []
+    for i in range(n_frames):
+        t0 = time.perf_counter()
+        d = model.infer_video_depth_one(frames[i], input_size=518, device="cuda")
+        lat.append((time.perf_counter() - t0) * 1e3)
+    steady = np.array(lat[45:])           # past the cache's steady state (42-entry list full)
+    return {"p50_ms": float(np.percentile(steady, 50)), "p99_ms": float(np.percentile(steady, 99)),
+            "mean_ms": float(steady.mean()), "frames": n_frames, "timed_frames": len(steady), "frame": f"{size}x{size}",
+            "arch": arch, "depth_min_max": [float(d.min()), float(d.max())]}
 
 
 def run_ours(a):
+    import numpy as np
     import torch
     import torch.distributed as dist
 
@@ -256,6 +436,18 @@ def run_ours(a):
     depth_stats = [float(d_last.min()), float(d_last.mean()), float(d_last.max())]
     clk = clocks.stop() if clocks else None
 
+    # ---- window latency: individually timed forwards (one in flight at a time), median
+    lat = []
+    for _ in range(max(20, a.steps)):
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record()
+        eng.forward(x_dev[0])
+        s1.record()
+        s1.synchronize()
+        lat.append(s0.elapsed_time(s1))
+    lat.sort()
+    p50 = max_over_ranks(lat[len(lat) // 2])
+
     # ---- the same K steps launched eagerly with CUDA events around every tensor-core launch
     # (events cannot be recorded inside a graph replay): per-kernel durations for the roofline
     L.PROFILE = []
@@ -285,6 +477,17 @@ def run_ours(a):
     ms_e2e = max_over_ranks(max(e0.elapsed_time(e1), 0.0))
     ms_e2e_wall = (time.perf_counter() - t0) * 1e3
 
+    # ---- extras: the other BASELINE configs (all ranks take part in the sharded video)
+    extra = {}
+    if not a.no_extras and not fp32 and a.arch == "vitl":
+        frames = synth_video(a.video_frames, 518, 518, seed=0)     # every rank holds the same clip (SPMD)
+        extra["video_1024f_vitl" if a.video_frames == 1024 else f"video_{a.video_frames}f_vitl"] = _guard(
+            lambda: video_extra(model, frames, world, rank, dist, torch, dev, "rank0"))
+        if world > 1:
+            extra["video_1024f_vitl_sharded_result"] = _guard(
+                lambda: video_extra(model, frames, world, rank, dist, torch, dev, "sharded"))
+        del frames
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -301,12 +504,14 @@ def run_ours(a):
     n_g, f_g, t_g = kinds.get("gemm", [1, 0.0, 1e-9])
     achieved = f_g / (t_g * 1e-3) / 1e12
     total_frames = T * a.steps * world
+    traffic, traffic_alg, traffic_src = ncu_traffic()
     line = {
         "metric": METRIC, "value": total_frames / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16" if not fp32 else "bf16x3 (fp32-accurate)", "data": "synthetic",
         "config": config_of(a),
-        "p50_window_latency_ms": ms / a.steps, "ms_per_step_eager_instrumented": ms_eager / a.steps,
+        "p50_window_latency_ms": p50, "window_latency_ms_min_max": [lat[0], lat[-1]], "window_latency_samples": len(lat),
+        "ms_per_step_eager_instrumented": ms_eager / a.steps,
         "e2e": {"value": total_frames / (ms_e2e * 1e-3), "unit": UNIT,
                 "h2d_bytes_per_step": x_host.numel() * 4, "d2h_bytes_per_step": T * H * W * 4,
                 "ms_per_step": ms_e2e / a.steps, "wall_ms_per_step": ms_e2e_wall / a.steps,
@@ -315,9 +520,9 @@ def run_ours(a):
         "clocks": clk,
         "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (plain GEMM launches: encoder/motion Linears, 1x1 convs)",
                      "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s", "frac": achieved / tf_peak,
-                     "traffic": ncu_traffic()[0], "traffic_algorithmic_bytes": ncu_traffic()[1],
-                     "traffic_note": "DRAM read+write bytes of one fc1 launch (M=43840,N=4096,K=1024), ncu --set full, "
-                                     f"profiles/{NCU_FC1}",
+                     "traffic": traffic, "traffic_algorithmic_bytes": traffic_alg,
+                     "traffic_note": "DRAM read+write bytes of one fc1 launch (M=43840,N=4096,K=1024), ncu --set full: "
+                                     + traffic_src,
                      "peak_source": peak_src, "launches": n_g,
                      "flops_per_launch": f_g / n_g, "ms_per_launch": t_g / n_g},
         "breakdown_ms_per_step": {k: v[2] / a.steps for k, v in kinds.items()},
@@ -326,12 +531,27 @@ def run_ours(a):
         "hbm_kernels": {k: {"ms_per_step": v[2] / a.steps, "GBps": v[1] / (v[2] * 1e-3) / 1e9,
                             "frac_of_hbm_peak": v[1] / (v[2] * 1e-3) / 1e9 / hbm_peak} for k, v in hbm.items() if v[2] > 0},
     }
+    if world == 1 and not a.no_extras and not fp32 and a.arch == "vitl":
+        def vitb_metric():
+            torch.manual_seed(0)
+            mb = randomize_zero_init_(VideoDepthAnything(**MODEL_CONFIGS["vitb"], metric=True)).to(dev).eval()
+            fr = synth_video(512, 720, 1280, seed=2)
+            return video_extra(mb, fr, 1, 0, dist, torch, dev, "rank0")
+
+        extra["video_512f_vitb_metric_720p"] = _guard(vitb_metric)
+        extra["stream_vits_518"] = _guard(lambda: stream_extra("vits", torch))
+        extra["stream_vitl_518"] = _guard(lambda: stream_extra("vitl", torch))
     if world == 1 and not a.no_cpu_baseline:
-        line["cpu_baseline"], _ = cpu_arm(a, 1, 1)
-    if world == 1 and a.torch_eager_gpu:
+        cb, _, c1 = cpu_arm(a, 1, with_config1=not a.no_extras)
+        line["cpu_baseline"] = cb
+        if c1:
+            extra["cpu_config1_vits_fp32"] = c1
+    if world == 1 and not a.no_extras:
         del model
         torch.cuda.empty_cache()
-        line["torch_eager_same_gpu"] = torch_eager_gpu_arm(a)
+        extra["torch_eager_same_gpu"] = _guard(lambda: torch_eager_gpu_arm(a))
+    if extra:
+        line["extra"] = extra
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -86,3 +86,19 @@ def test_preprocess_matches_oracle_bitwise():
         dst = np.empty((3, 56, 70), np.float32)
         _one(f, 56, 70, dst)
         np.testing.assert_array_equal(dst, O.preprocess_frame(f, 56, 70))
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="reference tree only exists in the build container")
+@pytest.mark.parametrize("script", ["run.py", "run_streaming.py"])
+def test_reference_entry_points_import_against_the_repo(script):
+    """The reference's own run.py / run_streaming.py, unmodified, resolve every import (`video_depth_anything.*`,
+    `utils.dc_utils`) against this repo when it is first on PYTHONPATH: `--help` runs their module level code up to
+    argparse (run.py:15-40, run_streaming.py:15-38)."""
+    import subprocess
+    import sys
+
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    r = subprocess.run([sys.executable, os.path.join("/root/reference", script), "--help"], cwd=ROOT, env=env,
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "--encoder" in r.stdout and "--input_size" in r.stdout

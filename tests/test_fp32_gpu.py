@@ -193,7 +193,7 @@ def test_fp32_forward_vs_reference_golden(name):
     check_close(got, want, what=name)
 
 
-@pytest.mark.parametrize("arch,T,H,W", [("vits", 32, 518, 518), ("vitl", 8, 518, 518), ("vitb", 4, 518, 924)])
+@pytest.mark.parametrize("arch,T,H,W", [("vits", 32, 518, 518), ("vitl", 32, 518, 518), ("vitb", 4, 518, 924)])
 def test_fp32_full_size_window_vs_oracle_on_gpu(arch, T, H, W):
     model = build(arch)
     sd_gpu = {k: v.cuda() for k, v in refload.seeded_state_dict(arch, 0).items()}

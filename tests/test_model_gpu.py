@@ -62,12 +62,13 @@ def test_stagewise_vits_diagnostics():
     eng = model.engine()
     ws = eng._ws(("diag", T, H, W))
     with torch.no_grad():
-        taps = eng.encoder(x[0], ws)
+        eng._patch(x[0].contiguous(), ws)
+        taps = eng.encoder(T, H, W, ws)
         want = O.encoder_taps(sd_gpu, x[0], arch)
         for i, (g, w_) in enumerate(zip(taps, want)):
             err = (g.float().view_as(w_) - w_).abs().max().item() / w_.abs().max().item()
             print(f"tap{i}: rel max err {err:.2e}")
-            assert err < 5e-2
+            assert err < 2e-2      # measured on B200: 4.6e-3 .. 6.9e-3 (profiles/r01_parity_first.log); budget = 3x
         # head on the ORACLE's taps (rounded to bf16) isolates the head kernels
         taps_b = [w_.reshape(-1, w_.shape[-1]).bfloat16().contiguous() for w_ in want]
         depth = eng.head(taps_b, H // 14, W // 14, T, ws).cpu().numpy()
@@ -154,7 +155,9 @@ def test_forward_pipelined_matches_forward():
         got = model.forward_pipelined(iter(xs))
     assert len(got) == 5
     for g, w_ in zip(got, want):
-        assert g.is_pinned() and torch.equal(g, w_)
+        # same kernels on the same input; not bitwise: the tail split-K of large proj / fc2 launches adds its partial
+        # sums into the fp32 residual in an order that is not fixed (csrc/api.cu)
+        assert g.is_pinned() and torch.allclose(g, w_, rtol=1e-4, atol=1e-6)
 
 
 @pytest.mark.parametrize("n_frames", [1, 5, 22, 23, 33, 55])

@@ -176,17 +176,16 @@ class Engine:
         return self.ws[key]
 
     # ------------------------------------------------------------------ encoder
-    def encoder(self, x, ws):
-        """x f32 [T,3,H,W] -> 4 taps, each bf16 [T*gh*gw, D] (final-norm applied, cls dropped)."""
+    def encoder(self, T, H, W, ws):
+        """Patch rows of a [T,3,H,W] window (gathered by _patch) -> 4 taps, each bf16 [T*gh*gw, D] (final-norm
+        applied, cls dropped)."""
         w = self.w
-        T, _, H, W = x.shape
         gh, gw = H // PATCH, W // PATCH
         hw, D, heads = gh * gw, w.D, w.heads
         S, M = hw + 1, T * (hw + 1)
         spad = _pad(S, 8)
         sp, Wd = self.fp32, self.W
         a = ws.get("patch_a", (T * hw, 592 * Wd))
-        L.patch_im2col(x, a, T, H, W, 592, split=int(sp))
         patch = ws.get("patch_f32", (T * hw, D), torch.float32)
         L.gemm(a, w.w_patch, L.make_epilogue(bias=w.b_patch, out_f32=patch, ldo=D), K=None if sp else 588)
         tok = ws.get("tokens", (M, D), torch.float32)
@@ -355,9 +354,10 @@ class Engine:
         """x f32 [T,3,H,W] on this device -> depth f32 [T,H,W] (a workspace buffer: copy before reuse).
         With `stream_ctx` (T == 1) the temporal attention reads the streaming K/V cache instead.
 
-        The launch sequence of a window is fixed per input shape, so after one eager pass it is
-        captured into a CUDA graph and replayed (one graph launch instead of ~270 kernel launches);
-        `use_graph = False` or an active L.PROFILE (per-launch event timing) runs it eagerly."""
+        The only kernel that reads `x` is the patch gather; it is launched eagerly from wherever `x` lives (no
+        staging copy of the window).  Everything after it has a launch sequence that is fixed per input shape, so
+        after one eager pass it is captured into a CUDA graph and replayed (one graph launch instead of ~270 kernel
+        launches); `use_graph = False` or an active L.PROFILE (per-launch event timing) runs it eagerly."""
         assert x.dim() == 4 and x.shape[1] == 3 and x.dtype == torch.float32 and x.is_cuda
         T, _, H, W = x.shape
         if H % PATCH or W % PATCH:
@@ -367,59 +367,70 @@ class Engine:
         key = ("win", T, H, W)
         ws = self._ws(key)
         with torch.cuda.device(self.device):
-            if not self.use_graph or L.PROFILE is not None:
-                return self._run(x.contiguous(), ws, stream_ctx)
+            x = x.contiguous()
+            eager = not self.use_graph or L.PROFILE is not None
             if stream_ctx is not None:
                 # Streaming step: once the cache is full (Tk == 32, from the second frame on) the launch
                 # sequence is fixed -- the per-frame slot list lives in a device buffer that begin_frame()
                 # refreshes -- so it is captured once per cache and replayed (per-frame latency is
                 # launch-bound otherwise: ~300 launches for one frame of work).
-                if stream_ctx.Tk != 32:
-                    return self._run(x.contiguous(), ws, stream_ctx)
-                key = ("stream", T, H, W, stream_ctx.serial)
-                xin = ws.get("graph_in", (T, 3, H, W), torch.float32)
-                xin.copy_(x)
-                g = self.graphs.get(key)
-                if g is None:
-                    if key not in self._warm:          # first full-cache frame runs eagerly (allocates buffers)
-                        self._warm = {key}
-                        self.graphs = {k: v for k, v in self.graphs.items() if k[0] != "stream"}
-                        return self._run(xin, ws, stream_ctx)
-                    torch.cuda.current_stream().synchronize()
-                    graph = torch.cuda.CUDAGraph()
-                    with torch.cuda.graph(graph):
-                        out = self._run(xin, ws, stream_ctx)
-                    g = self.graphs[key] = (graph, out)
-                n0 = L.LAUNCHES
-                g[0].replay()
-                L.LAUNCHES = n0 + self.launches_per_run[("win", T, H, W)]
-                return g[1]
-            xin = ws.get("graph_in", (T, 3, H, W), torch.float32)
-            xin.copy_(x)
-            g = self.graphs.get(key)
+                if eager or stream_ctx.Tk != 32:
+                    return self._run(x, ws, stream_ctx)
+                gkey = ("stream", T, H, W, stream_ctx.serial)
+                if gkey not in self.graphs and gkey not in self._warm:
+                    # first full-cache frame runs eagerly (allocates buffers); graphs of earlier streams are dropped
+                    self._warm = {gkey}
+                    self.graphs = {k: v for k, v in self.graphs.items() if k[0] != "stream"}
+                    return self._run(x, ws, stream_ctx)
+            else:
+                if eager:
+                    return self._run(x, ws, None)
+                gkey = key
+                if gkey not in self.graphs:
+                    self._run(x, ws, None)               # eager pass: allocates the workspace, sets kernel attributes
+            n0 = L.LAUNCHES
+            prev = L.set_pdl(stream_ctx is not None)
+            try:
+                self._patch(x, ws)
+            finally:
+                L.set_pdl(prev)
+            g = self.graphs.get(gkey)
             if g is None:
-                out = self._run(xin, ws, None)           # eager pass: allocates the workspace, sets kernel attributes
                 torch.cuda.current_stream().synchronize()
                 graph = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(graph):
-                    out = self._run(xin, ws, None)
-                g = self.graphs[key] = (graph, out)
-            n0 = L.LAUNCHES
+                    out = self._after_patch(T, H, W, ws, stream_ctx)
+                g = self.graphs[gkey] = (graph, out)
             g[0].replay()
             L.LAUNCHES = n0 + self.launches_per_run[key]
             return g[1]
 
-    def _run(self, x, ws, stream_ctx):
+    def _patch(self, x, ws):
+        """The one consumer of the input window: 14x14 patch gather into the A operand of the patch-embed GEMM."""
         T, _, H, W = x.shape
-        n0 = L.LAUNCHES
+        hw = (H // PATCH) * (W // PATCH)
+        a = ws.get("patch_a", (T * hw, 592 * self.W))
+        L.patch_im2col(x, a, T, H, W, 592, split=int(self.fp32))
+
+    def _after_patch(self, T, H, W, ws, stream_ctx):
         # Programmatic dependent launch only for the latency-bound single-frame sequence of the streaming mode
         # (~300 launches of one tile each: -2 % per frame); on a full window it costs 2 % (csrc/api.cu).
         prev = L.set_pdl(stream_ctx is not None)
         try:
-            taps = self.encoder(x, ws)
-            out = self.head(taps, H // PATCH, W // PATCH, T, ws, stream_ctx=stream_ctx)
+            taps = self.encoder(T, H, W, ws)
+            return self.head(taps, H // PATCH, W // PATCH, T, ws, stream_ctx=stream_ctx)
         finally:
             L.set_pdl(prev)
+
+    def _run(self, x, ws, stream_ctx):
+        T, _, H, W = x.shape
+        n0 = L.LAUNCHES
+        prev = L.set_pdl(stream_ctx is not None)
+        try:
+            self._patch(x, ws)
+        finally:
+            L.set_pdl(prev)
+        out = self._after_patch(T, H, W, ws, stream_ctx)
         self.launches_per_run[("win", T, H, W)] = L.LAUNCHES - n0
         return out
 

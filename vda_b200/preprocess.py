@@ -58,13 +58,14 @@ def preprocess_frames(frames, indices, nh, nw, device):
 
 
 class FrameFeeder:
-    """Incremental host -> device feed of source frames for the window loop (video_depth.py:100-107).
+    """Host -> device feed of the window loop (video_depth.py:92-107): fills the network input of one window.
 
-    Every source frame is uploaded and pre-processed exactly once, just before the first window that
-    needs it: uint8 frames are gathered into one of two pinned staging slots (allocated once per frame
-    size and reused: pinning ~1 GB per call costs more than a whole second on the GPU box), copied to the
-    device on the caller's stream and converted by `vda_preprocess_u8` into rows of the resident network
-    input table.  The host runs at most two windows ahead of the GPU (slot reuse waits on the copy)."""
+    The window's source frames are gathered as uint8 into one of two pinned staging slots (allocated once per
+    frame size and reused: pinning ~1 GB per call costs more than a whole second on the GPU box), copied to the
+    device on a side stream while the previous window still computes, and converted by `vda_preprocess_u8` straight
+    into the window's input tensor.  When the previous window of the video ran on this GPU too, its key-frame slots
+    ARE this window's first ten slots (video_depth.py:96-99: `pre_input[:, KEYFRAMES]`), so only the 22 new frames
+    are uploaded.  Nothing of size O(video) stays on the GPU."""
 
     SLOT_FRAMES = 32
 
@@ -74,33 +75,50 @@ class FrameFeeder:
         self.nh, self.nw = nh, nw
         self.pinned = [torch.empty(self.SLOT_FRAMES, h0, w0, 3, dtype=torch.uint8, pin_memory=True) for _ in range(2)]
         self.staged = [torch.empty(self.SLOT_FRAMES, h0, w0, 3, dtype=torch.uint8, device=device) for _ in range(2)]
-        self.done = [None, None]
+        self.copied = [None, None]     # H2D of the slot has finished: the pinned half may be rewritten
+        self.consumed = [None, None]   # the pre-process kernel has read the device half
         self.turn = 0
+        self.side = torch.cuda.Stream(device)
+        self.key_index = None
 
-    def feed(self, frames, indices, table, rows):
-        """Upload frames[indices] and write their network inputs into table[rows[0] : rows[0]+len(indices)]
-        (rows are consecutive).  Asynchronous on the current stream."""
+    def fill(self, frames, indices, x, key_slots=None):
+        """x f32 [len(indices),3,nh,nw] <- network inputs of frames[indices].  key_slots: if given, x still holds the
+        previous window's input and x[key_slots] become slots 0..len(key_slots)-1 (the caller guarantees that these
+        are the same source frames); only the remaining slots are uploaded.  Asynchronous on the current stream."""
         from . import lib as L
 
-        pos = 0
-        while pos < len(indices):
-            part = indices[pos:pos + self.SLOT_FRAMES]
-            t = self.turn
-            self.turn ^= 1
-            if self.done[t] is not None:
-                self.done[t].synchronize()
-            m = len(part)
-            dst = self.pinned[t].numpy()
-            if part[-1] - part[0] == m - 1:               # consecutive frames: one block copy
-                dst[:m] = frames[part[0]:part[0] + m]
-            else:
-                np.take(frames, part, axis=0, out=dst[:m])
+        first = 0
+        if key_slots is not None:
+            if self.key_index is None or self.key_index.numel() != len(key_slots):
+                self.key_index = torch.tensor(list(key_slots), dtype=torch.long, device=self.device)
+            first = len(key_slots)
+            x[:first].copy_(x.index_select(0, self.key_index))
+        part = list(indices[first:])
+        m = len(part)
+        if m == 0:
+            return
+        t = self.turn
+        self.turn ^= 1
+        if self.copied[t] is not None:
+            self.copied[t].synchronize()
+        dst = self.pinned[t].numpy()
+        if part[-1] - part[0] == m - 1 and all(b - a == 1 for a, b in zip(part, part[1:])):
+            dst[:m] = frames[part[0]:part[0] + m]          # consecutive frames: one block copy
+        else:
+            np.take(frames, part, axis=0, out=dst[:m])
+        main = torch.cuda.current_stream()
+        with torch.cuda.stream(self.side):
+            if self.consumed[t] is not None:
+                self.side.wait_event(self.consumed[t])
             self.staged[t][:m].copy_(self.pinned[t][:m], non_blocking=True)
             ev = torch.cuda.Event()
             ev.record()
-            self.done[t] = ev
-            L.preprocess_u8(self.staged[t][:m], table[rows[0] + pos:rows[0] + pos + m], self.nh, self.nw)
-            pos += m
+        self.copied[t] = ev
+        main.wait_event(ev)
+        L.preprocess_u8(self.staged[t][:m], x[first:first + m], self.nh, self.nw)
+        done = torch.cuda.Event()
+        done.record()
+        self.consumed[t] = done
 
 
 def preprocess_frames_cv2(frames, indices, nh, nw, device):

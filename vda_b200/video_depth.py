@@ -8,7 +8,7 @@ What differs is underneath: every window is a fixed launch sequence of libvda_b2
 GPU; the sequential scale/shift alignment and the cross-fade run as GPU kernels without host
 synchronisation; one device->host copy returns the result.
 """
-import threading
+import time
 from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
@@ -52,15 +52,6 @@ def randomize_zero_init_(model, seed=0):
         last.weight.abs_()
         last.bias.fill_(0.1)
     return model
-
-
-def _prefault(arr, chunk=16 << 20):
-    """Touch one element per 4 KB page of a freshly allocated array (chunked, so other threads get the GIL)."""
-    flat = arr.reshape(-1)
-    stride = max(1, 4096 // arr.itemsize)
-    per = chunk // arr.itemsize
-    for lo in range(0, flat.size, per):
-        flat[lo:lo + per:stride] = 0
 
 
 def window_frame_indices(n_frames):
@@ -205,161 +196,161 @@ class VideoDepthAnything(nn.Module):
         (align_corners=True) to that size before they leave the GPU -- the kwargs of the fork's engine copy,
         external_engine/video_depth_anything/video_depth.py:81-90, :181-203.
 
-        One pass, pipelined per window: upload + pre-process the window's new frames, forward, resize to the
-        source size, alignment scan step, then the frames that scan step made final go device -> pinned ring
-        -> the result array on a side stream while the next window computes."""
+        One pass, pipelined per window: upload + pre-process the window's frames, forward, resize to the source
+        size, one step of the alignment scan (vda_b200.parallel.WindowScan), then the frames that step made final go
+        device -> pinned ring -> the result array on a side stream while the next window computes.
+
+        Under torch.distributed (one process per GPU) the windows are dealt round-robin over the ranks and the result
+        goes where vda_b200.parallel.set_result_rank / set_result_sharded say: every rank (default), one rank (the
+        others return (None, fps)), or each rank only the frames of its own windows (the rest of the returned array
+        is uninitialised; `self.last_owned_frames` lists the [lo, hi) ranges that are valid)."""
         frames = np.asarray(frames)
         n, h0, w0 = frames.shape[:3]
         up = (int(original_height), int(original_width)) if original_width is not None and original_height is not None else None
-        if parallel.active() and not parallel.wants_result():
-            # vda_b200.parallel.set_result_rank: this rank only computes its windows and joins the exchange
-            self.infer_video_depth_device(frames, input_size=input_size, device=device, fp32=fp32)
-            return None, target_fps
-        out = np.empty((n,) + (up or (h0, w0)), np.float32)
-        if parallel.active():
-            # the result array is touched page by page on a helper thread while the GPUs work: first-touch
-            # faults of a fresh GB-sized array would otherwise serialise with the download at the end
-            toucher = threading.Thread(target=_prefault, args=(out,), daemon=True)
-            toucher.start()
-            depth = self.infer_video_depth_device(frames, input_size=input_size, device=device, fp32=fp32)
-            toucher.join()
-            dl = self._downloader(depth.device, h0, w0, up)
-            dl.begin(out)
-            for lo in range(0, n, dl.FRAMES):
-                dl.push(depth[lo:min(lo + dl.FRAMES, n)], lo)
-            dl.finish()
-            return out, target_fps
+        dev = self._device(device)
+        world, _ = parallel.world_rank()
+        want = parallel.wants_result()
+        out = np.empty((n,) + (up or (h0, w0)), np.float32) if want else None
         dl = None
+        owned = []
+        if want:
+            # slots for two rounds of final frames: one round being drained on the host while the next is enqueued
+            per_round = world if (world > 1 and parallel.result_mode() != "sharded") else 1
+            dl = self._downloader(dev, h0, w0, up, 2 * per_round)
+            dl.begin(out)
 
-        def on_window(scan, final_lo, final_hi):
-            nonlocal dl
-            if dl is None:
-                dl = self._downloader(scan.out.device, h0, w0, up)
-                dl.begin(out)
-            hi = min(final_hi, n)
-            if hi > final_lo:
-                dl.push(scan.out[final_lo:hi], final_lo)
+        def sink(lo, maps):
+            m = min(maps.shape[0], n - lo)
+            if m > 0:
+                dl.push(maps[:m], lo)
+                owned.append((lo, lo + m))
 
-        self._run_video(frames, input_size, device, fp32, None, on_window)
-        dl.finish()
+        self._run_video(frames, input_size, dev, fp32, sink if want else None, dl.next_round if want else None)
+        if want:
+            dl.finish()
+        self.last_owned_frames = owned
         return out, target_fps
 
     @torch.no_grad()
-    def infer_video_depth_device(self, frames, input_size=518, device="cuda", windows=None, return_raw=False, fp32=False):
-        """Same as infer_video_depth but leaves the aligned depth [N,H0,W0] on the GPU.
-        `windows` restricts the forward passes to a subset (multi-GPU sharding, vda_b200.parallel) and
-        return_raw returns their un-aligned maps [len(windows)*32, H0, W0]."""
+    def infer_video_depth_device(self, frames, input_size=518, device="cuda", fp32=False):
+        """Same as infer_video_depth but leaves the aligned depth [N,H0,W0] on the GPU (None on ranks that do not
+        receive the result)."""
         frames = np.asarray(frames)
-        if windows is None and not return_raw and parallel.active():
-            # one process per GPU (torchrun): shard the windows, all-gather the per-window depth over NCCL
-            n = len(frames)
-            return parallel.distributed_infer(
-                n, window_frame_indices,
-                lambda ids: self.infer_video_depth_device(frames, input_size, device, windows=ids, return_raw=True,
-                                                          fp32=fp32),
-                lambda raw: align_windows_device(raw, self.metric))
-        res = self._run_video(frames, input_size, device, fp32, windows, None, keep_raw=return_raw)
-        return res if return_raw else res[:len(frames)]
+        n, h0, w0 = frames.shape[:3]
+        dev = self._device(device)
+        want = parallel.wants_result()
+        out = torch.empty(n, h0, w0, dtype=torch.float32, device=dev) if want else None
 
-    def _run_video(self, frames, input_size, device, fp32, windows, on_window, keep_raw=False):
-        """The window loop.  keep_raw: returns raw [len(windows)*32, H0, W0]; otherwise runs the alignment scan
-        as it goes (all windows must be present, in order), calls on_window(scan, lo, hi) with the range of
-        aligned frames that became final, and returns the aligned maps (device)."""
+        def sink(lo, maps):
+            m = min(maps.shape[0], n - lo)
+            if m > 0:
+                out[lo:lo + m].copy_(maps[:m])
+
+        self._run_video(frames, input_size, dev, fp32, sink if want else None, None)
+        return out
+
+    def _device(self, device):
         dev = torch.device(device if device != "cuda" else f"cuda:{torch.cuda.current_device()}")
         if self.pretrained.cls_token.device != dev:
             raise RuntimeError(f"model is on {self.pretrained.cls_token.device}, call .to('{dev}') first")
+        return dev
+
+    def _run_video(self, frames, input_size, dev, fp32, sink, end_of_round):
+        """The window loop (video_depth.py:92-160).  Round j: this rank's window k = j*world + rank is fed,
+        forwarded, resized to the source size and pushed into the alignment scan together with the other ranks'
+        windows of the round; sink(first_frame, maps) receives the frames that became final; end_of_round() is
+        called after a round's GPU work has been enqueued (the downloader drains the PREVIOUS round there, so the
+        host-side copies of round j-1 run while the GPU computes round j)."""
         n, h0, w0 = frames.shape[:3]
         nh, nw = net_input_size(h0, w0, input_size)
         wins = window_frame_indices(n)
-        mine = list(range(len(wins))) if windows is None else list(windows)
-        assert keep_raw or mine == list(range(len(wins))), "the alignment scan needs every window, in order"
-        needed = sorted({i for k in mine for i in wins[k]})
-        row = {f: j for j, f in enumerate(needed)}
+        world, rank = parallel.world_rank()
         eng = self.engine(fp32)
+        timing = self.last_timing = {"windows": len(wins), "rounds": parallel.n_rounds(len(wins), world), "world": world}
         with torch.cuda.device(dev):
+            main = torch.cuda.current_stream()
+            main.synchronize()
+            t0 = time.perf_counter()
+            e_begin, e_last = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e_begin.record()
             feeder = getattr(self, "_feeder", None)
             if feeder is None or feeder.key != (h0, w0, nh, nw, str(dev)):
                 feeder = self._feeder = FrameFeeder(h0, w0, nh, nw, dev)
-            table = torch.empty(len(needed), 3, nh, nw, dtype=torch.float32, device=dev)   # network input per source frame
-            idx_all = torch.tensor([[row[f] for f in wins[k]] for k in mine], dtype=torch.long).reshape(len(mine), INFER_LEN)
-            idx_all = idx_all.to(dev, non_blocking=True)
-            fed = 0                                       # rows [0, fed) of `table` are resident
-            if keep_raw:
-                raw = torch.empty(len(mine) * INFER_LEN, h0, w0, dtype=torch.float32, device=dev)
-            else:
-                scan = AlignScan(len(wins), h0, w0, dev, self.metric)
-                slots = [torch.empty(INFER_LEN, h0, w0, dtype=torch.float32, device=dev) for _ in range(2)]
-            for j, k in enumerate(mine):
-                top = max(row[f] for f in wins[k]) + 1
-                if top > fed:                             # frames are needed in increasing order of index
-                    feeder.feed(frames, needed[fed:top], table, (fed, top))
-                    fed = top
-                d = eng.forward(table.index_select(0, idx_all[j]))
-                dst = raw[j * INFER_LEN:(j + 1) * INFER_LEN] if keep_raw else slots[j & 1]
-                L.bilinear_f32(d, dst, INFER_LEN, nh, nw, h0, w0)
-                if not keep_raw:
-                    lo, hi = scan.push(dst)
-                    if on_window is not None:
-                        on_window(scan, lo, hi)
-        return raw if keep_raw else scan.out
+            key = ("video", h0, w0, nh, nw, str(dev))
+            bufs = getattr(self, "_video_bufs", None)
+            if bufs is None or bufs[0] != key:
+                bufs = self._video_bufs = (key, torch.empty(INFER_LEN, 3, nh, nw, dtype=torch.float32, device=dev),
+                                           [torch.empty(INFER_LEN, h0, w0, dtype=torch.float32, device=dev) for _ in range(2)])
+            x, raws = bufs[1], bufs[2]
+            scan = parallel.WindowScan(len(wins), h0, w0, GpuAlignOps(dev), self.metric)
+            prev_k = None
+            for j in range(timing["rounds"]):
+                k = j * world + rank
+                raw = None
+                if k < len(wins):
+                    feeder.fill(frames, wins[k], x, KEYFRAMES if prev_k is not None and prev_k == k - 1 else None)
+                    prev_k = k
+                    d = eng.forward(x)
+                    raw = raws[j & 1]
+                    L.bilinear_f32(d, raw, INFER_LEN, nh, nw, h0, w0)
+                    e_last = torch.cuda.Event(enable_timing=True)
+                    e_last.record()
+                for lo, maps in scan.push(j, raw):
+                    if sink is not None:
+                        sink(lo, maps)
+                if end_of_round is not None:
+                    end_of_round()
+            main.synchronize()
+            timing["seconds_device"] = time.perf_counter() - t0
+            timing["seconds_to_last_forward"] = e_begin.elapsed_time(e_last) * 1e-3
+        return timing
 
-    def _downloader(self, dev, h0, w0, up):
-        key = (str(dev), h0, w0, up)
+    def _downloader(self, dev, h0, w0, up, slots):
+        key = (str(dev), h0, w0, up, slots)
         dl = getattr(self, "_dl", None)
         if dl is None or dl.key != key:
-            dl = self._dl = HostDownloader(dev, h0, w0, up)
+            dl = self._dl = HostDownloader(dev, h0, w0, up, slots)
         return dl
 
 
-class AlignScan:
-    """Sequential scale/shift alignment + 8-frame cross-fade (video_depth.py:120-160) as an incremental
-    scan on the GPU: push() takes one window's raw maps [32, H0, W0] and extends the aligned sequence
-    `out` [32 + 22*(n_windows-1), H0, W0].  No host synchronisation."""
+class GpuAlignOps:
+    """The arithmetic of vda_b200.parallel.WindowScan on the CUDA kernels of csrc/align.cu."""
 
-    def __init__(self, n_windows, h0, w0, device, metric=False, out=None):
-        self.metric = bool(metric)
-        self.per = h0 * w0
-        total = INFER_LEN + (INFER_LEN - OVERLAP) * (n_windows - 1)
-        self.out = out if out is not None else torch.empty(total, h0, w0, dtype=torch.float32, device=device)
+    def __init__(self, device):
+        self.device = device
         self.sums = torch.zeros(5, dtype=torch.float64, device=device)
-        self.ss = torch.empty(2, dtype=torch.float32, device=device)
-        self.filled = 0
-        self.n_windows, self.k = n_windows, 0
-        self.ref = None
 
-    def push(self, raw):
-        """Returns (lo, hi): aligned frames [lo, hi) can no longer change (the last INTERP_LEN frames of
-        the sequence are cross-faded with the next window, except after the last one)."""
-        out, per = self.out, self.per
-        step, n_align = INFER_LEN - OVERLAP, OVERLAP - INTERP_LEN
-        last = self.k == self.n_windows - 1
-        if self.k == 0:
-            out[:INFER_LEN].copy_(raw)
-            self.ref = [out[KEYFRAMES[0]], out[KEYFRAMES[1]]]
-            self.filled = INFER_LEN
-            lo = 0
-        else:
-            filled = self.filled
-            self.sums.zero_()
-            for i in range(n_align):
-                L.lsq_accum(raw[i], self.ref[i], per, self.sums)
-            L.lsq_solve(self.sums, self.ss, self.metric)
-            L.affine_clamp_blend(out[filled - INTERP_LEN:filled], raw[n_align:OVERLAP], per, INTERP_LEN, self.ss)
-            L.affine_clamp(raw[OVERLAP:INFER_LEN], out[filled:filled + step], per * step, self.ss)
-            self.ref = [self.ref[0], out[filled + KEYFRAMES[1] - OVERLAP]]
-            lo = filled - INTERP_LEN
-            self.filled = filled + step
-        self.k += 1
-        return lo, (self.filled if last else self.filled - INTERP_LEN)
+    def empty(self, *shape):
+        return torch.empty(*shape, dtype=torch.float32, device=self.device)
+
+    def scale_shift_table(self, n):
+        t = torch.zeros(n, 2, dtype=torch.float32, device=self.device)
+        t[:, 0] = 1.0
+        return t
+
+    def scale_shift(self, pred, target, ss, metric):
+        """ss <- least-squares (scale, shift) of pred onto target (utils/util.py:40-62), FP64 sums; the solve leaves
+        the sums zeroed for the next window."""
+        L.lsq_accum(pred, target, pred.numel(), self.sums)
+        L.lsq_solve(self.sums, ss, metric, reset=True)
+
+    def affine_clamp(self, src, dst, ss):
+        L.affine_clamp(src, dst, src.numel(), ss)
+
+    def affine_clamp_blend(self, pre, post, ss):
+        L.affine_clamp_blend(pre, post, pre[0].numel(), pre.shape[0], ss)
 
 
-def align_windows_device(raw, metric=False, out=None):
-    """All windows at once: raw f32 [n_windows*32, H0, W0] -> f32 [32 + 22*(n_windows-1), H0, W0]."""
+def align_windows_device(raw, metric=False):
+    """All windows at once on one GPU: raw f32 [n_windows*32, H0, W0] -> f32 [32 + 22*(n_windows-1), H0, W0]."""
     n_win = raw.shape[0] // INFER_LEN
-    scan = AlignScan(n_win, raw.shape[1], raw.shape[2], raw.device, metric, out=out)
+    scan = parallel.WindowScan(n_win, raw.shape[1], raw.shape[2], GpuAlignOps(raw.device), metric, group=parallel.SOLO)
+    out = torch.empty(INFER_LEN + (INFER_LEN - OVERLAP) * (n_win - 1), raw.shape[1], raw.shape[2], dtype=torch.float32,
+                      device=raw.device)
     for k in range(n_win):
-        scan.push(raw[k * INFER_LEN:(k + 1) * INFER_LEN])
-    return scan.out
+        for lo, maps in scan.push(k, raw[k * INFER_LEN:(k + 1) * INFER_LEN]):
+            out[lo:lo + maps.shape[0]].copy_(maps)
+    return out
 
 
 _POOL = None
@@ -373,29 +364,29 @@ def _copy_pool():
 
 
 class HostDownloader:
-    """Device -> host path of the result (video_depth.py:113,162): chunks of <= 32 maps go through a
-    two-slot pinned ring on a side stream and are copied into the caller's (pageable) array while the GPU
-    works on the next window.  The ring is allocated once per frame size and reused across calls; the
-    optional bilinear upscale to the caller's plate size runs on the main stream before the copy."""
+    """Device -> host path of the result (video_depth.py:113,162): batches of <= 32 final maps go through a ring
+    of pinned slots on a side stream and are copied into the caller's (pageable) array one round later, while the
+    GPU works on the next window.  The ring is allocated once per frame size and reused across calls (pinning is
+    slow: ~1 s per GB on the GPU box); the optional bilinear upscale to the caller's plate size runs on the main
+    stream before the copy."""
 
     FRAMES = INFER_LEN
     THREADS = 4
 
-    def __init__(self, dev, h0, w0, up=None):
-        self.key = (str(dev), h0, w0, up)
+    def __init__(self, dev, h0, w0, up=None, slots=2):
+        self.key = (str(dev), h0, w0, up, slots)
         self.dev, self.h0, self.w0, self.up = dev, h0, w0, up
         oh, ow = up or (h0, w0)
-        self.ring = [torch.empty(self.FRAMES, oh, ow, dtype=torch.float32, pin_memory=True) for _ in range(2)]
-        self.upbuf = [torch.empty(self.FRAMES, oh, ow, dtype=torch.float32, device=dev) for _ in range(2)] if up else None
+        self.ring = [torch.empty(self.FRAMES, oh, ow, dtype=torch.float32, pin_memory=True) for _ in range(slots)]
+        self.upbuf = [torch.empty(self.FRAMES, oh, ow, dtype=torch.float32, device=dev) for _ in range(slots)] if up else None
         self.side = torch.cuda.Stream(dev)
-        self.pending = [None, None]
-        self.turn = 0
-        self.out = None
+        self.begin(None)
 
     def begin(self, out):
         self.out = out
-        self.pending = [None, None]
-        self.turn = 0
+        self.pending = [None] * len(self.ring)
+        self.turn = 0                         # pushes so far; push i uses slot i % len(ring)
+        self.prev_start = self.round_start = 0  # pushes [round_start, turn) belong to the round being enqueued
 
     def _drain(self, t):
         if self.pending[t] is not None:
@@ -412,8 +403,8 @@ class HostDownloader:
 
     def push(self, src, lo):
         """src: device f32 [m <= 32, h0, w0], final; becomes out[lo:lo+m]."""
-        t = self.turn
-        self.turn ^= 1
+        t = self.turn % len(self.ring)
+        self.turn += 1
         self._drain(t)
         m = src.shape[0]
         with torch.cuda.device(self.dev):
@@ -429,7 +420,14 @@ class HostDownloader:
                 done.record()
         self.pending[t] = (done, lo, m)
 
+    def next_round(self):
+        """Called when a round's GPU work has been enqueued: copies the PREVIOUS round's maps into the result
+        array (their device -> pinned copies finished while this round was being enqueued or will shortly)."""
+        for i in range(max(self.prev_start, self.turn - len(self.ring)), self.round_start):
+            self._drain(i % len(self.ring))
+        self.prev_start, self.round_start = self.round_start, self.turn
+
     def finish(self):
-        self._drain(self.turn)
-        self._drain(self.turn ^ 1)
+        for t in range(len(self.ring)):
+            self._drain((self.turn + t) % len(self.ring))
         self.out = None
