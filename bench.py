@@ -51,7 +51,7 @@ def parse():
     ap.add_argument("--frames", type=int, default=32)
     ap.add_argument("--size", type=int, default=518)
     ap.add_argument("--cpu-frames", type=int, default=0, help="frames of the CPU-baseline sample window (0 = largest that fits --cpu-budget)")
-    ap.add_argument("--cpu-budget", type=float, default=45.0, help="seconds one CPU-baseline pass may take")
+    ap.add_argument("--cpu-budget", type=float, default=60.0, help="seconds one CPU-baseline pass may take")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="headline line only (profiling runs)")
     ap.add_argument("--video-frames", type=int, default=1024)

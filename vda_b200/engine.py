@@ -161,6 +161,9 @@ class Engine:
         self.launches_per_run = {}
         self.use_graph = True
         self._warm = set()
+        # tail chunking (see head()): A/B knobs VDA_TAIL_MODE / VDA_TAIL_CHUNK
+        self.tail_mode = int(os.environ.get("VDA_TAIL_MODE", "0"))
+        self.tail_chunk = int(os.environ.get("VDA_TAIL_CHUNK", "1"))
 
     def _ep(self, width, **kw):
         """Epilogue of a launch whose bf16 outputs / residuals are `width` channels wide (x3 parts in
@@ -255,7 +258,7 @@ class Engine:
         return out
 
     # ------------------------------------------------------------------ DPT head
-    def _fusion(self, idx, ws, T, h, w_, x0, skip, skip_relu, size):
+    def _fusion(self, idx, ws, T, h, w_, x0, skip, skip_relu, size, upsample=True):
         """FeatureFusionBlock (util/blocks.py:135-162) on NHWC bf16 maps of h x w_ pixels.
         x0: first input (None for refinenet4, whose only input arrives as skip/skip_relu);
         skip/skip_relu: layerN_rn output and its rectified copy.  The 1x1 out_conv is applied BEFORE
@@ -280,6 +283,8 @@ class Engine:
         L.conv3x3(t, w2, self._ep(Fc, bias=b2, res1=s, out=u), T, h, w_, Fw, Fc)
         v = ws.get(tag + "v", (rows, Fw))
         L.gemm(u, f.w_out, self._ep(Fc, bias=f.b_out, out=v))
+        if not upsample:
+            return v
         H2, W2 = size
         up = ws.get(tag + "up", (T * H2 * W2, Fw))
         sp_stride = Fc if self.fp32 else 0
@@ -329,24 +334,38 @@ class Engine:
         p3 = self._fusion(3, ws, T, gh, gw, p4m, r3, r3r, (2 * gh, 2 * gw))
         p3m = self.motion(3, p3, T, 4 * hw, ws, ws.get("path3m", (T * 4 * hw, Fc * Wd)), stream_ctx=stream_ctx)
         p2 = self._fusion(2, ws, T, 2 * gh, 2 * gw, p3m, r2, r2r, (4 * gh, 4 * gw))
-        p1 = self._fusion(1, ws, T, 4 * gh, 4 * gw, p2, r1, r1r, (8 * gh, 8 * gw))
         F2p = w.F2p
-        o1 = ws.get("out1", (T * 64 * hw, F2p * Wd))
-        L.conv3x3(p1, w.w_oc1, self._ep(F2p, bias=w.b_oc1, out=o1), T, 8 * gh, 8 * gw, Fc * Wd, F2p)
         Ho, Wo = gh * PATCH, gw * PATCH
         depth = ws.get("depth", (T, Ho, Wo), torch.float32)
-        if not sp and F2p in (64, 128) and os.environ.get("VDA_TAIL_FUSED", "0") == "1":
-            # upsample + 3x3(->32) + ReLU + 1x1(->1) + ReLU in one kernel (csrc/depth_tail.cu).  Opt-in: at
-            # one 8-warp CTA per SM its interpolation phase is issue-bound (1.9 ms) and the mma.sync phase
-            # takes 1.5 ms, 3.3 ms together against 3.25 ms for the two-kernel path below.
-            L.depth_tail(o1, w.w_oc2, w.b_oc2, w.w_last, w.b_last, depth, T, 8 * gh, 8 * gw, Ho, Wo, F2p)
-            return depth
-        up = ws.get("out1_up", (T * Ho * Wo, F2p * Wd))
-        sp_stride = F2p if sp else 0
-        L.bilinear_nhwc(o1, up, T, 8 * gh, 8 * gw, Ho, Wo, F2p, ldx=F2p * Wd, ldo=F2p * Wd, split_in=sp_stride,
-                        split_out=sp_stride)
-        L.conv3x3(up, w.w_oc2, L.make_epilogue(bias=w.b_oc2, out_f32=depth, w2=w.w_last, b2=w.b_last,
-                                               store_mode=L.ST_HEADDOT), T, Ho, Wo, F2p * Wd, 32)
+        sp_f, sp_2 = (Fc if sp else 0), (F2p if sp else 0)
+        # Tail = refinenet1's upsample (x2) -> output_conv1 3x3 -> upsample to the input size -> 3x3(->32)+ReLU+1x1+ReLU
+        # (dpt_temporal.py:96-123).  Each stage is a bandwidth-heavy map (1.4 / 0.7 / 2.2 GB per vitl window) that the
+        # next stage reads exactly once, so the chain runs over chunks of `tail_chunk` frames through buffers of ONE
+        # chunk that every chunk reuses: a stage's output is still in the 126 MB L2 when the next stage reads it and
+        # is overwritten before it is ever written back (the reference micro-batches the same stages by 4 frames,
+        # :96-123, to cap memory).  tail_mode 0: whole-window launches; 1: only the last pair chunked; 2: all four.
+        mode, chunk = self.tail_mode, max(1, min(self.tail_chunk, T))
+        if sp or mode == 0:
+            mode, chunk = 0, T
+        v1 = self._fusion(1, ws, T, 4 * gh, 4 * gw, p2, r1, r1r, (8 * gh, 8 * gw), upsample=(mode != 2))
+        h4, w4, h8, w8 = 4 * gh, 4 * gw, 8 * gh, 8 * gw
+        o1_all = None if mode == 2 else ws.get("out1", (T * h8 * w8, F2p * Wd))
+        if mode != 2:
+            L.conv3x3(v1, w.w_oc1, self._ep(F2p, bias=w.b_oc1, out=o1_all), T, h8, w8, Fc * Wd, F2p)
+        for f0 in range(0, T, chunk):
+            n = min(chunk, T - f0)
+            if mode == 2:
+                up = ws.get("tail_up", (chunk * h8 * w8, Fc * Wd))
+                L.bilinear_nhwc(v1[f0 * h4 * w4:], up, n, h4, w4, h8, w8, Fc, ldx=Fc * Wd, ldo=Fc * Wd, split_in=sp_f,
+                                split_out=sp_f)
+                o1 = ws.get("tail_o1", (chunk * h8 * w8, F2p * Wd))
+                L.conv3x3(up, w.w_oc1, self._ep(F2p, bias=w.b_oc1, out=o1), n, h8, w8, Fc * Wd, F2p)
+            else:
+                o1 = o1_all[f0 * h8 * w8:]
+            up2 = ws.get("out1_up", (chunk * Ho * Wo, F2p * Wd))
+            L.bilinear_nhwc(o1, up2, n, h8, w8, Ho, Wo, F2p, ldx=F2p * Wd, ldo=F2p * Wd, split_in=sp_2, split_out=sp_2)
+            L.conv3x3(up2, w.w_oc2, L.make_epilogue(bias=w.b_oc2, out_f32=depth[f0:], w2=w.w_last, b2=w.b_last,
+                                                    store_mode=L.ST_HEADDOT), n, Ho, Wo, F2p * Wd, 32)
         return depth
 
     # ------------------------------------------------------------------ whole window

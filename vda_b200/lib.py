@@ -108,7 +108,6 @@ def _declare(lib):
         "vda_minmax_f32": [vp, C.c_longlong, vp, vp],
         "vda_depth_colorize": [vp, C.c_longlong, vp, vp, vp, i, vp],
         "vda_depth_normalize": [vp, vp, C.c_longlong, i, C.c_double, C.c_double, i, vp, vp],
-        "vda_depth_tail": [vp, i, vp, vp, vp, f, vp, i, i, i, i, i, i, vp],
         "vda_attn_f32": [vp, i, i, vp, i, i, i, i, i, vp],
         "vda_temporal_attn_f32": [vp, vp, vp, i, vp, i, i, i, i, i, i, i, vp],
         "vda_lsq_accum": [vp, vp, C.c_longlong, vp, vp],
@@ -201,13 +200,6 @@ def conv3x3(x, w, epi, n, H, W, Cin, Cout, ldx=None):
 def flash_attn(qk, vt, out, frames, S, heads, s_pad):
     with _timed("attn", 4.0 * frames * heads * S * S * 64):
         check(load().vda_flash_attn_fwd(ptr(qk), ptr(vt), ptr(out), frames, S, heads, s_pad, stream_ptr()))
-    _launched()
-
-
-def depth_tail(x, w3, b3, w1, b1, out, n, h, w, H, W, C, ldx=None):
-    with _timed("conv3x3", 2.0 * n * H * W * 32 * 9 * C):
-        check(load().vda_depth_tail(ptr(x), C if ldx is None else ldx, ptr(w3), ptr(b3), ptr(w1), b1, ptr(out), n, h, w, H, W,
-                                    C, stream_ptr()))
     _launched()
 
 
