@@ -23,3 +23,32 @@ def test_sharded_driver_matches_single_gpu():
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     print(r.stdout[-2000:])
     assert r.returncode == 0, (r.stdout[-1500:] + "\n" + r.stderr[-3000:])
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs on the box")
+def test_two_devices_in_one_process():
+    """Per-device launch state (kernel attributes, SM count): a model on cuda:1 after one on cuda:0 in the same
+    process -- the single-process multi-device mode SURVEY.md 8(e) names as the run.py alternative."""
+    import numpy as np
+
+    from oracle import make_golden as G
+    from oracle import refload
+    from oracle import vda_oracle as O
+    from video_depth_anything.video_depth import VideoDepthAnything
+
+    arch, T, H, W = "vits", 4, 70, 98
+    cfg = O.ARCH[arch]
+    sd = refload.seeded_state_dict(arch, 0)
+    x = G.window_input(T, H, W)
+    gold = np.load(os.path.join(G.GOLDEN_DIR, "fwd_vits_t4_70x98.npz"))["depth"]
+    outs = []
+    for dev in ("cuda:0", "cuda:1", "cuda:0"):
+        m = VideoDepthAnything(encoder=arch, features=cfg["features"], out_channels=cfg["out_channels"])
+        m.load_state_dict(sd, strict=True)
+        m = m.to(dev).eval()
+        with torch.no_grad(), torch.cuda.device(dev):
+            outs.append(m(x.to(dev)).cpu().numpy())
+    for o in outs:
+        msk = gold > 1e-6
+        assert float(np.mean(np.abs(o[msk] - gold[msk]) / gold[msk])) <= 1e-2
+    assert np.abs(outs[0] - outs[1]).max() <= 1e-4 * np.abs(outs[0]).max()
