@@ -202,7 +202,8 @@ def torch_eager_gpu_arm(a, steps=2, warmup=1):
                 out[name]["absrel_vs_eager_fp32"] = float(((y.float() - ref_out).abs()[m] / ref_out[m]).mean())
         finally:
             O.vit_block = naive_block
-    out["note"] = (f"oracle forward (eager torch {torch.__version__}, TF32 off), {a.frames}-frame {a.size}x{a.size} {a.arch} "
+    out["note"] = (f"oracle forward (eager torch {torch.__version__}, torch's default math modes: fp32 matmul without TF32, "
+                   f"cuDNN convolutions may use TF32), {a.frames}-frame {a.size}x{a.size} {a.arch} "
                    f"window, {steps} timed passes after {warmup} warm-up; *_sdpa swaps the naive attention for "
                    f"F.scaled_dot_product_attention")
     return out

@@ -16,6 +16,8 @@ from vda_b200 import parallel
 from vda_b200.video_depth import MODEL_CONFIGS, window_frame_indices
 from video_depth_anything.video_depth import VideoDepthAnything
 
+torch.backends.cuda.matmul.allow_tf32 = False    # the oracle must be a true fp32 reference
+torch.backends.cudnn.allow_tf32 = False
 local = int(os.environ.get("LOCAL_RANK", "0"))
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -67,6 +69,9 @@ assert float(np.abs(gots[own] - got[own]).max()) <= 1e-5 * float(np.abs(got).max
 # FP32-accuracy mode through the sharded path: every pixel within rtol 1e-3 of the oracle (BASELINE.json)
 parallel.set_result_rank(None)
 g32, _ = m.infer_video_depth(frames, 30, input_size=size, device="cuda", fp32=True)
+with parallel.solo():
+    a32, _ = m.infer_video_depth(frames, 30, input_size=size, device="cuda", fp32=True)
+assert float(np.abs(g32 - a32).max()) <= 1e-5 * float(np.abs(a32).max())
 worst = float((np.abs(g32 - want) / (1e-3 * np.abs(want) + 1e-5 * np.abs(want).max())).max())
 print(f"rank {rank}: fp32 mode worst |err| / (1e-3 |ref| + 1e-5 max|ref|) = {worst:.3f}", flush=True)
 assert worst <= 1.0

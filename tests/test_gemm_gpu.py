@@ -130,6 +130,29 @@ def test_gemm_geglu(L, M, C):
     _close(out, want)
 
 
+@pytest.mark.parametrize("halo2", ["1", "2", "0"])
+@pytest.mark.parametrize("n,H,W,C,Cout,bn", [(2, 120, 120, 128, 128, 128), (1, 296, 296, 256, 128, 128), (3, 21, 37, 64, 128, 128),
+                                             (2, 50, 70, 192, 256, 256), (1, 148, 148, 256, 256, 256)])
+def test_conv3x3_cta_pair_halo(L, n, H, W, C, Cout, bn, halo2, monkeypatch):
+    """Halo mode of the CTA-pair kernel (one 10x18 patch per channel block + W ring): BN = 128 by default,
+    BN = 256 with VDA_CONV_HALO2=2; ragged tile edges, odd tile counts; 0 = the tap-by-tap path as comparand."""
+    monkeypatch.setenv("VDA_CONV_HALO2", halo2)
+    x = _rand(n, C, H, W, seed=1).bfloat16()
+    wt = _rand(Cout, C, 3, 3, scale=(9 * C) ** -0.5, seed=2).bfloat16()
+    b = _rand(Cout, seed=3)
+    want = F.conv2d(x.float(), wt.float(), b, padding=1).relu().permute(0, 2, 3, 1)
+    xn = x.permute(0, 2, 3, 1).contiguous()
+    wk = wt.permute(0, 2, 3, 1).reshape(Cout, 9 * C).contiguous()
+    numel, guard = n * H * W * Cout, 4096
+    buf = torch.full((numel + 2 * guard,), 7.0, device="cuda", dtype=torch.bfloat16)
+    out = buf[guard:guard + numel].view(n, H, W, Cout)
+    out.fill_(float("nan"))
+    L.conv3x3(xn, wk, L.make_epilogue(bias=b, out=out, ldo=Cout, act=L.ACT_RELU, cta_pair=2, block_n=bn), n, H, W, C, Cout)
+    torch.cuda.synchronize()
+    _close(out, want)
+    assert (buf[:guard] == 7.0).all() and (buf[guard + numel:] == 7.0).all(), "store outside the output tensor"
+
+
 @pytest.mark.parametrize("s,cin,cout,h,w", [(4, 64, 48, 5, 7), (2, 128, 96, 9, 4), (4, 256, 256, 37, 37), (2, 128, 64, 9, 4),
                                              (2, 512, 512, 37, 66), (4, 64, 32, 19, 3)])
 def test_gemm_convtranspose_store(L, s, cin, cout, h, w):

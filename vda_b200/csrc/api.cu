@@ -339,8 +339,9 @@ int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W,
   p.n_tiles = (Cout + bn - 1) / bn;
   p.epi_tma = pick_epi_tma(epi, true);
   p.stages = pick_stages(bn, two, epi, p.epi_tma);
-  // halo mode (gemm.cu): few output channels -> one halo patch + 9 W tiles per channel block instead of
-  // 9 separate (tap, block) stages.  1-CTA kernel, 8 x 16-pixel tiles, BN <= 64.
+  // halo mode (gemm.cu): one halo patch per channel block + tap-shifted descriptors instead of nine separate
+  // (tap, block) A tiles.  1-CTA kernel: few output channels (BN <= 64; a stage = patch + its 9 W tiles).
+  // CTA-pair kernel: BN = 128 (output_conv1), W tiles in their own ring; needs the bf16 box-store epilogue.
   {
     const char* hv = getenv("VDA_CONV_HALO");  // A/B knob: 0 disables
     p.halo = !(hv && atoi(hv) == 0) && !two && bn <= 64 && C % 64 == 0;
@@ -351,6 +352,15 @@ int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W,
       p.stages = staged ? 2 : max_halo;  // the epilogue's 48 KB of boxes / residual ring sit behind the ring
       const int ring = (bn <= 32 ? 8 * 20480 : 8 * 24576) > max_halo * halo_stage ? (bn <= 32 ? 8 * 20480 : 8 * 24576) : max_halo * halo_stage;
       if (staged && p.stages * halo_stage + 48 * 1024 > ring) p.halo = 0, p.stages = pick_stages(bn, two, epi, p.epi_tma);
+    }
+    const char* h2 = getenv("VDA_CONV_HALO2");  // A/B knob: 0 off, 1 (default) BN = 128 only, 2 also BN = 256
+    const int h2v = h2 ? atoi(h2) : 1;
+    if (two && C % 64 == 0 && p.epi_tma == 2 && ((bn == 128 && h2v >= 1) || (bn == 256 && h2v >= 2))) {
+      const int ring = bn >= 256 ? 6 * 32768 : 8 * 24576;            // Gemm2Cfg<BN>::kStages * kStageBytes
+      const int w_bytes = (bn / 2) * 128;
+      int nw = (ring - epi_box_area_bytes(p.epi_tma) - 2 * 23 * 1024) / w_bytes;
+      if (nw > 16) nw = 16;
+      if (nw >= 4) p.halo = 1, p.stages = nw;
     }
   }
   if (p.halo) {

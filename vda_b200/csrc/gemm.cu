@@ -50,8 +50,10 @@ struct Gemm2Cfg {
   static constexpr int kStages = (BN >= 256) ? 6 : 8;
   static constexpr int kTmemCols = GemmCfg<BN>::kTmemCols;
   static constexpr int kBiasBytes = 2 * 2 * BN * 4;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256 + kBiasBytes + kRowOffBytes;
+  static constexpr int kBarBytes = 512;   // up to kMaxRing2 full + empty barriers, 2 + 2 accumulator, 2 + 2 halo patch
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + kBarBytes + kBiasBytes + kRowOffBytes;
 };
+constexpr int kMaxRing2 = 16;
 
 // halo mode of the 1-CTA kernel: patch of an 8 x 16-pixel tile plus a 1-pixel border, one 64-channel block
 constexpr int kHaloW = 10, kHaloH = 18;
@@ -320,11 +322,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
   // the dynamic smem base offset is identical in both CTAs, so aligned offsets match across the pair
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
-  uint64_t* empty_bar = full_bar + Cfg::kStages;
-  uint64_t* tfull_bar = empty_bar + Cfg::kStages;
+  uint64_t* empty_bar = full_bar + kMaxRing2;
+  uint64_t* tfull_bar = empty_bar + kMaxRing2;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
-  float* s_epi = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + 256);
+  uint64_t* pfull_bar = tempty_bar + 2;   // halo mode: the two patch slots
+  uint64_t* pempty_bar = pfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(pempty_bar + 2);
+  float* s_epi = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes + Cfg::kBarBytes);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -347,13 +351,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
     tma_prefetch_desc(&p.tmB);
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < Cfg::kStages; ++s) {
+    for (int s = 0; s < kMaxRing2; ++s) {
       mbar_init(&full_bar[s], 1);   // leader's: one arrive.expect_tx by the leader's producer
       mbar_init(&empty_bar[s], 1);  // one multicast commit from the leader's MMA thread
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);               // multicast commit
       mbar_init(&tempty_bar[s], 2 * kEpiWarps);  // leader's: epilogue warps of both CTAs
+      mbar_init(&pfull_bar[s], 1);
+      mbar_init(&pempty_bar[s], 1);
     }
     fence_mbar_init();
   }
@@ -367,6 +373,80 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
   const uint32_t tmem_base = *tmem_slot;
   pdl_sync();  // everything above overlapped the previous kernel's tail; global memory from here on
 
+  // ---- halo mode of the CTA-pair kernel (3x3 convs; see the 1-CTA kernel for the idea).  With nine separate
+  // (tap, channel block) A tiles a 256 x 128 pair tile pulls 96 B/clk/SM of operands through L2 -> SM, far above
+  // what the fabric sustains (output_conv1 at 296x296: tensor pipe 46 % active, 19.9 GB of L2 -> SM traffic for a
+  // 1.4 GB map).  Here each CTA fetches ONE 10 x 18-pixel halo patch per 64-channel block (two slots) and the nine
+  // taps are tap-shifted UMMA descriptors into it; the W tiles (this CTA's half, one per tap) stream through their
+  // own ring of p.stages slots behind the patches.  Operand traffic per channel block: 23 + 9 x 8 KB instead of
+  // 9 x 24 KB (BN = 128).
+  constexpr int kWBytes = Cfg::kBBytes;
+  uint8_t* const w_ring = smem + 2 * kHaloSlotBytes;
+  if (p.halo && warp == 0) {
+    const int cblocks = p.C / kBlockK;
+    int ws = 0, ps = 0;
+    uint32_t wphase = 0, pphase = 0;
+    for (int v = tile_begin; v < tile_end; v += tile_step) {
+      const int m2 = v / p.n_tiles, n_t = v - m2 * p.n_tiles;
+      const TileCoord tc = conv_tile_coord(p, 2 * m2 + static_cast<int>(rank));
+      for (int cb = 0; cb < cblocks; ++cb) {
+        mbar_wait(&pempty_bar[ps], pphase ^ 1);
+        if (elect_one()) {
+          if (leader) mbar_expect_tx(&pfull_bar[ps], 2 * kHaloBytes);
+          tma_load_4d_2sm(smem + ps * kHaloSlotBytes, &p.tmH, &pfull_bar[ps], cb * kBlockK, tc.w0 - 1, tc.h0 - 1, tc.img);
+        }
+        __syncwarp();
+        if (++ps == 2) ps = 0, pphase ^= 1;
+        for (int tap = 0; tap < 9; ++tap) {
+          mbar_wait(&empty_bar[ws], wphase ^ 1);
+          if (elect_one()) {
+            if (leader) mbar_expect_tx(&full_bar[ws], 2 * kWBytes);
+            tma_load_2d_2sm(w_ring + ws * kWBytes, &p.tmB, &full_bar[ws], (tap * cblocks + cb) * kBlockK,
+                            n_t * BN + static_cast<int>(rank) * (BN / 2));
+          }
+          __syncwarp();
+          if (++ws == p.stages) ws = 0, wphase ^= 1;
+        }
+      }
+    }
+  } else if (p.halo && warp == 1) {
+    if (leader) {
+      constexpr uint32_t idesc = umma_idesc_f16(2 * kBlockM, BN, true);
+      const int cblocks = p.C / kBlockK;
+      int ws = 0, ps = 0, it = 0;
+      uint32_t wphase = 0, pphase = 0;
+      for (int v = tile_begin; v < tile_end; v += tile_step, ++it) {
+        const int as = it & 1;
+        mbar_wait(&tempty_bar[as], ((it >> 1) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int cb = 0; cb < cblocks; ++cb) {
+          mbar_wait(&pfull_bar[ps], pphase);
+          const uint32_t patch = smem_u32(smem + ps * kHaloSlotBytes);
+          for (int tap = 0; tap < 9; ++tap) {
+            mbar_wait(&full_bar[ws], wphase);
+            tc_fence_after();
+            const int dy = tap / 3, dx = tap - dy * 3;
+            const uint64_t adesc = umma_desc_k_sw128_sbo(patch + (dy * kHaloW + dx) * 128, kHaloW * 128);
+            const uint64_t bdesc = umma_desc_k_sw128(smem_u32(w_ring + ws * kWBytes));
+            if (elect_one()) {
+#pragma unroll
+              for (int k = 0; k < kBlockK / 16; ++k)
+                umma_f16_ss_2cta(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (cb | tap | k) != 0);
+              umma_commit_2cta(&empty_bar[ws]);
+              if (tap == 8) {
+                umma_commit_2cta(&pempty_bar[ps]);
+                if (cb == cblocks - 1) umma_commit_2cta(&tfull_bar[as]);
+              }
+            }
+            __syncwarp();
+            if (++ws == p.stages) ws = 0, wphase ^= 1;
+          }
+          if (++ps == 2) ps = 0, pphase ^= 1;
+        }
+      }
+    }
+  } else
   if (warp == 0) {
     int stage = 0;
     uint32_t phase = 0;
@@ -439,10 +519,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
     const int r = quad * 32 + lane;
     const int et = threadIdx.x - 128;
     const TileSched ts = {tile_begin, tile_step, tile_end, 2, static_cast<int>(rank)};
-    ResRing rr = make_res_ring<BN>(p, ts, smem + p.stages * Cfg::kStageBytes, (Cfg::kStages - p.stages) * Cfg::kStageBytes, et,
-                                   r, half);
+    // operand bytes this launch uses; the epilogue's boxes / residual ring live behind them
+    const int ring_used = p.halo ? 2 * kHaloSlotBytes + p.stages * kWBytes : p.stages * Cfg::kStageBytes;
+    ResRing rr = make_res_ring<BN>(p, ts, smem + ring_used, Cfg::kStages * Cfg::kStageBytes - ring_used, et, r, half);
     // box epilogues: epi_boxes(mode) boxes per column slice in the freed stages; thread 0 of each slice issues the TMA
-    const uint32_t red_base = smem_u32(smem + p.stages * Cfg::kStageBytes) + static_cast<uint32_t>(half) * epi_boxes(p.epi_tma) * kRedBoxBytes;
+    const uint32_t red_base = smem_u32(smem + ring_used) + static_cast<uint32_t>(half) * epi_boxes(p.epi_tma) * kRedBoxBytes;
     const bool red_issuer = (et & 127) == 0;
     int box_ctr = 0;
     int it = 0;
