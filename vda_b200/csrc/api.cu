@@ -353,12 +353,14 @@ int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W,
       const int ring = (bn <= 32 ? 8 * 20480 : 8 * 24576) > max_halo * halo_stage ? (bn <= 32 ? 8 * 20480 : 8 * 24576) : max_halo * halo_stage;
       if (staged && p.stages * halo_stage + 48 * 1024 > ring) p.halo = 0, p.stages = pick_stages(bn, two, epi, p.epi_tma);
     }
-    const char* h2 = getenv("VDA_CONV_HALO2");  // A/B knob: 0 off, 1 (default) BN = 128 only, 2 also BN = 256
-    const int h2v = h2 ? atoi(h2) : 1;
-    if (two && C % 64 == 0 && p.epi_tma == 2 && ((bn == 128 && h2v >= 1) || (bn == 256 && h2v >= 2))) {
+    const char* h2 = getenv("VDA_CONV_HALO2");  // A/B knob: 0 off, 1 BN = 128 only, 2 (default) BN = 128 and 256
+    const int h2v = h2 ? atoi(h2) : 2;
+    const bool res_staged = !p.epi_tma && epi->res_f32 && epi->store_mode == ST_PLAIN && epi->act != ACT_GEGLU;
+    if (two && C % 64 == 0 && (p.epi_tma == 2 || (p.epi_tma == 0 && !res_staged)) &&
+        ((bn == 128 && h2v >= 1) || (bn == 256 && h2v >= 2))) {
       const int ring = bn >= 256 ? 6 * 32768 : 8 * 24576;            // Gemm2Cfg<BN>::kStages * kStageBytes
       const int w_bytes = (bn / 2) * 128;
-      int nw = (ring - epi_box_area_bytes(p.epi_tma) - 2 * 23 * 1024) / w_bytes;
+      int nw = (ring - (p.epi_tma ? epi_box_area_bytes(p.epi_tma) : 0) - 2 * 23 * 1024) / w_bytes;
       if (nw > 16) nw = 16;
       if (nw >= 4) p.halo = 1, p.stages = nw;
     }
