@@ -130,6 +130,20 @@ def test_gemm_geglu(L, M, C):
     _close(out, want)
 
 
+@pytest.mark.parametrize("M,N,K", [(1370, 1024, 4096), (1370, 1024, 1024), (361, 1024, 4096), (130, 256, 512), (5476, 256, 1024)])
+def test_gemm_small_m_split_k(L, M, N, K):
+    """Small-M reduce-add GEMMs (streaming proj / fc2): every pair tile is cut into K ranges that meet in the fp32
+    residual (api.cu: small_m_ksplit); bias must be added exactly once, LayerScale applies to every partial."""
+    a = _rand(M, K, seed=1).bfloat16()
+    w = _rand(N, K, scale=K ** -0.5, seed=2).bfloat16()
+    b, g = _rand(N, seed=3), _rand(N, seed=4)
+    res = _rand(M, N, seed=5)
+    want = res + (a.float() @ w.float().T + b) * g
+    L.gemm(a, w, L.make_epilogue(bias=b, scale=g, res_f32=res, out_f32=res, ldo=N))
+    torch.cuda.synchronize()
+    _close(res, want, 2e-3)
+
+
 @pytest.mark.parametrize("halo2", ["1", "2", "0"])
 @pytest.mark.parametrize("n,H,W,C,Cout,bn", [(2, 120, 120, 128, 128, 128), (1, 296, 296, 256, 128, 128), (3, 21, 37, 64, 128, 128),
                                              (2, 50, 70, 192, 256, 256), (1, 148, 148, 256, 256, 256)])

@@ -108,16 +108,39 @@ static void pick_tile(const vda_epilogue* e, int N, int m_tiles, int* bn_out, bo
     *bn_out = e->block_n;
     return;
   }
+  // single-CTA kernel: the BN with the cheapest schedule, cost = waves x (BN + a fixed per-tile share).  "Largest BN
+  // that still fills the SMs" left e.g. the streaming fc1 (M = 1370, N = 4096) with 176 tiles of 256 columns on 148
+  // SMs = two full-length waves, the second one 19 % occupied; 352 tiles of 128 columns take three half-length waves.
   const int cands[4] = {256, 128, 64, 32};
+  long long best_cost = -1;
+  *bn_out = N >= 64 ? 64 : 32;
   for (int i = 0; i < 4; ++i) {
     const int bn = cands[i];
     if (bn > 32 && bn > ((N + 31) / 32) * 32) continue;
-    if (static_cast<long long>(m_tiles) * ((N + bn - 1) / bn) >= num_sms()) {
-      *bn_out = bn;
-      return;
-    }
+    const long long tiles = static_cast<long long>(m_tiles) * ((N + bn - 1) / bn);
+    const long long waves = (tiles + num_sms() - 1) / num_sms();
+    const long long cost = waves * (bn + 48);
+    if (best_cost < 0 || cost < best_cost) best_cost = cost, *bn_out = bn;
   }
-  *bn_out = N >= 64 ? 64 : 32;
+}
+
+// Small-M problems whose epilogue is the in-place fp32 residual update (proj / fc2 of a streaming frame: M = 1370):
+// too few tiles for the SMs but a long K.  Every 256 x 256 pair tile is cut into `ks` K ranges handled by different CTA
+// pairs whose partial sums meet in the residual through the TMA reduce-add (the tail split-K mechanism with
+// tail_begin = 0).  Returns ks >= 2, or 0 when the launch does not qualify.
+static int small_m_ksplit(const vda_epilogue* e, int M, int N, int K) {
+  const char* kv = getenv("VDA_GEMM_KSPLIT");  // A/B knob: 0 disables
+  if (kv && atoi(kv) == 0) return 0;
+  if (e->cta_pair == 1 || (e->block_n && e->block_n != 256) || N % 256 || e->act != ACT_NONE) return 0;
+  if (!e->res_f32 || e->res_f32 != e->out_f32 || e->out || e->out_relu || e->res1 || e->res2 || e->split ||
+      e->store_mode != ST_PLAIN)
+    return 0;
+  const int pairs = num_sms() / 2, tiles = ((M + 255) / 256) * (N / 256), kblocks = (K + 63) / 64;
+  if (tiles >= pairs) return 0;
+  int ks = pairs / tiles;
+  if (ks > kblocks / 4) ks = kblocks / 4;
+  if (ks > 8) ks = 8;
+  return ks >= 2 ? ks : 0;
 }
 
 // Epilogue flavour (gemm_epilogue.cuh): 1 = in-place fp32 residual update as TMA reduce-add,
@@ -259,8 +282,10 @@ int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, 
   int bn;
   bool two;
   pick_tile(epi, N, p.m_tiles, &bn, &two);
-  p.n_tiles = (N + bn - 1) / bn;
   p.epi_tma = pick_epi_tma(epi, false);
+  const int small_ks = p.epi_tma == 1 ? small_m_ksplit(epi, M, N, K) : 0;
+  if (small_ks) bn = 256, two = true;
+  p.n_tiles = (N + bn - 1) / bn;
   if (p.epi_tma == 4 && bn < 128) p.epi_tma = 0;  // a GEGLU box spans 64 accumulator columns of one column slice
   p.stages = pick_stages(bn, two, epi, p.epi_tma);
   if (p.epi_tma == 1) {
@@ -287,6 +312,7 @@ int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, 
         if (ks >= 2) p.ksplit = ks, p.tail_begin = tiles - rem;
       }
     }
+    if (small_ks && !p.f32_store && p.sched != 2) p.ksplit = small_ks, p.tail_begin = 0;
   } else if (p.epi_tma == 2 || p.epi_tma == 4) {
     // QKV: only the Q|K columns [0, 2D) are stored through the map; GEGLU: N/2 output columns
     const uint64_t dims[2] = {(uint64_t)(epi->store_mode == ST_QKV ? 2 * epi->qkv_d : p.n_out), (uint64_t)M};

@@ -599,7 +599,8 @@ static cudaError_t launch2_bn(const GemmParams& p, int num_sms, cudaStream_t str
     if (e != cudaSuccess) return e;
     configured = 1;
   }
-  const int pairs = ((p.m_tiles + 1) / 2) * p.n_tiles;
+  int pairs = ((p.m_tiles + 1) / 2) * p.n_tiles;
+  if (p.ksplit > 1) pairs += (pairs - p.tail_begin) * (p.ksplit - 1);   // work units: K ranges of the split tiles
   const int max_pairs = num_sms / 2;
   const int grid = 2 * (pairs < max_pairs ? pairs : max_pairs);
   return launch_pdl(gemm_tc2_kernel<BN>, dim3(grid), dim3(kGemmThreads), Cfg::kSmemBytes, stream, p);  // cluster dims are compiled in
