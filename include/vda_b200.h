@@ -136,6 +136,14 @@ int vda_temporal_attn_stream_f32(const float* q, const float* knew, const float*
                                  const float* pe_v, void* out, int ldo, int split, int hw, int heads, int head_dim,
                                  int Tk, void* stream);
 
+/* Fused depth tail (dpt_temporal.py:116-123, dpt.py:117-124): bilinear(align_corners=True) of the NHWC bf16 map
+ * x [n,h,w,ldx>=C] to (H,W), 3x3 conv C->32 (w3 bf16 [32, 9*C], k=(kh,kw,c); b3) + ReLU, 1x1 conv 32->1 (w1, b1) + ReLU
+ * -> out f32 [n,H,W], in one tcgen05 kernel that never materialises the upsampled map.  C in {64, 128}; returns -7 if
+ * the upsampling ratio needs more than 8 x 12 source pixels per 10 x 18 patch (callers then use vda_bilinear_nhwc +
+ * vda_conv3x3_nhwc). */
+int vda_depth_tail(const void* x, int ldx, const void* w3, const float* b3, const float* w1, float b1, float* out,
+                   int n, int h, int w, int H, int W, int C, void* stream);
+
 /* Depth visualisation (utils/dc_utils.py:72-86): minmax2 = {min, max} of x as two fp32 words (any sign);
  * colorize: q = ((d - min) / (max - min) * 255).astype(uint8) evaluated with numpy's three fp32 roundings and
  * truncating cast (bit-exact), out = lut_rgb[q] (3 bytes per pixel) or q if grey. */

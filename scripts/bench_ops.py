@@ -91,6 +91,7 @@ ops = {
     "tailconv": (lambda: L.conv3x3(up2_out, tw3, L.make_epilogue(bias=tb3, out_f32=tdepth, w2=tw1, b2=0.1,
                                                                   store_mode=L.ST_HEADDOT), T, 518, 518, 128, 32),
                  2 * T * 518 * 518 * 32 * 1152),
+    "tail_fused": (lambda: L.depth_tail(up2_in, tw3, tb3, tw1, 0.1, tdepth, T, 296, 296, 518, 518, 128), 2 * T * 518 * 518 * 32 * 1152),
     "gn74": (lambda: L.groupnorm_nhwc(gn_x, gn_w, gn_b, gn_o, gn_ws, T, 5476, 256, 1e-6), 0),
     "tail_unfused": (lambda: (L.bilinear_nhwc(up2_in, up2_out, T, 296, 296, 518, 518, 128),
                               L.conv3x3(up2_out, tw3, L.make_epilogue(bias=tb3, out_f32=tdepth, w2=tw1, b2=0.1,

@@ -237,6 +237,40 @@ def test_preprocess_u8_matches_cv2_path(L, h0, w0, size):
     assert err < 1e-3  # cv2's float cubic path (IPP / SIMD) differs in the last bits of the tap weights: <= 1e-4 of the input range
 
 
+@pytest.mark.parametrize("n,h,w,H,W,C", [(2, 40, 40, 70, 70, 128), (3, 24, 40, 42, 70, 64), (1, 296, 296, 518, 518, 128),
+                                         (2, 296, 528, 518, 924, 64), (1, 8, 16, 14, 28, 128)])
+def test_depth_tail_fused(L, n, h, w, H, W, C):
+    """Fused upsample + 3x3(->32) + ReLU + 1x1 + ReLU (tcgen05, csrc/depth_tail.cu) against the unfused kernel pair
+    (same bf16 interpolation to the bit, so only the fp32 summation order differs) and against torch."""
+    from vda_b200 import packing as P
+
+    assert L.depth_tail_supported(h, w, H, W, C)
+    x = _rand(n, C, h, w, seed=1).bfloat16()
+    w3 = _rand(32, C, 3, 3, scale=(9 * C) ** -0.5, seed=2)
+    b3, w1 = _rand(32, seed=3), _rand(32, seed=4).abs()
+    b1 = 0.05
+    xn = x.permute(0, 2, 3, 1).contiguous()
+    wk, bk = P.conv3x3(w3, b3, device="cuda")
+    numel, guard = n * H * W, 4096
+    buf = torch.full((numel + 2 * guard,), 7.0, device="cuda")
+    out = buf[guard:guard + numel].view(n, H, W)
+    out.fill_(float("nan"))
+    L.depth_tail(xn, wk, bk, w1, b1, out, n, h, w, H, W, C)
+    up = torch.empty(n, H, W, C, device="cuda", dtype=torch.bfloat16)
+    L.bilinear_nhwc(xn, up, n, h, w, H, W, C)
+    ref2 = torch.empty(n, H, W, device="cuda")
+    L.conv3x3(up, wk, L.make_epilogue(bias=bk, out_f32=ref2, w2=w1, b2=b1, store_mode=L.ST_HEADDOT), n, H, W, C, 32)
+    torch.cuda.synchronize()
+    assert not torch.isnan(out).any(), "some output pixels were never written"
+    assert (buf[:guard] == 7.0).all() and (buf[guard + numel:] == 7.0).all(), "store outside the output tensor"
+    upt = F.interpolate(x.float(), size=(H, W), mode="bilinear", align_corners=True).bfloat16().float()
+    y = F.conv2d(upt, w3.bfloat16().float(), b3, padding=1).relu()
+    want = (y * w1.view(1, 32, 1, 1)).sum(1).add(b1).relu()
+    scale = want.abs().max().item()
+    assert (out - ref2).abs().max().item() < 2e-3 * scale      # same operands, different summation order
+    assert (out - want).abs().max().item() < 2e-2 * scale      # torch rounds the upsample differently in the last bf16 bit
+
+
 def test_depth_colorize_bit_exact(L):
     """dc_utils.py:72-86: clip-global min/max, three float32 roundings, truncating uint8 cast -- byte for byte --
     then the colour table look-up.  Includes negative values (min/max are taken over the raw floats)."""

@@ -59,6 +59,12 @@ int encode_bf16_map(CUtensorMap* tm, const void* base, int rank, const uint64_t*
   return encode_map(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, CU_TENSOR_MAP_SWIZZLE_128B, base, rank, dims, strides_bytes, box);
 }
 
+// bf16 tensor map without swizzle (boxes that threads, not the UMMA, read back)
+int encode_bf16_map_plain(CUtensorMap* tm, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                          const uint32_t* box) {
+  return encode_map(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, CU_TENSOR_MAP_SWIZZLE_NONE, base, rank, dims, strides_bytes, box);
+}
+
 static int encode_map(CUtensorMap* tm, CUtensorMapDataType dt, CUtensorMapSwizzle sw, const void* base, int rank,
                       const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box) {
   if (!g_encode) return set_error(-2, "vda_init() has not been called");

@@ -162,6 +162,7 @@ class Engine:
         self.use_graph = True
         self._warm = set()
         # tail chunking (see head()): A/B knobs VDA_TAIL_MODE / VDA_TAIL_CHUNK
+        self.tail_fused = os.environ.get("VDA_TAIL_FUSED", "1") == "1"
         self.tail_mode = int(os.environ.get("VDA_TAIL_MODE", "0"))
         self.tail_chunk = int(os.environ.get("VDA_TAIL_CHUNK", "1"))
 
@@ -347,6 +348,7 @@ class Engine:
         mode, chunk = self.tail_mode, max(1, min(self.tail_chunk, T))
         if sp or mode == 0:
             mode, chunk = 0, T
+        fused = (not sp) and mode == 0 and self.tail_fused and L.depth_tail_supported(8 * gh, 8 * gw, Ho, Wo, F2p)
         v1 = self._fusion(1, ws, T, 4 * gh, 4 * gw, p2, r1, r1r, (8 * gh, 8 * gw), upsample=(mode != 2))
         h4, w4, h8, w8 = 4 * gh, 4 * gw, 8 * gh, 8 * gw
         o1_all = None if mode == 2 else ws.get("out1", (T * h8 * w8, F2p * Wd))
@@ -362,6 +364,11 @@ class Engine:
                 L.conv3x3(up, w.w_oc1, self._ep(F2p, bias=w.b_oc1, out=o1), n, h8, w8, Fc * Wd, F2p)
             else:
                 o1 = o1_all[f0 * h8 * w8:]
+            if fused:
+                # upsample + 3x3(->32) + ReLU + 1x1 + ReLU in one tcgen05 kernel (csrc/depth_tail.cu): the upsampled
+                # map (2.2 GB per vitl window) is built tile by tile in shared memory and never touches HBM
+                L.depth_tail(o1, w.w_oc2, w.b_oc2, w.w_last, w.b_last, depth[f0:], n, h8, w8, Ho, Wo, F2p)
+                continue
             up2 = ws.get("out1_up", (chunk * Ho * Wo, F2p * Wd))
             L.bilinear_nhwc(o1, up2, n, h8, w8, Ho, Wo, F2p, ldx=F2p * Wd, ldo=F2p * Wd, split_in=sp_2, split_out=sp_2)
             L.conv3x3(up2, w.w_oc2, L.make_epilogue(bias=w.b_oc2, out_f32=depth[f0:], w2=w.w_last, b2=w.b_last,

@@ -108,6 +108,7 @@ def _declare(lib):
         "vda_minmax_f32": [vp, C.c_longlong, vp, vp],
         "vda_depth_colorize": [vp, C.c_longlong, vp, vp, vp, i, vp],
         "vda_depth_normalize": [vp, vp, C.c_longlong, i, C.c_double, C.c_double, i, vp, vp],
+        "vda_depth_tail": [vp, i, vp, vp, vp, f, vp, i, i, i, i, i, i, vp],
         "vda_attn_f32": [vp, i, i, vp, i, i, i, i, i, vp],
         "vda_temporal_attn_f32": [vp, vp, vp, i, vp, i, i, i, i, i, i, i, vp],
         "vda_lsq_accum": [vp, vp, C.c_longlong, vp, vp],
@@ -200,6 +201,23 @@ def conv3x3(x, w, epi, n, H, W, Cin, Cout, ldx=None):
 def flash_attn(qk, vt, out, frames, S, heads, s_pad):
     with _timed("attn", 4.0 * frames * heads * S * S * 64):
         check(load().vda_flash_attn_fwd(ptr(qk), ptr(vt), ptr(out), frames, S, heads, s_pad, stream_ptr()))
+    _launched()
+
+
+def depth_tail_supported(h, w, H, W, C):
+    """True if vda_depth_tail takes this shape (host restatement of its argument check)."""
+    if C not in (64, 128) or h <= 1 or w <= 1 or H < h or W < w:
+        return False
+    sy, sx = (h - 1) / (H - 1), (w - 1) / (W - 1)
+    return int(17 * sy + 1e-3) + 3 <= 12 and int(9 * sx + 1e-3) + 3 <= 8
+
+
+def depth_tail(x, w3, b3, w1, b1, out, n, h, w, H, W, C, ldx=None):
+    """Fused bilinear upsample + 3x3 conv (C -> 32) + ReLU + 1x1 (32 -> 1) + ReLU; x NHWC bf16, out f32 [n,H,W]."""
+    nbytes = n * (h * w * C * 2 + H * W * 4)
+    with _timed("conv3x3", 2.0 * n * H * W * 32 * 9 * C, f"depth_tail n={n} {h}x{w}->{H}x{W} C={C} ({nbytes >> 20} MB algorithmic)"):
+        check(load().vda_depth_tail(ptr(x), C if ldx is None else ldx, ptr(w3), ptr(b3), ptr(w1), b1, ptr(out), n, h, w, H, W,
+                                    C, stream_ptr()))
     _launched()
 
 
