@@ -77,9 +77,12 @@ int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W,
 
 /* Flash-style spatial attention, head_dim 64, non-causal (dinov2_layers/attention.py:53-59 / :76).
  * qk: [frames*S, 2D] bf16 (Q | K), vt: [frames*heads, 64, s_pad] bf16 (V transposed, zero padded,
- * s_pad % 8 == 0) -- both written by vda_gemm_bf16 with VDA_ST_QKV.  out: [frames*S, D] bf16. */
+ * s_pad % 8 == 0) -- both written by vda_gemm_bf16 with VDA_ST_QKV.  out: [frames*S, D] bf16.
+ * fixup_flags: NULL = exact online softmax.  Otherwise frames*heads*ceil(S/128) ints, zero on entry and on return:
+ * the kernel runs the optimistic softmax (offset fixed after the first KV tile, no running maximum) and a second
+ * launch recomputes with the exact algorithm any query tile whose sums left the safe range -- same result, faster. */
 int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int frames, int S, int heads, int s_pad,
-                       void* stream);
+                       int* fixup_flags, void* stream);
 
 /* LayerNorm over the last dim (dinov2_layers/block.py:84,87; dinov2.py:310; motion_module.py:175,186).
  * x: [rows, C] f32 (x_is_f32) or bf16; out bf16.  If tokens_per_frame > 0 the first `skip` tokens of

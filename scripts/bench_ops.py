@@ -24,6 +24,7 @@ w2, b2 = r(D, 4 * D, sc=(4 * D) ** -0.5).bfloat16(), r(D)
 qk = torch.empty(M, 2 * D, device=dev, dtype=torch.bfloat16)
 vt = torch.zeros(T * heads, 64, spad, device=dev, dtype=torch.bfloat16)
 ao = torch.empty(M, D, device=dev, dtype=torch.bfloat16)
+aflags = torch.zeros(T * heads * ((S + 127) // 128), device=dev, dtype=torch.int32)
 qkvs = (torch.randn(M, 9 * D, device=dev) * 0.5).bfloat16()   # FP32-accuracy mode: q | k | v as [hi | lo | hi]
 ao3 = torch.empty(M, 3 * D, device=dev, dtype=torch.bfloat16)
 h1 = torch.empty(M, 4 * D, device=dev, dtype=torch.bfloat16)
@@ -109,7 +110,8 @@ ops = {
     "qkv": (lambda: L.gemm(xn, wqkv, L.make_epilogue(bias=bqkv, out=qk, ldo=2 * D, store_mode=L.ST_QKV,
                                                      qkv=(vt, D, heads, S, spad))), 2 * M * 3 * D * D),
     "attn_f32": (lambda: L.attn_f32(qkvs, ao3, D, T, S, heads, in_split=3 * D), 3 * 4 * T * heads * S * S * 64),
-    "attn": (lambda: L.flash_attn(qk, vt, ao, T, S, heads, spad), 4 * T * heads * S * S * 64),
+    "attn": (lambda: L.flash_attn(qk, vt, ao, T, S, heads, spad, aflags), 4 * T * heads * S * S * 64),
+    "attn_exact": (lambda: L.flash_attn(qk, vt, ao, T, S, heads, spad), 4 * T * heads * S * S * 64),
     "proj": (lambda: L.gemm(ao, wproj, L.make_epilogue(bias=bproj, scale=g1, res_f32=tok, out_f32=tok, ldo=D)),
              2 * M * D * D),
     "fc1": (lambda: L.gemm(xn, w1, L.make_epilogue(bias=b1, out=h1, ldo=4 * D, act=L.ACT_GELU)), 2 * M * 4 * D * D),

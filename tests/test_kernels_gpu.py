@@ -28,8 +28,14 @@ def _close(got, want, tol=2e-2):
     assert err <= tol * max(ref, 1e-6), f"max abs err {err} vs ref max {ref}"
 
 
-@pytest.mark.parametrize("frames,S,heads", [(1, 128, 1), (2, 197, 2), (3, 1370, 6), (1, 2443, 3), (2, 64, 1), (32, 1370, 16)])
-def test_flash_attention(L, frames, S, heads):
+def _attn_flags(frames, S, heads):
+    return torch.zeros(frames * heads * ((S + 127) // 128), device="cuda", dtype=torch.int32)
+
+
+@pytest.mark.parametrize("optimistic", [False, True])
+@pytest.mark.parametrize("frames,S,heads", [(1, 128, 1), (2, 197, 2), (3, 1370, 6), (1, 2443, 3), (2, 64, 1), (32, 1370, 16), (1, 7, 2)])
+def test_flash_attention(L, frames, S, heads, optimistic):
+    """optimistic: offset fixed after the first KV tile + fix-up pass (flags stay zero on well-behaved scores)."""
     D = heads * 64
     spad = (S + 7) // 8 * 8
     q = _rand(frames, S, heads, 64, scale=1.5, seed=1).bfloat16()
@@ -39,10 +45,42 @@ def test_flash_attention(L, frames, S, heads):
     vt = torch.zeros(frames * heads, 64, spad, device="cuda", dtype=torch.bfloat16)
     vt[:, :, :S] = v.permute(0, 2, 3, 1).reshape(frames * heads, 64, S)
     out = torch.full((frames * S, D), float("nan"), device="cuda", dtype=torch.bfloat16)
-    L.flash_attn(qk, vt, out, frames, S, heads, spad)
+    flags = _attn_flags(frames, S, heads) if optimistic else None
+    L.flash_attn(qk, vt, out, frames, S, heads, spad, flags)
     torch.cuda.synchronize()
     want = F.scaled_dot_product_attention(q.float().transpose(1, 2), k.float().transpose(1, 2), v.float().transpose(1, 2))
     _close(out.view(frames, S, heads, 64), want.transpose(1, 2), 2e-2)
+    if optimistic:
+        assert int(flags.sum()) == 0
+
+
+@pytest.mark.parametrize("boost", [6.0, 60.0, 400.0])
+def test_flash_attention_optimistic_fixup(L, boost):
+    """Scores far above the first KV tile's maximum: a moderate jump stays inside the optimistic kernel's safe range,
+    a huge one overflows its fixed offset, raises the tile's flag and is recomputed exactly by the fix-up pass.  Either
+    way the result is the exact softmax and the flags are zero again afterwards."""
+    frames, S, heads = 2, 700, 2
+    D = heads * 64
+    spad = (S + 7) // 8 * 8
+    q = _rand(frames, S, heads, 64, scale=1.0, seed=1).bfloat16()
+    k = _rand(frames, S, heads, 64, scale=1.0, seed=2)
+    k[:, 300:340] *= boost            # keys of the third tile dominate (for the rows whose q.k is positive)
+    k[:, 600:] *= 0.5 * boost
+    k = k.bfloat16()
+    v = _rand(frames, S, heads, 64, seed=3).bfloat16()
+    qk = torch.cat([q.reshape(frames * S, D), k.reshape(frames * S, D)], dim=1).contiguous()
+    vt = torch.zeros(frames * heads, 64, spad, device="cuda", dtype=torch.bfloat16)
+    vt[:, :, :S] = v.permute(0, 2, 3, 1).reshape(frames * heads, 64, S)
+    out = torch.full((frames * S, D), float("nan"), device="cuda", dtype=torch.bfloat16)
+    flags = _attn_flags(frames, S, heads)
+    L.flash_attn(qk, vt, out, frames, S, heads, spad, flags)
+    torch.cuda.synchronize()
+    want = F.scaled_dot_product_attention(q.float().transpose(1, 2), k.float().transpose(1, 2), v.float().transpose(1, 2))
+    _close(out.view(frames, S, heads, 64), want.transpose(1, 2), 2e-2)
+    assert int(flags.sum()) == 0, "the fix-up pass must consume every flag"
+    ref = torch.full_like(out, float("nan"))
+    L.flash_attn(qk, vt, ref, frames, S, heads, spad)          # exact kernel alone
+    assert (out.float() - ref.float()).abs().max().item() <= 2e-2 * want.abs().max().item()
 
 
 def test_flash_attention_growing_maxima(L):

@@ -96,6 +96,7 @@ struct alignas(64) AttnParams {
   int S, D, heads, frames;
   int q_tiles, kv_tiles;
   float scale_log2;  // head_dim^-0.5 * log2(e)
+  int* flags;        // [frames*heads*q_tiles] overflow flags of the optimistic kernel / work list of the fix-up pass
 };
 
 // =============================================================================================
@@ -117,9 +118,17 @@ constexpr float kRescaleThreshold = 8.0f;
 // LATE: the wait for PV_{j-1} (needed before P is overwritten / O rescaled) is taken after the
 // exponentials of tile j instead of before them, so that MMA latency hides behind the MUFU work.
 // PK: packed f32x2 scale / row-sum and 3-input max (helpers above).
-template <int POLY, bool LATE, bool PK = false>
+// OPT: optimistic softmax (see the softmax section): no running max / rescale after the first KV tile; a row whose
+// sums left the safe range raises flags[cta] and the same kernel compiled with FIXUP recomputes exactly those query
+// tiles with the exact online softmax (a second launch that normally finds no flag and exits at once).
+template <int POLY, bool LATE, bool PK = false, bool OPT = false, bool FIXUP = false>
 __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __grid_constant__ AttnParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
+  const int cta_linear = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+  if (FIXUP) {
+    pdl_wait();
+    if (p.flags[cta_linear] == 0) return;   // uniform over the CTA: nothing allocated yet
+  }
   if ((smem_u32(smem) & 1023u) != 0) __trap();
   uint8_t* sQ = smem;
   uint8_t* sK = smem + kQBytes;          // [2][16 KB]
@@ -163,7 +172,12 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tmem_S = tmem_base, tmem_P = tmem_base + 128, tmem_O = tmem_base + 192;
-  pdl_sync();  // the QKV GEMM's outputs are read from here on
+  if (FIXUP) {
+    pdl_launch_dependents();
+    if (threadIdx.x == 0) p.flags[cta_linear] = 0;   // consumed (every thread has read it before the barrier above)
+  } else {
+    pdl_sync();  // the QKV GEMM's outputs are read from here on
+  }
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -238,6 +252,103 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
     const float sc = p.scale_log2;
     float m_run = -INFINITY, l_run = 0.f;
 
+    if constexpr (OPT) {
+      // ---- optimistic softmax.  The exact online softmax spends a fifth of its instructions and a dependent chain
+      // of 16 three-input maxima per KV tile on the running maximum, and its lazy O rescale almost never fires after
+      // the first tile.  Here the offset is fixed after tile 0: m_off = (row maximum of tile 0) + 40, so
+      // p = 2^(s - m_off) stays finite unless a later score exceeds tile 0's maximum by more than 2^167 (and still
+      // resolves weights down to 2^-86 of the row's largest); bf16 P and the fp32 accumulators are scale invariant, so
+      // the result is the exact one.  A row whose sum left the safe range (>= 1e30) raises the CTA's flag and the
+      // fix-up pass recomputes that query tile with the exact algorithm below.  With no maximum to wait for, the S
+      // row is consumed in two halves: the second half's tcgen05.ld is in flight while the first half's exponentials run.
+      const uint64_t sc2 = pack2(sc, sc);
+      uint64_t la = pack2(0.f, 0.f), lb = la;
+      float neg_m = 0.f;
+      for (int j = 0; j < n_tiles; ++j) {
+        mbar_wait(s_full, j & 1);
+        tc_fence_after();
+        uint32_t s[128];
+        uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
+        uint32_t(&s1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
+        uint32_t(&s2)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[64]);
+        uint32_t(&s3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[96]);
+        const int kv_left = p.S - j * 128;
+        if (j == 0) {
+          tmem_ld32(tmem_S + lane_off + 0, s0);
+          tmem_ld32(tmem_S + lane_off + 32, s1);
+          tmem_ld32(tmem_S + lane_off + 64, s2);
+          tmem_ld32(tmem_S + lane_off + 96, s3);
+          tmem_ld_wait();
+          if (kv_left < 128) {   // a sequence shorter than one tile: its padding must not set the offset
+#pragma unroll
+            for (int c = 0; c < 128; ++c)
+              if (c >= kv_left) s[c] = 0xff800000u;  // -inf
+          }
+          float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+          for (int c = 0; c < 128; c += 8) {
+            mx0 = fmax3(mx0, __uint_as_float(s[c]), __uint_as_float(s[c + 1]));
+            mx1 = fmax3(mx1, __uint_as_float(s[c + 2]), __uint_as_float(s[c + 3]));
+            mx2 = fmax3(mx2, __uint_as_float(s[c + 4]), __uint_as_float(s[c + 5]));
+            mx3 = fmax3(mx3, __uint_as_float(s[c + 6]), __uint_as_float(s[c + 7]));
+          }
+          neg_m = -(fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * sc + 40.0f);
+        } else {
+          tmem_ld32(tmem_S + lane_off + 0, s0);
+          tmem_ld32(tmem_S + lane_off + 32, s1);
+          tmem_ld_wait();
+          tmem_ld32(tmem_S + lane_off + 64, s2);   // in flight during the first half's exponentials
+          tmem_ld32(tmem_S + lane_off + 96, s3);
+        }
+        const uint64_t nm2 = pack2(neg_m, neg_m);
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          if (hh == 1) {
+            if (j > 0) tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(s_free);   // the whole S row is in registers: S_{j+1} may overwrite it
+          }
+          if (kv_left < 128 && j > 0) {   // last tile: columns beyond the sequence carry no weight (ex2(-inf) = 0)
+#pragma unroll
+            for (int i = 0; i < 64; ++i)
+              if (64 * hh + i >= kv_left) s[64 * hh + i] = 0xff800000u;
+          }
+          uint32_t pk[32];
+#pragma unroll
+          for (int i = 0; i < 64; i += 2) {
+            const int c = 64 * hh + i;
+            float p0, p1;
+            const uint64_t x2 = ffma2(pack2(__uint_as_float(s[c]), __uint_as_float(s[c + 1])), sc2, nm2);
+            if (POLY > 0 && ((i >> 1) % POLY) == 0) {
+              poly_exp2_x2(x2, p0, p1);
+            } else {
+              float x0, x1;
+              unpack2(x2, x0, x1);
+              p0 = fast_exp2(x0), p1 = fast_exp2(x1);
+            }
+            if (i & 2) lb = fadd2(lb, pack2(p0, p1));
+            else la = fadd2(la, pack2(p0, p1));
+            __nv_bfloat162 h = __floats2bfloat162_rn(p0, p1);
+            pk[i >> 1] = *reinterpret_cast<uint32_t*>(&h);
+          }
+          if (hh == 0 && j > 0) {   // PV_{j-1} reads P: it must be complete before P is overwritten
+            mbar_wait(o_done, (j - 1) & 1);
+            tc_fence_after();
+          }
+          tmem_st16(tmem_P + lane_off + 32 * hh, *reinterpret_cast<uint32_t(*)[16]>(&pk[0]));
+          tmem_st16(tmem_P + lane_off + 32 * hh + 16, *reinterpret_cast<uint32_t(*)[16]>(&pk[16]));
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(p_full);
+      }
+      float l0, l1;
+      unpack2(fadd2(la, lb), l0, l1);
+      l_run = l0 + l1;
+      if (__any_sync(0xffffffffu, !(l_run < 1e30f)) && lane == 0) p.flags[cta_linear] = 1;
+    } else
     for (int j = 0; j < n_tiles; ++j) {
       mbar_wait(s_full, j & 1);
       tc_fence_after();
@@ -412,7 +523,7 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
 using namespace vda;
 
 extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int frames, int S, int heads, int s_pad,
-                                  void* stream) {
+                                  int* fixup_flags, void* stream) {
   if (!qk || !vt || !out || frames <= 0 || S <= 0 || heads <= 0 || s_pad < S || s_pad % 8)
     return set_error(-1, "vda_flash_attn_fwd: bad arguments");
   const int D = heads * 64;
@@ -437,26 +548,40 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
   p.q_tiles = (S + 127) / 128;
   p.kv_tiles = (S + 127) / 128;
   p.scale_log2 = 0.125f * 1.4426950408889634f;
-  // A/B knob: VDA_ATTN_POLY = 0 / 4 / 8 (default): one score pair in N evaluated with the packed polynomial exp2
+  p.flags = fixup_flags;
+  // A/B knobs: VDA_ATTN_POLY = 0 / 4 / 8 (default): one score pair in N evaluated with the packed polynomial exp2;
+  // VDA_ATTN_OPT = 0: exact online softmax only, even when the caller passes fix-up flags
   const char* ep = getenv("VDA_ATTN_POLY");
   const int poly = ep ? atoi(ep) : 8;
+  const char* eo = getenv("VDA_ATTN_OPT");
+  const bool opt = fixup_flags != nullptr && !(eo && atoi(eo) == 0);
   static DeviceOnce once;
   int& configured = once.slot();
   if (!configured) {
-    int rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<8, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn smem");
-    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<4, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn smem");
-    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kA2Smem), "attn smem");
+    const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+    int rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<8, true, true>, attr, kA2Smem), "attn smem");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<4, true, true>, attr, kA2Smem), "attn smem");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0, true, true>, attr, kA2Smem), "attn smem");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<8, true, true, true>, attr, kA2Smem), "attn smem");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0, true, true, true>, attr, kA2Smem), "attn smem");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<8, true, true, false, true>, attr, kA2Smem), "attn smem");
     if (rc) return rc;
     configured = 1;
   }
   const dim3 grid(p.q_tiles, heads, frames);
   const cudaStream_t st = static_cast<cudaStream_t>(stream);
   cudaError_t le;
-  if (poly == 8)
+  if (opt) {
+    le = poly == 0 ? launch_pdl(attn_fwd_v2_kernel<0, true, true, true>, grid, dim3(kAttThreads), kA2Smem, st, p)
+                   : launch_pdl(attn_fwd_v2_kernel<8, true, true, true>, grid, dim3(kAttThreads), kA2Smem, st, p);
+    if (le == cudaSuccess)   // fix-up pass: exact kernel on the flagged query tiles only (normally none)
+      le = launch_pdl(attn_fwd_v2_kernel<8, true, true, false, true>, grid, dim3(kAttThreads), kA2Smem, st, p);
+  } else if (poly == 8) {
     le = launch_pdl(attn_fwd_v2_kernel<8, true, true>, grid, dim3(kAttThreads), kA2Smem, st, p);
-  else if (poly == 4)
+  } else if (poly == 4) {
     le = launch_pdl(attn_fwd_v2_kernel<4, true, true>, grid, dim3(kAttThreads), kA2Smem, st, p);
-  else
+  } else {
     le = launch_pdl(attn_fwd_v2_kernel<0, true, true>, grid, dim3(kAttThreads), kA2Smem, st, p);
+  }
   return check_cuda(le, "attn launch");
 }

@@ -202,6 +202,7 @@ class Engine:
         else:
             qk = ws.get("qk", (M, 2 * D))
             vt = ws.get("vt", (T * heads, 64, spad), zero=True)
+            aflags = ws.get("attn_flags", (T * heads * ((S + 127) // 128),), torch.int32, zero=True)
         taps = []
         for i, b in enumerate(w.blocks):
             L.layernorm(tok, b["n1w"], b["n1b"], xn, 1e-6, C=D, split=int(sp))
@@ -211,7 +212,7 @@ class Engine:
             else:
                 L.gemm(xn, b["wqkv"], L.make_epilogue(bias=b["bqkv"], out=qk, ldo=2 * D, store_mode=L.ST_QKV,
                                                       qkv=(vt, D, heads, S, spad)))
-                L.flash_attn(qk, vt, ao, T, S, heads, spad)
+                L.flash_attn(qk, vt, ao, T, S, heads, spad, aflags)
             L.gemm(ao, b["wproj"], L.make_epilogue(bias=b["bproj"], scale=b["g1"], res_f32=tok, out_f32=tok, ldo=D))
             L.layernorm(tok, b["n2w"], b["n2b"], xn, 1e-6, C=D, split=int(sp))
             L.gemm(xn, b["w1"], self._ep(4 * D, bias=b["b1"], out=h1, act=L.ACT_GELU))

@@ -93,7 +93,7 @@ def _declare(lib):
         "vda_set_pdl": [i],
         "vda_gemm_bf16": [vp, i, vp, i, i, i, i, ep, vp],
         "vda_conv3x3_nhwc": [vp, i, vp, i, i, i, i, i, ep, vp],
-        "vda_flash_attn_fwd": [vp, vp, vp, i, i, i, i, vp],
+        "vda_flash_attn_fwd": [vp, vp, vp, i, i, i, i, vp, vp],
         "vda_layernorm": [vp, i, vp, vp, vp, vp, vp, i, i, f, i, i, i, i, i, vp],
         "vda_groupnorm_nhwc": [vp, i, vp, vp, vp, vp, i, i, i, f, i, vp],
         "vda_patch_im2col": [vp, vp, i, i, i, i, i, vp],
@@ -198,10 +198,11 @@ def conv3x3(x, w, epi, n, H, W, Cin, Cout, ldx=None):
     _launched()
 
 
-def flash_attn(qk, vt, out, frames, S, heads, s_pad):
+def flash_attn(qk, vt, out, frames, S, heads, s_pad, flags=None):
+    """flags: int32 [frames*heads*ceil(S/128)] zeros (stays zero) -> optimistic softmax + fix-up pass; None -> exact."""
     with _timed("attn", 4.0 * frames * heads * S * S * 64):
-        check(load().vda_flash_attn_fwd(ptr(qk), ptr(vt), ptr(out), frames, S, heads, s_pad, stream_ptr()))
-    _launched()
+        check(load().vda_flash_attn_fwd(ptr(qk), ptr(vt), ptr(out), frames, S, heads, s_pad, ptr(flags), stream_ptr()))
+    _launched(1 if flags is None else 2)
 
 
 def depth_tail_supported(h, w, H, W, C):
