@@ -34,8 +34,10 @@ def _attn_flags(frames, S, heads):
 
 @pytest.mark.parametrize("optimistic", [False, True])
 @pytest.mark.parametrize("frames,S,heads", [(1, 128, 1), (2, 197, 2), (3, 1370, 6), (1, 2443, 3), (2, 64, 1), (32, 1370, 16), (1, 7, 2)])
-def test_flash_attention(L, frames, S, heads, optimistic):
-    """optimistic: offset fixed after the first KV tile + fix-up pass (flags stay zero on well-behaved scores)."""
+def test_flash_attention(L, frames, S, heads, optimistic, monkeypatch):
+    """optimistic: offset fixed after the first KV tile + fix-up pass (flags stay zero on well-behaved scores);
+    opt-in with VDA_ATTN_OPT=1 (slower than the exact kernel on B200, kept as a measured variant)."""
+    monkeypatch.setenv("VDA_ATTN_OPT", "1" if optimistic else "0")
     D = heads * 64
     spad = (S + 7) // 8 * 8
     q = _rand(frames, S, heads, 64, scale=1.5, seed=1).bfloat16()
@@ -55,10 +57,11 @@ def test_flash_attention(L, frames, S, heads, optimistic):
 
 
 @pytest.mark.parametrize("boost", [6.0, 60.0, 400.0])
-def test_flash_attention_optimistic_fixup(L, boost):
+def test_flash_attention_optimistic_fixup(L, boost, monkeypatch):
     """Scores far above the first KV tile's maximum: a moderate jump stays inside the optimistic kernel's safe range,
     a huge one overflows its fixed offset, raises the tile's flag and is recomputed exactly by the fix-up pass.  Either
     way the result is the exact softmax and the flags are zero again afterwards."""
+    monkeypatch.setenv("VDA_ATTN_OPT", "1")
     frames, S, heads = 2, 700, 2
     D = heads * 64
     spad = (S + 7) // 8 * 8

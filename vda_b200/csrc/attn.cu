@@ -550,11 +550,15 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
   p.scale_log2 = 0.125f * 1.4426950408889634f;
   p.flags = fixup_flags;
   // A/B knobs: VDA_ATTN_POLY = 0 / 4 / 8 (default): one score pair in N evaluated with the packed polynomial exp2;
-  // VDA_ATTN_OPT = 0: exact online softmax only, even when the caller passes fix-up flags
+  // VDA_ATTN_OPT = 1: optimistic softmax + fix-up pass when the caller passes flags.  OFF by default: measured on B200
+  // it is 5 % SLOWER in the window (10.5 -> 11.0 ms, profiles/r02c_ab_attn_optimistic_negative.log) although it issues a
+  // third fewer instructions per KV tile and has no maximum chain -- the kernel is not issue- or latency-bound but sits
+  // on two equally loaded pipes, TMEM reads (a 128 x 128 fp32 S tile is 64 KB at 64 B/clk/SM = 1024 clk) and MUFU
+  // (128 ex2 per row at 16/clk/SM = 1024 clk), and the extra launch of the fix-up pass costs more than the lean loop saves.
   const char* ep = getenv("VDA_ATTN_POLY");
   const int poly = ep ? atoi(ep) : 8;
   const char* eo = getenv("VDA_ATTN_OPT");
-  const bool opt = fixup_flags != nullptr && !(eo && atoi(eo) == 0);
+  const bool opt = fixup_flags != nullptr && eo && atoi(eo) == 1;
   static DeviceOnce once;
   int& configured = once.slot();
   if (!configured) {

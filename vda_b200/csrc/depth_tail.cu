@@ -6,10 +6,11 @@
 // The two-kernel form writes the upsampled map (2.2 GB per vitl window) and reads it back: 5.1 GB of HBM traffic for
 // 0.75 GB of algorithmic bytes.  Here the upsampled map never exists: per 8 x 16-pixel output tile
 //   * the TMA producer fetches the source pixels under the tile's 10 x 18 halo patch (at most 8 x 12 of them),
-//   * ten interpolation warps build the UPSAMPLED halo patch straight in shared memory, one thread per (patch
-//     column, 8 channels, half of the rows): the source row pair is reduced to its horizontal lerp in fp32 registers
-//     and every patch row is one vertical lerp, rounded to bf16 and stored in the SWIZZLE_128B pattern that a TMA box
-//     would have produced (same arithmetic, to the bit, as bilinear_nhwc_kernel + the conv's zero padding),
+//   * twenty interpolation warps build the UPSAMPLED halo patch straight in shared memory, one thread per (patch
+//     column, 8 channels, quarter of the rows): the source row pair is reduced to its horizontal lerp in fp32 registers
+//     (packed fp32x2 arithmetic) and every patch row is one vertical lerp, rounded to bf16 and stored in the
+//     SWIZZLE_128B pattern that a TMA box would have produced (same arithmetic, to the bit, as bilinear_nhwc_kernel +
+//     the conv's zero padding),
 //   * the MMA warp reads the nine taps as tap-shifted UMMA descriptors into that patch (gemm.cu, halo mode) against
 //     the 9 x C/64 weight tiles, which stay resident in shared memory for the whole kernel,
 //   * four epilogue warps do bias + ReLU + the 32-wide dot + ReLU on the TMEM accumulator and store one float per pixel.
@@ -46,7 +47,8 @@ struct alignas(64) TailParams {
 
 template <int CB>
 struct TailCfg {
-  static constexpr int kInterpWarps = 5 * CB;   // 10 patch columns x 8*CB channel chunks x 2 row halves = 160*CB threads
+  static constexpr int kRowParts = 4;           // the 18 patch rows are split 5 + 5 + 4 + 4 over four threads
+  static constexpr int kInterpWarps = 10 * CB;  // 10 patch columns x 8*CB channel chunks x 4 row parts = 320*CB threads
   static constexpr int kThreads = 32 * (kTailCtrlWarps + kTailEpiWarps + kInterpWarps);
   static constexpr int kWBytes = 9 * CB * kWTile;
   static constexpr int kSrcStage = CB * kSrcBytes;
@@ -196,9 +198,9 @@ __global__ void __launch_bounds__(TailCfg<CB>::kThreads, 1) depth_tail_tc_kernel
     constexpr int kChunks = 8 * CB;
     const int chunk = t % kChunks;
     const int px = (t / kChunks) % kPW;
-    const int half = t / (kChunks * kPW);
+    const int part = t / (kChunks * kPW);
     const int cb = chunk >> 3, k = chunk & 7;
-    const int py_begin = half * (kPH / 2), py_end = py_begin + kPH / 2;
+    const int py_begin = part < 2 ? 5 * part : 10 + 4 * (part - 2), py_end = py_begin + (part < 2 ? 5 : 4);
     int it = 0;
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
       const int s = it & 1;
@@ -212,23 +214,26 @@ __global__ void __launch_bounds__(TailCfg<CB>::kThreads, 1) depth_tail_tc_kernel
       const int x0 = min(static_cast<int>(fx), p.w - 1);
       const int x1 = min(x0 + 1, p.w - 1);
       const float lx = fx - x0;
+      const uint64_t lx2 = f2pack(lx, lx);
       mbar_wait(&src_full[s], ph);
       mbar_wait(&patch_empty[s], ph ^ 1);
       const uint32_t src = smem_u32(sSrc + s * Cfg::kSrcStage + cb * kSrcBytes) + k * 16;
       const uint32_t o0 = static_cast<uint32_t>(x0 - sx0) * 128, o1 = static_cast<uint32_t>(x1 - sx0) * 128;
       const uint32_t dst = smem_u32(sPatch + s * Cfg::kPatchStage + cb * kPatchSlot);
-      float h0[8], h1[8];
-      auto load_row = [&](int y, float (&hh)[8]) {
+      // h0 / h1: horizontal lerps of the two source rows under the current patch row, 8 channels as 4 fp32 pairs
+      uint64_t h0[4], h1[4];
+      auto load_row = [&](int y, uint64_t (&hh)[4]) {
         const uint32_t row = src + static_cast<uint32_t>(y - sy0) * (kSW * 128);
         uint32_t pp[4], qq[4];
         asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(pp[0]), "=r"(pp[1]), "=r"(pp[2]), "=r"(pp[3]) : "r"(row + o0));
         asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(qq[0]), "=r"(qq[1]), "=r"(qq[2]), "=r"(qq[3]) : "r"(row + o1));
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const float2 fp = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(pp + i));
-          const float2 fq = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(qq + i));
-          hh[2 * i] = fmaf(lx, fq.x - fp.x, fp.x);
-          hh[2 * i + 1] = fmaf(lx, fq.y - fp.y, fp.y);
+          // bf16x2 word -> (fp32, fp32): low half shifted up, high half masked; fq - fp and the fma as in the
+          // scalar kernel (fmaf(lx, fq - fp, fp)), two channels per instruction
+          const uint64_t fp = f2pack(__uint_as_float(pp[i] << 16), __uint_as_float(pp[i] & 0xffff0000u));
+          const uint64_t fq = f2pack(__uint_as_float(qq[i] << 16), __uint_as_float(qq[i] & 0xffff0000u));
+          hh[i] = f2fma(lx2, f2sub(fq, fp), fp);
         }
       };
       int cur0 = -1, cur1 = -1;
@@ -242,10 +247,11 @@ __global__ void __launch_bounds__(TailCfg<CB>::kThreads, 1) depth_tail_tc_kernel
           const int y0 = min(static_cast<int>(fy), p.h - 1);
           const int y1 = min(y0 + 1, p.h - 1);
           const float ly = fy - y0;
+          const uint64_t ly2 = f2pack(ly, ly);
           if (y0 != cur0) {
             if (y0 == cur1) {
 #pragma unroll
-              for (int i = 0; i < 8; ++i) h0[i] = h1[i];
+              for (int i = 0; i < 4; ++i) h0[i] = h1[i];
             } else {
               load_row(y0, h0);
             }
@@ -254,7 +260,7 @@ __global__ void __launch_bounds__(TailCfg<CB>::kThreads, 1) depth_tail_tc_kernel
           if (y1 != cur1) {
             if (y1 == y0) {
 #pragma unroll
-              for (int i = 0; i < 8; ++i) h1[i] = h0[i];
+              for (int i = 0; i < 4; ++i) h1[i] = h0[i];
             } else {
               load_row(y1, h1);
             }
@@ -262,8 +268,9 @@ __global__ void __launch_bounds__(TailCfg<CB>::kThreads, 1) depth_tail_tc_kernel
           }
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            const __nv_bfloat162 r2 = __floats2bfloat162_rn(fmaf(ly, h1[2 * i] - h0[2 * i], h0[2 * i]),
-                                                            fmaf(ly, h1[2 * i + 1] - h0[2 * i + 1], h0[2 * i + 1]));
+            float r0, r1;
+            f2unpack(f2fma(ly2, f2sub(h1[i], h0[i]), h0[i]), r0, r1);
+            const __nv_bfloat162 r2 = __floats2bfloat162_rn(r0, r1);
             o[i] = *reinterpret_cast<const uint32_t*>(&r2);
           }
         }
