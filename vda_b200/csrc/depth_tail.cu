@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(TailCfg<CB>::kThreads, 1) depth_tail_tc_kernel
       int img, Y0, X0;
       tail_tile_coord(p, tile, img, Y0, X0);
       const int sy0 = tail_src_base(p.sy, Y0, p.h), sx0 = tail_src_base(p.sx, X0, p.w);
-      mbar_wait(&src_empty[s], ((it >> 1) & 1) ^ 1);
+      mbar_wait_parked(&src_empty[s], ((it >> 1) & 1) ^ 1);
       if (elect_one()) {
         mbar_expect_tx(&src_full[s], Cfg::kSrcStage);
         for (int cb = 0; cb < CB; ++cb)
@@ -145,8 +145,8 @@ __global__ void __launch_bounds__(TailCfg<CB>::kThreads, 1) depth_tail_tc_kernel
     for (int tile = blockIdx.x; tile < p.num_tiles; tile += gridDim.x, ++it) {
       const int s = it & 1;
       const uint32_t ph = (it >> 1) & 1;
-      mbar_wait(&tempty[s], ph ^ 1);
-      mbar_wait(&patch_full[s], ph);
+      mbar_wait_parked(&tempty[s], ph ^ 1);
+      mbar_wait_parked(&patch_full[s], ph);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + s * 32;
       const uint32_t patch = smem_u32(sPatch + s * Cfg::kPatchStage);
@@ -177,7 +177,7 @@ __global__ void __launch_bounds__(TailCfg<CB>::kThreads, 1) depth_tail_tc_kernel
       const int s = it & 1;
       int img, Y0, X0;
       tail_tile_coord(p, tile, img, Y0, X0);
-      mbar_wait(&tfull[s], (it >> 1) & 1);
+      mbar_wait_parked(&tfull[s], (it >> 1) & 1);
       tc_fence_after();
       uint32_t raw[32];
       tmem_ld32(tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + s * 32, raw);
@@ -215,13 +215,15 @@ __global__ void __launch_bounds__(TailCfg<CB>::kThreads, 1) depth_tail_tc_kernel
       const int x1 = min(x0 + 1, p.w - 1);
       const float lx = fx - x0;
       const uint64_t lx2 = f2pack(lx, lx);
-      mbar_wait(&src_full[s], ph);
-      mbar_wait(&patch_empty[s], ph ^ 1);
+      mbar_wait_parked(&src_full[s], ph, 200);
+      mbar_wait_parked(&patch_empty[s], ph ^ 1, 200);
       const uint32_t src = smem_u32(sSrc + s * Cfg::kSrcStage + cb * kSrcBytes) + k * 16;
       const uint32_t o0 = static_cast<uint32_t>(x0 - sx0) * 128, o1 = static_cast<uint32_t>(x1 - sx0) * 128;
       const uint32_t dst = smem_u32(sPatch + s * Cfg::kPatchStage + cb * kPatchSlot);
-      // h0 / h1: horizontal lerps of the two source rows under the current patch row, 8 channels as 4 fp32 pairs
-      uint64_t h0[4], h1[4];
+      // hA / hB: horizontal lerps (8 channels as 4 fp32 pairs) of the two source rows under the current patch row.
+      // Which of the two holds the upper row alternates (`flip`), so moving down by one source row reloads one
+      // buffer and copies nothing.
+      uint64_t hA[4], hB[4];
       auto load_row = [&](int y, uint64_t (&hh)[4]) {
         const uint32_t row = src + static_cast<uint32_t>(y - sy0) * (kSW * 128);
         uint32_t pp[4], qq[4];
@@ -236,45 +238,46 @@ __global__ void __launch_bounds__(TailCfg<CB>::kThreads, 1) depth_tail_tc_kernel
           hh[i] = f2fma(lx2, f2sub(fq, fp), fp);
         }
       };
-      int cur0 = -1, cur1 = -1;
-      for (int py = py_begin; py < py_end; ++py) {
-        const int Y = Y0 - 1 + py;
-        const int R = py * kPW + px;   // patch row
-        const uint32_t at = dst + static_cast<uint32_t>(R) * 128 + (static_cast<uint32_t>(k ^ (R & 7)) << 4);
-        uint32_t o[4] = {0u, 0u, 0u, 0u};   // outside the image: the convolution's zero padding
-        if (col_in && Y >= 0 && Y < p.H) {
-          const float fy = p.sy * Y;
-          const int y0 = min(static_cast<int>(fy), p.h - 1);
-          const int y1 = min(y0 + 1, p.h - 1);
-          const float ly = fy - y0;
-          const uint64_t ly2 = f2pack(ly, ly);
-          if (y0 != cur0) {
-            if (y0 == cur1) {
+      auto emit = [&](uint32_t at, float ly, const uint64_t (&lo)[4], const uint64_t (&hi)[4]) {
+        const uint64_t ly2 = f2pack(ly, ly);
+        uint32_t o[4];
 #pragma unroll
-              for (int i = 0; i < 4; ++i) h0[i] = h1[i];
-            } else {
-              load_row(y0, h0);
-            }
-            cur0 = y0;
-          }
-          if (y1 != cur1) {
-            if (y1 == y0) {
-#pragma unroll
-              for (int i = 0; i < 4; ++i) h1[i] = h0[i];
-            } else {
-              load_row(y1, h1);
-            }
-            cur1 = y1;
-          }
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            float r0, r1;
-            f2unpack(f2fma(ly2, f2sub(h1[i], h0[i]), h0[i]), r0, r1);
-            const __nv_bfloat162 r2 = __floats2bfloat162_rn(r0, r1);
-            o[i] = *reinterpret_cast<const uint32_t*>(&r2);
-          }
+        for (int i = 0; i < 4; ++i) {
+          float r0, r1;
+          f2unpack(f2fma(ly2, f2sub(hi[i], lo[i]), lo[i]), r0, r1);
+          const __nv_bfloat162 r2 = __floats2bfloat162_rn(r0, r1);
+          o[i] = *reinterpret_cast<const uint32_t*>(&r2);
         }
         asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(at), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+      };
+      int ya = -1, yb = -1;   // source rows held by hA / hB
+#pragma unroll
+      for (int i = 0; i < 5; ++i) {
+        const int py = py_begin + i;
+        if (py < py_end) {
+          const int Y = Y0 - 1 + py;
+          const int R = py * kPW + px;   // patch row
+          const uint32_t at = dst + static_cast<uint32_t>(R) * 128 + (static_cast<uint32_t>(k ^ (R & 7)) << 4);
+          if (col_in && Y >= 0 && Y < p.H) {
+            const float fy = p.sy * Y;
+            const int y0 = min(static_cast<int>(fy), p.h - 1);
+            const int y1 = min(y0 + 1, p.h - 1);
+            const float ly = fy - y0;
+            if (y0 == ya) {            // hA is the upper row
+              if (y1 != yb) load_row(y1, hB), yb = y1;
+              emit(at, ly, hA, hB);
+            } else if (y0 == yb) {     // moved down by one source row: hB becomes the upper row
+              if (y1 != ya) load_row(y1, hA), ya = y1;
+              emit(at, ly, hB, hA);
+            } else {
+              load_row(y0, hA), ya = y0;
+              if (y1 != yb) load_row(y1, hB), yb = y1;
+              emit(at, ly, hA, hB);
+            }
+          } else {                     // outside the image: the convolution's zero padding
+            asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(at), "r"(0u) : "memory");
+          }
+        }
       }
       fence_proxy_async_smem();   // generic-proxy writes of the patch -> visible to the UMMA (async proxy) reads
       __syncwarp();
