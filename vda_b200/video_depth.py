@@ -225,9 +225,11 @@ class VideoDepthAnything(nn.Module):
                 dl.push(maps[:m], lo)
                 owned.append((lo, lo + m))
 
-        self._run_video(frames, input_size, dev, fp32, sink if want else None, dl.next_round if want else None)
+        # the scan owns the device buffers the downloader's side-stream copies read: keep it until they have drained
+        scan = self._run_video(frames, input_size, dev, fp32, sink if want else None, dl.next_round if want else None)
         if want:
             dl.finish()
+        del scan
         self.last_owned_frames = owned
         return out, target_fps
 
@@ -303,7 +305,7 @@ class VideoDepthAnything(nn.Module):
             main.synchronize()
             timing["seconds_device"] = time.perf_counter() - t0
             timing["seconds_to_last_forward"] = e_begin.elapsed_time(e_last) * 1e-3
-        return timing
+        return scan
 
     def _downloader(self, dev, h0, w0, up, slots):
         key = (str(dev), h0, w0, up, slots)

@@ -11,7 +11,7 @@ from torch import nn
 from . import lib as L
 from .engine import Engine, StreamCache
 from .modules import ARCH, DinoEncoder, DPTTemporalHead
-from .preprocess import net_input_size, preprocess_frames
+from .preprocess import net_input_size
 from .video_depth import INFER_LEN, INTERP_LEN, OVERLAP
 
 
@@ -36,6 +36,7 @@ class VideoDepthAnything(nn.Module):
         self.id = -1
         self._engine = None
         self._cache = None
+        self._io = None
 
     def _apply(self, fn, *a, **k):
         self._engine = None
@@ -95,7 +96,22 @@ class VideoDepthAnything(nn.Module):
             elif self._cache.fp32 != eng.fp32:
                 raise RuntimeError("infer_video_depth_one: `fp32` must stay the same for all frames of a stream "
                                    "(the temporal cache holds projections in that precision)")
-            x = preprocess_frames(frame[None], [0], nh, nw, dev)
+            io = self._io
+            if io is None or io["key"] != (self.frame_height, self.frame_width, nh, nw, str(dev)):
+                # per-stream staging, allocated once: pinned frame in, device frame, network input, resized depth,
+                # pinned depth out (a pinned allocation per frame costs more than the pre-processing kernel)
+                h0, w0 = self.frame_height, self.frame_width
+                io = self._io = dict(
+                    key=(h0, w0, nh, nw, str(dev)),
+                    pin_in=torch.empty(1, h0, w0, 3, dtype=torch.uint8, pin_memory=True),
+                    dev_in=torch.empty(1, h0, w0, 3, dtype=torch.uint8, device=dev),
+                    x=torch.empty(1, 3, nh, nw, dtype=torch.float32, device=dev),
+                    out=torch.empty(1, h0, w0, dtype=torch.float32, device=dev),
+                    pin_out=torch.empty(h0, w0, dtype=torch.float32, pin_memory=True))
+            io["pin_in"].numpy()[0] = frame
+            io["dev_in"].copy_(io["pin_in"], non_blocking=True)
+            L.preprocess_u8(io["dev_in"], io["x"], nh, nw)
+            x = io["x"]
             slot = self._free_slot()
             if self.id == 0:
                 cur = []
@@ -104,9 +120,10 @@ class VideoDepthAnything(nn.Module):
                 assert len(cur) == INFER_LEN - 1
             self._cache.begin_frame(cur, slot)
             d = eng.forward(x, stream_ctx=self._cache)
-            out = torch.empty(1, self.frame_height, self.frame_width, dtype=torch.float32, device=dev)
-            L.bilinear_f32(d, out, 1, nh, nw, self.frame_height, self.frame_width)
-            new_depth = out[0].cpu().numpy()
+            L.bilinear_f32(d, io["out"], 1, nh, nw, self.frame_height, self.frame_width)
+            io["pin_out"].copy_(io["out"][0], non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            new_depth = io["pin_out"].numpy().copy()
         if self.id == 0:
             # copy the cache to simulate a full window (video_depth_stream.py:117-119)
             self.frame_cache_list = [slot] * INFER_LEN
