@@ -2,11 +2,11 @@
 # Round profile under gpurun (one GPU): launch list of the bench command + ncu --set full captures of the
 # hot kernels, each only after the same command has exited 0 without ncu.  Outputs in gpurun_out/.
 mkdir -p gpurun_out
-TAG=${TAG:-r01b}
+TAG=${TAG:-r02}
 set -x
-python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/${TAG}_plain_bench.log 2>&1 &&
+python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-extras > gpurun_out/${TAG}_plain_bench.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 2500 --csv --log-file gpurun_out/${TAG}_launches.csv \
-  python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/${TAG}_ncu_ll.log 2>&1
+  python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-extras > gpurun_out/${TAG}_ncu_ll.log 2>&1
 for op in ${OPS:-attn fc1 tailconv ln}; do
   case $op in
     attn) k=attn_fwd_v2 ;;
