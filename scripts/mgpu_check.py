@@ -48,12 +48,14 @@ print(f"rank {rank}/{world} all: windows {n_win}, absrel vs oracle fp32 {e_oracl
       f"{e_alone:.2e}", flush=True)
 assert got.shape == (n, h, w) and e_oracle <= 1e-2 and e_alone < 1e-4
 
+print(f"rank {rank}: result on rank 0 only", flush=True)
 parallel.set_result_rank(0)
 got0, _ = m.infer_video_depth(frames, 30, input_size=size, device="cuda")
 assert (got0 is None) == (rank != 0)
 if rank == 0:
     assert float(np.abs(got0 - got).max()) <= 1e-5 * float(np.abs(got).max())
 
+print(f"rank {rank}: sharded result", flush=True)
 parallel.set_result_sharded()
 gots, _ = m.infer_video_depth(frames, 30, input_size=size, device="cuda")
 own = np.zeros(n, bool)
@@ -67,6 +69,7 @@ assert (own == want_own).all()
 assert float(np.abs(gots[own] - got[own]).max()) <= 1e-5 * float(np.abs(got).max())
 
 # FP32-accuracy mode through the sharded path: every pixel within rtol 1e-3 of the oracle (BASELINE.json)
+print(f"rank {rank}: fp32 mode", flush=True)
 parallel.set_result_rank(None)
 g32, _ = m.infer_video_depth(frames, 30, input_size=size, device="cuda", fp32=True)
 with parallel.solo():

@@ -22,7 +22,12 @@ def test_sharded_driver_matches_single_gpu():
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "scripts", "mgpu_check.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     print(r.stdout[-2000:])
-    assert r.returncode == 0, (r.stdout[-1500:] + "\n" + r.stderr[-3000:])
+    if r.returncode != 0:        # the whole stderr, not a tail: exit-time NCCL warnings bury the Python traceback
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(ROOT, "gpurun_out", "mgpu_check_failure.log"), "w") as f:
+            f.write(r.stdout + "\n==== stderr ====\n" + r.stderr)
+    tb = r.stderr[r.stderr.find("Traceback"):] if "Traceback" in r.stderr else r.stderr
+    assert r.returncode == 0, (r.stdout[-1500:] + "\n" + tb[:4000])
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs on the box")

@@ -132,7 +132,7 @@ def _run(world, n_frames, mode):
     return res
 
 
-@pytest.mark.parametrize("world,n_frames", [(2, 100), (2, 23), (3, 130), (2, 20)])
+@pytest.mark.parametrize("world,n_frames", [(2, 100), (2, 23), (3, 130), (2, 20), (4, 100)])
 def test_sharded_scan_every_rank_gets_the_oracle_result(world, n_frames):
     res = _run(world, n_frames, "all")
     want = _oracle(n_frames)
@@ -145,6 +145,13 @@ def test_result_on_one_rank_only():
     res = _run(2, 120, "1")
     np.testing.assert_array_equal(res[1], _oracle(120))
     assert np.isnan(res[0]).all()
+
+
+def test_result_on_rank0_with_idle_ranks_in_the_last_round():
+    """4 ranks, 5 windows: ranks 1..3 have no window in round 1 but still take part in its exchange and gather."""
+    res = _run(4, 100, "0")
+    np.testing.assert_array_equal(res[0], _oracle(100))
+    assert all(np.isnan(res[r]).all() for r in (1, 2, 3))
 
 
 def test_result_sharded_frames_partition_the_video():
