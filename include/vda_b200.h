@@ -99,6 +99,16 @@ int vda_layernorm(const void* x, int x_is_f32, const float* gamma, const float* 
 int vda_groupnorm_nhwc(const void* x, int ldx, const float* gamma, const float* beta, void* out, double* stats_ws,
                        int n, int hw, int C, float eps, int split, void* stream);
 /* split > 0: x is a split tensor whose parts are `split` elements apart; out is [n, hw, 3*C] split, parts C apart. */
+/* Allocation-free variant of vda_groupnorm_nhwc for callers that cannot allocate scratch (CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  It has NO counterpart in the reference.
+ * The statistics scratch is a file-scope `static __device__` array inside the library
+ * (96 * VDA_GROUPNORM_STATIC_MAX_N doubles = 48 KB, held by every GPU that loads the library until exit); its device
+ * address is resolved once per device with cudaGetSymbolAddress.  The call makes no cudaMalloc / cudaFree / allocating
+ * library call.  n > VDA_GROUPNORM_STATIC_MAX_N is rejected (-8).  All calls on a device share the array: calls that
+ * overlap on the GPU (different streams) race; serialise them or use vda_groupnorm_nhwc with your own scratch. */
+#define VDA_GROUPNORM_STATIC_MAX_N 64
+int vda_groupnorm_nhwc_static(const void* x, int ldx, const float* gamma, const float* beta, void* out, int n, int hw,
+                              int C, float eps, int split, void* stream);
 
 /* 14x14/stride-14 patch gather: x f32 NCHW [frames,3,H,W] -> A bf16 [frames*(H/14)*(W/14), ldk],
  * k = (c,kh,kw), zero padded to ldk (dinov2_layers/patch_embed.py:66,76-78). */

@@ -453,6 +453,29 @@ static int launch_ln(const void* x, const float* gamma, const float* beta, void*
   return check_cuda(le, "layernorm launch");
 }
 
+// ------------------------------------------------------------------ allocation-free GroupNorm scratch
+// Scratch of vda_groupnorm_nhwc_static: lives in the module image of every device that loads the library (48 KB
+// each, until exit).  In HOST code the name `g_gn_static_ws` is only a handle for the runtime, not a device address:
+// the address is asked for once per device, with that device current, through cudaGetSymbolAddress.
+constexpr int kGnStaticMaxN = VDA_GROUPNORM_STATIC_MAX_N;
+static __device__ __align__(256) double g_gn_static_ws[96 * kGnStaticMaxN];
+
+static int gn_static_ws(double** out) {
+  static double* resolved[kMaxDevices] = {};  // benign race: every thread resolves the same address
+  const int dev = current_device();
+  if (dev < 0 || dev >= kMaxDevices) return set_error(-2, "vda_groupnorm_nhwc_static: device %d out of range", dev);
+  if (!resolved[dev]) {
+    double* p = nullptr;
+    const int rc = check_cuda(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_gn_static_ws),
+                              "cudaGetSymbolAddress(g_gn_static_ws)");
+    if (rc) return rc;
+    if (!p) return set_error(-2, "vda_groupnorm_nhwc_static: no device address for the static scratch on device %d", dev);
+    resolved[dev] = p;
+  }
+  *out = resolved[dev];
+  return 0;
+}
+
 extern "C" {
 
 int vda_layernorm(const void* x, int x_is_f32, const float* gamma, const float* beta, void* out, void* out_nope,
@@ -550,6 +573,21 @@ int vda_im2col_s2(const void* x, void* a, int n, int h, int w, int C, void* stre
                                static_cast<cudaStream_t>(stream), static_cast<const bf16*>(x), static_cast<bf16*>(a), h, w, ho, wo, C,
                                total),
                     "im2col_s2 launch");
+}
+
+// GroupNorm without any allocation by the caller or the library: the statistics scratch is the file-scope device array
+// above.  Same launches as vda_groupnorm_nhwc (the sums are cleared by its memset each call; the array otherwise keeps
+// the previous call's contents).  All calls on one device share the array: calls that overlap on the GPU race.
+int vda_groupnorm_nhwc_static(const void* x, int ldx, const float* gamma, const float* beta, void* out, int n, int hw,
+                              int C, float eps, int split, void* stream) {
+  if (n > kGnStaticMaxN)
+    return set_error(-8, "vda_groupnorm_nhwc_static: n=%d images exceed the static scratch (VDA_GROUPNORM_STATIC_MAX_N=%d); "
+                         "use vda_groupnorm_nhwc with caller-owned scratch", n, kGnStaticMaxN);
+  if (!x || !out || C % 64 || n <= 0 || hw <= 0) return set_error(-1, "vda_groupnorm_nhwc_static: bad arguments (C%%64)");
+  double* ws = nullptr;
+  const int rc = gn_static_ws(&ws);
+  if (rc) return rc;
+  return vda_groupnorm_nhwc(x, ldx, gamma, beta, out, ws, n, hw, C, eps, split, stream);
 }
 
 }  // extern "C"

@@ -96,6 +96,7 @@ def _declare(lib):
         "vda_flash_attn_fwd": [vp, vp, vp, i, i, i, i, vp, vp],
         "vda_layernorm": [vp, i, vp, vp, vp, vp, vp, i, i, f, i, i, i, i, i, vp],
         "vda_groupnorm_nhwc": [vp, i, vp, vp, vp, vp, i, i, i, f, i, vp],
+        "vda_groupnorm_nhwc_static": [vp, i, vp, vp, vp, i, i, i, f, i, vp],
         "vda_patch_im2col": [vp, vp, i, i, i, i, i, vp],
         "vda_add_cls_pos": [vp, vp, vp, vp, i, i, i, vp],
         "vda_bilinear_nhwc": [vp, i, vp, i, i, i, i, i, i, i, i, i, vp],
@@ -270,6 +271,16 @@ def groupnorm_nhwc(x, gamma, beta, out, stats_ws, n, hw, C, eps, ldx=None, split
     with _timed("hbm:groupnorm", n * hw * C * 2 * (2 * (2 if split else 1) + parts), f"groupnorm n={n} hw={hw} C={C}"):
         check(load().vda_groupnorm_nhwc(ptr(x), C if ldx is None else ldx, ptr(gamma), ptr(beta), ptr(out), ptr(stats_ws),
                                         n, hw, C, eps, split, stream_ptr()))
+    _launched(3)
+
+
+GROUPNORM_STATIC_MAX_N = 64    # VDA_GROUPNORM_STATIC_MAX_N of include/vda_b200.h
+
+
+def groupnorm_nhwc_static(x, gamma, beta, out, n, hw, C, eps, ldx=None, split=0):
+    """GroupNorm whose scratch is the library's file-scope device array (no allocation anywhere; n <= 64)."""
+    check(load().vda_groupnorm_nhwc_static(ptr(x), C if ldx is None else ldx, ptr(gamma), ptr(beta), ptr(out),
+                                           n, hw, C, eps, split, stream_ptr()))
     _launched(3)
 
 
