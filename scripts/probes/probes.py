@@ -26,4 +26,5 @@ def load():
     vp, i = C.c_void_p, C.c_int
     lib.vda_debug_umma_shift.argtypes = [vp, vp, vp, i, i, i, vp]
     lib.vda_debug_mma_rate.argtypes = [vp, i, i, i, vp]
+    lib.vda_debug_pipe_rate.argtypes = [vp, i, i, i, i, vp]
     return lib

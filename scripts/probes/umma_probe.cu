@@ -14,6 +14,12 @@ extern "C" {
 int vda_debug_umma_shift(const void* G, const void* W, float* D, int row0, int sbo, int base_offset, void* stream);
 /* `ctas` x `threads` threads each issue iters*8 mma.sync.m16n8k16 bf16 (no memory traffic). */
 int vda_debug_mma_rate(float* out, int ctas, int threads, int iters, void* stream);
+/* Pipe-rate probes for the attention kernel's softmax warps: every warp of `ctas` x `threads` runs `iters` rounds of
+ * what = 0: four tcgen05.ld.32x32b.x32 (its 32 lanes x 128 fp32 columns = 16 KB) + wait::ld;
+ * what = 1: 32 independent ex2.approx.ftz.f32;  what = 2: 32 independent cvt.rn.bf16x2.f32;
+ * what = 3: 16 ex2 + 8 cvt + 8 fma.f32x2 interleaved (the softmax mix).
+ * clk[cta*warps + warp] = clock64 ticks that warp spent in the loop. */
+int vda_debug_pipe_rate(long long* clk, int what, int ctas, int threads, int iters, void* stream);
 }
 
 namespace vda {
@@ -97,9 +103,125 @@ __global__ void __launch_bounds__(512) mma_rate_kernel(float* out, int iters) {
   if (acc == 123.456f) out[0] = acc;
 }
 
+
+template <int what>
+__global__ void __launch_bounds__(512) pipe_rate_kernel(long long* clk, int iters) {
+  __shared__ uint32_t tmem_slot;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0) {
+    tmem_alloc(&tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t t0 = tmem_slot + (static_cast<uint32_t>((warp & 3) * 32) << 16) + ((warp >> 2) & 3) * 128;
+  uint32_t acc = lane;
+  float f[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) f[i] = -0.001f * (lane + i + 1);
+  __syncthreads();
+  const long long c0 = clock64();
+  if (what == 0) {
+    for (int it = 0; it < iters; ++it) {
+      uint32_t a[32], b[32], c[32], d[32];
+      tmem_ld32(t0, a);
+      tmem_ld32(t0 + 32, b);
+      tmem_ld32(t0 + 64, c);
+      tmem_ld32(t0 + 96, d);
+      tmem_ld_wait();
+      acc ^= a[0] ^ b[7] ^ c[13] ^ d[31];
+    }
+  } else if (what == 1) {
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(f[i]));
+    }
+  } else if (what == 2) {
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+      for (int i = 0; i < 32; i += 2) {
+        uint32_t h0, h1;
+        asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(h0) : "f"(f[i]), "f"(f[i + 1]));
+        asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(h1) : "f"(f[i + 1]), "f"(f[i]));
+        acc ^= h0 + h1;
+      }
+    }
+  } else if (what == 4 || what == 5 || what == 8) {
+    float m[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) m[i] = f[i];
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        if (what == 4) asm volatile("max.f32 %0, %0, %1, %2;" : "+f"(m[i & 7]) : "f"(f[i]), "f"(f[(i + 5) & 31]));
+        if (what == 5) asm volatile("max.f32 %0, %0, %1;" : "+f"(m[i & 7]) : "f"(f[i]));
+        if (what == 8) {
+          if (i & 1) asm volatile("max.f32 %0, %0, %1, %2;" : "+f"(m[i & 7]) : "f"(f[i]), "f"(f[(i + 5) & 31]));
+          else asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(f[i]));
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc ^= __float_as_uint(m[i]);
+  } else if (what == 6 || what == 7) {
+    uint64_t g[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) asm("mov.b64 %0, {%1, %2};" : "=l"(g[i]) : "f"(f[2 * i]), "f"(f[2 * i + 1]));
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        if (what == 6) asm volatile("fma.rn.f32x2 %0, %0, %0, %0;" : "+l"(g[i & 15]));
+        else asm volatile("add.f32x2 %0, %0, %0;" : "+l"(g[i & 15]));
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) acc ^= static_cast<uint32_t>(g[i]);
+  } else {
+    uint64_t g[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) asm("mov.b64 %0, {%1, %2};" : "=l"(g[i]) : "f"(f[2 * i]), "f"(f[2 * i + 1]));
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(f[2 * i]));
+        asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(f[2 * i + 1]));
+        uint32_t h0;
+        asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(h0) : "f"(f[16 + i]), "f"(f[17 + i]));
+        asm volatile("fma.rn.f32x2 %0, %0, %0, %0;" : "+l"(g[i]));
+        acc ^= h0;
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc ^= static_cast<uint32_t>(g[i]);
+  }
+  const long long c1 = clock64();
+#pragma unroll
+  for (int i = 0; i < 32; ++i) acc ^= __float_as_uint(f[i]);
+  if (lane == 0) clk[blockIdx.x * (blockDim.x >> 5) + warp] = (c1 - c0) | (acc == 0x12345u ? 1 : 0);
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem_slot, 512);
+  }
+}
+
 }  // namespace vda
 
 using namespace vda;
+
+extern "C" int vda_debug_pipe_rate(long long* clk, int what, int ctas, int threads, int iters, void* stream) {
+  if (!clk || ctas <= 0 || threads <= 0 || threads > 512 || threads % 32) return set_error(-1, "vda_debug_pipe_rate: bad arguments");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  switch (what) {
+#define VDA_PR(W) case W: pipe_rate_kernel<W><<<ctas, threads, 0, st>>>(clk, iters); break;
+    VDA_PR(0) VDA_PR(1) VDA_PR(2) VDA_PR(3) VDA_PR(4) VDA_PR(5) VDA_PR(6) VDA_PR(7) VDA_PR(8)
+#undef VDA_PR
+    default: return set_error(-1, "vda_debug_pipe_rate: what = 0..8");
+  }
+  return check_cuda(cudaGetLastError(), "pipe rate launch");
+}
 
 extern "C" int vda_debug_mma_rate(float* out, int ctas, int threads, int iters, void* stream) {
   if (!out || ctas <= 0 || threads <= 0 || threads > 512 || threads % 32) return set_error(-1, "vda_debug_mma_rate: bad arguments");

@@ -17,87 +17,11 @@
 #include <string.h>
 
 #include "common.cuh"
+#include "attn_common.cuh"
 #include "api_internal.h"
 #include "../../include/vda_b200.h"
 
 namespace vda {
-
-__device__ __forceinline__ float fast_exp2(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-
-// 2^x on the FMA pipe (Cody-Waite split + degree-3 polynomial, rel. error 1.1e-4, invisible after the
-// bf16 rounding of P): the MUFU unit does 16 ex2/clk/SM and bounds head_dim-64 attention, so a fixed
-// fraction of the exponentials is evaluated here instead to balance the XU and FMA pipes.
-__device__ __forceinline__ float poly_exp2(float x) {
-  x = fmaxf(x, -126.0f);
-  const float fl = x + 12582912.0f;           // 1.5 * 2^23: integer part lands in the low mantissa bits
-  const float f = x - (fl - 12582912.0f);     // f in [-0.5, 0.5]
-  float r = fmaf(0.05459282f, f, 0.24221784f);
-  r = fmaf(r, f, 0.6933686f);
-  r = fmaf(r, f, 1.0f);
-  return __int_as_float(__float_as_int(r) + (__float_as_int(fl) << 23));
-}
-
-// Packed fp32x2 arithmetic (FFMA2 / FADD2) and the 3-input max (FMNMX3) of sm_100: the softmax warps are
-// issue-slot bound next to the MUFU limit, and these halve the FMA-pipe instruction count per score.
-__device__ __forceinline__ uint64_t pack2(float a, float b) {
-  uint64_t r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
-  return r;
-}
-__device__ __forceinline__ void unpack2(uint64_t v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
-__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
-  uint64_t d;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
-  return d;
-}
-__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
-  uint64_t d;
-  asm("add.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-  return d;
-}
-__device__ __forceinline__ float fmax3(float a, float b, float c) {
-  float d;
-  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
-  return d;
-}
-
-// poly_exp2 on a pair of scores with packed arithmetic (10 FMA-pipe instructions per pair).
-__device__ __forceinline__ void poly_exp2_x2(uint64_t x, float& p0, float& p1) {
-  float x0, x1;
-  unpack2(x, x0, x1);
-  x = pack2(fmaxf(x0, -126.0f), fmaxf(x1, -126.0f));
-  const uint64_t magic = pack2(12582912.0f, 12582912.0f), nmagic = pack2(-12582912.0f, -12582912.0f);
-  const uint64_t fl = fadd2(x, magic);
-  const uint64_t f = ffma2(fadd2(fl, nmagic), pack2(-1.0f, -1.0f), x);
-  uint64_t r = ffma2(pack2(0.05459282f, 0.05459282f), f, pack2(0.24221784f, 0.24221784f));
-  r = ffma2(r, f, pack2(0.6933686f, 0.6933686f));
-  r = ffma2(r, f, pack2(1.0f, 1.0f));
-  float r0, r1, f0, f1;
-  unpack2(r, r0, r1);
-  unpack2(fl, f0, f1);
-  p0 = __int_as_float(__float_as_int(r0) + (__float_as_int(f0) << 23));
-  p1 = __int_as_float(__float_as_int(r1) + (__float_as_int(f1) << 23));
-}
-
-constexpr int kAttThreads = 192;
-constexpr int kQBytes = 128 * 64 * 2;        // 16 KB
-constexpr int kKBytes = 128 * 64 * 2;        // 16 KB
-constexpr int kVBytes = 64 * 128 * 2;        // 16 KB (two 64x64 sub-tiles)
-constexpr int kAttTmemCols = 256;            // S: cols [0,128), P: [128,192), O: [192,256)
-
-struct alignas(64) AttnParams {
-  CUtensorMap tmQK;  // 3D (2D, S, frames), box (64, 128, 1)
-  CUtensorMap tmV;   // 3D (s_pad, 64, frames*heads), box (64, 64, 1)
-  bf16* out;
-  int S, D, heads, frames;
-  int q_tiles, kv_tiles;
-  float scale_log2;  // head_dim^-0.5 * log2(e)
-  int* flags;        // [frames*heads*q_tiles] overflow flags of the optimistic kernel / work list of the fix-up pass
-};
 
 // =============================================================================================
 // S row in registers, P and O in TMEM (the first-generation kernel staged P through shared memory and kept O in
@@ -121,7 +45,7 @@ constexpr float kRescaleThreshold = 8.0f;
 // OPT: optimistic softmax (see the softmax section): no running max / rescale after the first KV tile; a row whose
 // sums left the safe range raises flags[cta] and the same kernel compiled with FIXUP recomputes exactly those query
 // tiles with the exact online softmax (a second launch that normally finds no flag and exits at once).
-template <int POLY, bool LATE, bool PK = false, bool OPT = false, bool FIXUP = false>
+template <int POLY, bool LATE, bool PK = false, bool OPT = false, bool FIXUP = false, bool PROF = false>
 __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __grid_constant__ AttnParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const int cta_linear = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
@@ -348,10 +272,15 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
       unpack2(fadd2(la, lb), l0, l1);
       l_run = l0 + l1;
       if (__any_sync(0xffffffffu, !(l_run < 1e30f)) && lane == 0) p.flags[cta_linear] = 1;
-    } else
+    } else {
+    long long pt[7] = {0, 0, 0, 0, 0, 0, 0};
+    const long long pt_begin = PROF ? clk_after(0.f) : 0;
     for (int j = 0; j < n_tiles; ++j) {
+      long long c0 = 0, c1 = 0, c2 = 0, c3 = 0, c4 = 0, c5 = 0;
+      if (PROF) c0 = clk_after(l_run);
       mbar_wait(s_full, j & 1);
       tc_fence_after();
+      if (PROF) c1 = clk_after(0.f);
       uint32_t s[128];
       {
         uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
@@ -367,6 +296,7 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(s_free);
+      if (PROF) c2 = clk_after(__uint_as_float(s[127]));
       const int kv_left = p.S - j * 128;
       if (kv_left < 128) {
 #pragma unroll
@@ -421,6 +351,7 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
         }
       }
       const float neg_m = -m_run;
+      if (PROF) c3 = clk_after(neg_m);
       float l0 = 0.f, l1 = 0.f;
       const uint64_t sc2 = pack2(sc, sc), nm2 = pack2(neg_m, neg_m);
       uint64_t la = pack2(0.f, 0.f), lb = la;
@@ -458,9 +389,15 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
         if (!LATE) tmem_st16(tmem_P + lane_off + (c0 >> 1), *reinterpret_cast<uint32_t(*)[16]>(pc));
       }
       if (LATE) {
+        if (PROF) {
+          float d0, d1;
+          unpack2(fadd2(la, lb), d0, d1);
+          c4 = clk_after(d0 + d1 + __uint_as_float(pk[63]));
+        }
         if (j > 0) {
           mbar_wait(o_done, (j - 1) & 1);
           tc_fence_after();
+          if (PROF) c5 = clk_after(0.f);
           if (__any_sync(0xffffffffu, need)) {
 #pragma unroll
             for (int c0 = 0; c0 < 64; c0 += 32) {
@@ -483,6 +420,16 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(p_full);
+      if (PROF) {
+        const long long c6 = clk_after(0.f);
+        if (j == 0) c5 = c4;
+        pt[0] += c1 - c0, pt[1] += c2 - c1, pt[2] += c3 - c2, pt[3] += c4 - c3, pt[4] += c5 - c4, pt[5] += c6 - c5;
+      }
+    }
+    if (PROF && lane == 0) {
+      pt[6] = clk_after(0.f) - pt_begin;
+      for (int i = 0; i < 7; ++i) p.prof[(static_cast<long long>(cta_linear) * 4 + quad) * 8 + i] = pt[i];
+    }
     }
     // ---- epilogue: O / l -> bf16
     mbar_wait(o_done, (n_tiles - 1) & 1);
@@ -520,7 +467,19 @@ __global__ void __launch_bounds__(kAttThreads, 2) attn_fwd_v2_kernel(const __gri
 
 }  // namespace vda
 
+#ifdef VDA_ATTN_EXPERIMENTS   // A/B builds only (see attn3.cu): persistent / ping-pong variants and the phase clocks
+namespace vda {
+int launch_attn_v3(const AttnParams& p, int poly, bool pingpong, cudaStream_t st);   // attn3.cu
+int launch_attn_v3_chained(const AttnParams& p, cudaStream_t st);
+}
+#endif
 using namespace vda;
+
+#ifdef VDA_ATTN_EXPERIMENTS
+// Phase-clock instrumentation (scripts/attn_phase_prof.py): not declared in the public header.
+static long long* g_attn_prof = nullptr;
+extern "C" void vda_debug_attn_prof(long long* buf) { g_attn_prof = buf; }
+#endif
 
 extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int frames, int S, int heads, int s_pad,
                                   int* fixup_flags, void* stream) {
@@ -549,16 +508,39 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
   p.kv_tiles = (S + 127) / 128;
   p.scale_log2 = 0.125f * 1.4426950408889634f;
   p.flags = fixup_flags;
+#ifdef VDA_ATTN_EXPERIMENTS
+  p.prof = g_attn_prof;
+#endif
   // A/B knobs: VDA_ATTN_POLY = 0 / 4 / 8 (default): one score pair in N evaluated with the packed polynomial exp2;
   // VDA_ATTN_OPT = 1: optimistic softmax + fix-up pass when the caller passes flags.  OFF by default: measured on B200
   // it is 5 % SLOWER in the window (10.5 -> 11.0 ms, profiles/r02c_ab_attn_optimistic_negative.log) although it issues a
-  // third fewer instructions per KV tile and has no maximum chain -- the kernel is not issue- or latency-bound but sits
-  // on two equally loaded pipes, TMEM reads (a 128 x 128 fp32 S tile is 64 KB at 64 B/clk/SM = 1024 clk) and MUFU
-  // (128 ex2 per row at 16/clk/SM = 1024 clk), and the extra launch of the fix-up pass costs more than the lean loop saves.
+  // third fewer instructions per KV tile and has no maximum chain.  What the phase clocks and pipe probes of round 2 show
+  // (profiles/r02d_attn_v2_phase_clocks_*.log, r02d_pipe_rate_all.log, r02d_ncu_attn_phase_buckets.txt): TMEM reads are
+  // NOT a limit (tcgen05.ld sustains ~900 B/clk/SM; a 64 KB S tile is ~150 clk of latency); a softmax warp alone on its
+  // scheduler needs ~1040 clk per KV tile for the exponentials (MUFU floor 896 with 1 pair in 8 on the FMA pipe) plus
+  // ~900 clk in which it issues no MUFU at all (wait for S incl. the CTA's first TMA round trip, tcgen05.ld + row maximum
+  // ~470, barrier round trips, P store, epilogue).  Two co-resident CTAs overlap those phases by chance: 2500 clk per tile
+  // and CTA = 1250 per SM against the 900-1040 the MUFU pipe would allow.
   const char* ep = getenv("VDA_ATTN_POLY");
   const int poly = ep ? atoi(ep) : 8;
   const char* eo = getenv("VDA_ATTN_OPT");
   const bool opt = fixup_flags != nullptr && eo && atoi(eo) == 1;
+#ifdef VDA_ATTN_EXPERIMENTS
+  // VDA_ATTN_V = 3: persistent ping-pong kernel (attn3.cu; VDA_ATTN_PP = 0: free-running streams); 4: chained mode
+  // (VDA_ATTN_IPC work items per CTA); default 2 = this file.  All measured slower (profiles/r02d_ab_attn_v3_*).
+  const char* ev = getenv("VDA_ATTN_V");
+  const int version = ev ? atoi(ev) : 2;
+  if (version == 4 && !opt) {
+    const char* ei = getenv("VDA_ATTN_IPC");
+    p.ipc = ei ? atoi(ei) : 2;
+    if (p.ipc < 1) p.ipc = 1;
+    return launch_attn_v3_chained(p, static_cast<cudaStream_t>(stream));
+  }
+  if (version == 3 && !opt) {
+    const char* epp = getenv("VDA_ATTN_PP");
+    return launch_attn_v3(p, poly, !(epp && atoi(epp) == 0), static_cast<cudaStream_t>(stream));
+  }
+#endif
   static DeviceOnce once;
   int& configured = once.slot();
   if (!configured) {
@@ -575,6 +557,15 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
   const dim3 grid(p.q_tiles, heads, frames);
   const cudaStream_t st = static_cast<cudaStream_t>(stream);
   cudaError_t le;
+#ifdef VDA_ATTN_EXPERIMENTS
+  if (p.prof) {
+    const char* e1 = getenv("VDA_ATTN_ONE_CTA");   // phase clocks without a co-resident CTA: pad the smem request
+    const int smem = (e1 && atoi(e1) == 1) ? 120 * 1024 : kA2Smem;
+    check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<8, true, true, false, false, true>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, smem), "attn smem");
+    le = launch_pdl(attn_fwd_v2_kernel<8, true, true, false, false, true>, grid, dim3(kAttThreads), smem, st, p);
+  } else
+#endif
   if (opt) {
     le = poly == 0 ? launch_pdl(attn_fwd_v2_kernel<0, true, true, true>, grid, dim3(kAttThreads), kA2Smem, st, p)
                    : launch_pdl(attn_fwd_v2_kernel<8, true, true, true>, grid, dim3(kAttThreads), kA2Smem, st, p);
