@@ -77,7 +77,23 @@ m3_h = r(T * 5476, 256)
 m3_wg, m3_bg = r(2048, 256, sc=1 / 16).to(torch.bfloat16), r(2048)
 m3_g = torch.empty(T * 5476, 1024, device=dev, dtype=torch.bfloat16)
 
+cr1, cr2 = torch.randn_like(cy), torch.randn_like(cy)
+cyr = torch.empty_like(cy)
+m3_r1 = r(T * 5476, 256).to(torch.bfloat16)
+m3_o = torch.empty_like(m3_r1)
+pj_r1 = r(M, D).to(torch.bfloat16)
+pj_o = torch.empty_like(pj_r1)
+
 ops = {
+    # bf16 residuals / ReLU'd second output (FeatureFusion / ResidualConvUnit epilogues, motion proj_out + residual)
+    "conv148_r2": (lambda: L.conv3x3(cx, cw, L.make_epilogue(bias=cb, res1=cr1, res2=cr2, out=cy, out_relu=cyr, ldo=256), T, 148, 148, 256, 256),
+                   2 * T * 148 * 148 * 256 * 9 * 256),
+    "conv148_r1": (lambda: L.conv3x3(cx, cw, L.make_epilogue(bias=cb, res1=cr1, out=cy, ldo=256), T, 148, 148, 256, 256),
+                   2 * T * 148 * 148 * 256 * 9 * 256),
+    "conv148_orelu": (lambda: L.conv3x3(cx, cw, L.make_epilogue(bias=cb, out=cy, out_relu=cyr, ldo=256), T, 148, 148, 256, 256),
+                      2 * T * 148 * 148 * 256 * 9 * 256),
+    "mm3_res1": (lambda: L.gemm(m3_a, m3_wo, L.make_epilogue(bias=m3_bo, res1=m3_r1, out=m3_o, ldo=256)), 2 * T * 5476 * 256 * 256),
+    "gemm1024_res1": (lambda: L.gemm(ao, wproj, L.make_epilogue(bias=bproj, res1=pj_r1, out=pj_o, ldo=D)), 2 * M * D * D),
     "mm3_geglu": (lambda: L.gemm(m3_a, m3_wg, L.make_epilogue(bias=m3_bg, out=m3_g, ldo=1024, act=L.ACT_GEGLU)), 2 * T * 5476 * 2048 * 256),
     "mm3_qkv": (lambda: L.gemm(m3_a, m3_wqkv, L.make_epilogue(out=m3_qkv, ldo=768)), 2 * T * 5476 * 768 * 256),
     "mm3_out": (lambda: L.gemm(m3_a, m3_wo, L.make_epilogue(bias=m3_bo, res_f32=m3_h, out_f32=m3_h, ldo=256)), 2 * T * 5476 * 256 * 256),

@@ -74,7 +74,11 @@ parallel.set_result_rank(None)
 g32, _ = m.infer_video_depth(frames, 30, input_size=size, device="cuda", fp32=True)
 with parallel.solo():
     a32, _ = m.infer_video_depth(frames, 30, input_size=size, device="cuda", fp32=True)
-assert float(np.abs(g32 - a32).max()) <= 1e-5 * float(np.abs(a32).max())
+# sharded vs one rank alone: equal up to the order of the fp32 adds of the split-K reduce-add tiles (3x longer K in this
+# mode, so more GEMMs take that path); a tenth of the rtol 1e-3 budget
+d32 = float(np.abs(g32 - a32).max() / np.abs(a32).max())
+print(f"rank {rank}: fp32 mode max rel diff vs one rank alone {d32:.2e}", flush=True)
+assert d32 <= 1e-4
 worst = float((np.abs(g32 - want) / (1e-3 * np.abs(want) + 1e-5 * np.abs(want).max())).max())
 print(f"rank {rank}: fp32 mode worst |err| / (1e-3 |ref| + 1e-5 max|ref|) = {worst:.3f}", flush=True)
 assert worst <= 1.0

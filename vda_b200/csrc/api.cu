@@ -155,6 +155,13 @@ static int pick_epi_tma(const vda_epilogue* e, bool conv) {
   const char* ev = getenv("VDA_GEMM_NO_TMA_EPI");  // A/B knob: 1 disables all, 2 disables the bf16 store flavour
   const int off_lvl = ev ? atoi(ev) : 0;
   const bool off = off_lvl == 1;
+  const auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+  if (!off && !e->split && (e->out_relu || e->res1 || e->res2)) {
+    // bf16 residuals / ReLU'd second output: cooperative 64-byte-row boxes (gemm_epilogue.cuh, MODE 5)
+    const bool ok = e->store_mode == ST_PLAIN && e->act != ACT_GEGLU && !e->out_f32 && !e->res_f32 && (e->out || e->out_relu) &&
+                    e->ldo % 8 == 0 && al16(e->out) && al16(e->out_relu) && al16(e->res1) && al16(e->res2) && off_lvl != 5;
+    return ok ? 5 : 0;
+  }
   if (off || e->out_relu || e->res1 || e->res2 || e->split) return 0;
   if (e->act == ACT_GEGLU) {  // value * gelu(gate) pairs -> bf16 boxes of 32 outputs (64 accumulator columns)
     const bool ok = !conv && e->store_mode == ST_PLAIN && e->out && !e->out_f32 && !e->res_f32 && e->ldo % 8 == 0 &&
@@ -293,6 +300,7 @@ int vda_gemm_bf16(const void* A, int lda, const void* W, int ldw, int M, int N, 
   if (small_ks) bn = 256, two = true;
   p.n_tiles = (N + bn - 1) / bn;
   if (p.epi_tma == 4 && bn < 128) p.epi_tma = 0;  // a GEGLU box spans 64 accumulator columns of one column slice
+  if (p.epi_tma == 5 && N % 32) p.epi_tma = 0;    // whole 32-column boxes only
   p.stages = pick_stages(bn, two, epi, p.epi_tma);
   if (p.epi_tma == 1) {
     const char* rs = getenv("VDA_GEMM_RED_AS_STORE");  // knob for timing experiments only (drops the residual)
@@ -370,6 +378,7 @@ int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W,
   pick_tile(epi, Cout, p.m_tiles, &bn, &two);
   p.n_tiles = (Cout + bn - 1) / bn;
   p.epi_tma = pick_epi_tma(epi, true);
+  if (p.epi_tma == 5 && Cout % 32) p.epi_tma = 0;   // whole 32-column boxes only
   p.stages = pick_stages(bn, two, epi, p.epi_tma);
   // halo mode (gemm.cu): one halo patch per channel block + tap-shifted descriptors instead of nine separate
   // (tap, block) A tiles.  1-CTA kernel: few output channels (BN <= 64; a stage = patch + its 9 W tiles).
@@ -383,12 +392,13 @@ int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W,
       const bool staged = p.epi_tma || (epi->res_f32 && epi->store_mode == ST_PLAIN && epi->act != ACT_GEGLU);
       p.stages = staged ? 2 : max_halo;  // the epilogue's 48 KB of boxes / residual ring sit behind the ring
       const int ring = (bn <= 32 ? 8 * 20480 : 8 * 24576) > max_halo * halo_stage ? (bn <= 32 ? 8 * 20480 : 8 * 24576) : max_halo * halo_stage;
-      if (staged && p.stages * halo_stage + 48 * 1024 > ring) p.halo = 0, p.stages = pick_stages(bn, two, epi, p.epi_tma);
+      const int epi_need = p.epi_tma ? epi_box_area_bytes(p.epi_tma) : 48 * 1024;
+      if (staged && p.stages * halo_stage + epi_need > ring) p.halo = 0, p.stages = pick_stages(bn, two, epi, p.epi_tma);
     }
     const char* h2 = getenv("VDA_CONV_HALO2");  // A/B knob: 0 off, 1 BN = 128 only, 2 (default) BN = 128 and 256
     const int h2v = h2 ? atoi(h2) : 2;
     const bool res_staged = !p.epi_tma && epi->res_f32 && epi->store_mode == ST_PLAIN && epi->act != ACT_GEGLU;
-    if (two && C % 64 == 0 && (p.epi_tma == 2 || (p.epi_tma == 0 && !res_staged)) &&
+    if (two && C % 64 == 0 && (p.epi_tma == 2 || p.epi_tma == 5 || (p.epi_tma == 0 && !res_staged)) &&
         ((bn == 128 && h2v >= 1) || (bn == 256 && h2v >= 2))) {
       const int ring = bn >= 256 ? 6 * 32768 : 8 * 24576;            // Gemm2Cfg<BN>::kStages * kStageBytes
       const int w_bytes = (bn / 2) * 128;

@@ -276,6 +276,7 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
       long long* s_rowoff = reinterpret_cast<long long*>(s_epi + 4 * BN) + as * kBlockM;
       stage_row_offsets(p, m_t, et, s_rowoff);
       stage_bias_scale<BN>(p, n_t, et, s_bias, s_scale);
+      if (p.epi_tma == 5) coop_tile_begin<BN>(p, n_t, r, half, red_base, box_ctr, s_rowoff);
       if (tile + tile_step < tile_end)  // residual rows of the NEXT tile into L2: a whole tile of lead time
         epilogue_prefetch<BN>(p, (tile + tile_step) / p.n_tiles, (tile + tile_step) % p.n_tiles, r, half);
       mbar_wait(&tfull_bar[as], aphase);
@@ -291,13 +292,15 @@ __global__ void __launch_bounds__(kGemmThreads, 1) gemm_tc_kernel(const __grid_c
         epilogue_tile_box<BN, 3>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer, s_rowoff);
       else if (p.epi_tma == 4)
         epilogue_tile_box<BN, 4>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer);
+      else if (p.epi_tma == 5)
+        epilogue_tile_coop<BN>(p, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, s_rowoff);
       else
         epilogue_tile<BN>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, ts, rr, it);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty_bar[as]);
     }
-    if (p.epi_tma && red_issuer) bulk_wait_all();
+    if (p.epi_tma && p.epi_tma != 5 && red_issuer) bulk_wait_all();
   }
 
   tc_fence_before();
@@ -539,6 +542,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
       long long* s_rowoff = reinterpret_cast<long long*>(s_epi + 4 * BN) + as * kBlockM;
       stage_row_offsets(p, m_t, et, s_rowoff);
       stage_bias_scale<BN>(p, n_t, et, s_bias, s_scale, u.kb0 == 0);  // the bias rides with the first K range only
+      if (p.epi_tma == 5) coop_tile_begin<BN>(p, n_t, r, half, red_base, box_ctr, s_rowoff);
       if (tile + tile_step < tile_end)
         epilogue_prefetch<BN>(p, 2 * ((tile + tile_step) / p.n_tiles) + static_cast<int>(rank),
                               (tile + tile_step) % p.n_tiles, r, half);
@@ -555,13 +559,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
         epilogue_tile_box<BN, 3>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer, s_rowoff);
       else if (p.epi_tma == 4)
         epilogue_tile_box<BN, 4>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, red_issuer);
+      else if (p.epi_tma == 5)
+        epilogue_tile_coop<BN>(p, n_t, t_acc, r, half, s_bias, s_scale, red_base, box_ctr, s_rowoff);
       else
         epilogue_tile<BN>(p, m_t, n_t, t_acc, r, half, s_bias, s_scale, ts, rr, it);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(&tempty_bar[as], 0);
     }
-    if (p.epi_tma && red_issuer) bulk_wait_all();
+    if (p.epi_tma && p.epi_tma != 5 && red_issuer) bulk_wait_all();
   }
 
   // nobody may exit (or free TMEM) while the peer can still touch this CTA's smem, barriers or TMEM

@@ -227,10 +227,22 @@ struct EpiSlice {
 // Requests the fp32 residual lines this thread will read for the tile into L2 (no registers held).
 template <int BN>
 __device__ __forceinline__ void epilogue_prefetch(const GemmParams& p, int m_tile, int n_t, int r, int half) {
-  if (p.res_f32 == nullptr || p.store_mode != ST_PLAIN) return;
   constexpr int kPer = EpiSlice<BN>::kPer;
   const int cbeg = half * kPer;
   if (cbeg >= BN) return;
+  if (p.epi_tma == 5) {   // bf16 residual rows of the tile (cooperative boxes): 2 * kPer bytes per row and tensor
+    if (p.res1 == nullptr && p.res2 == nullptr) return;
+    const RowMap rm = map_row(p, m_tile, r);
+    const int col = n_t * BN + cbeg;
+    if (!rm.valid || col >= p.N) return;
+#pragma unroll
+    for (int i = 0; i < kPer; i += 64) {
+      if (p.res1) prefetch_l2(p.res1 + rm.row * p.ldo + col + i);
+      if (p.res2) prefetch_l2(p.res2 + rm.row * p.ldo + col + i);
+    }
+    return;
+  }
+  if (p.res_f32 == nullptr || p.store_mode != ST_PLAIN) return;
   const RowMap rm = map_row(p, m_tile, r);
   if (!rm.valid) return;
   const int col = n_t * BN + cbeg;
@@ -354,10 +366,12 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, uint32_t src_
 // Output element offset of every row of a tile for the scattered stores of MODE 3 (-1 = row not stored),
 // computed once per tile by the first 128 epilogue threads into a table double-buffered by tile parity.
 __device__ __forceinline__ void stage_row_offsets(const GemmParams& p, int m_tile, int et, long long* s_rowoff) {
-  if (p.epi_tma != 3 || et >= kBlockM) return;
+  if ((p.epi_tma != 3 && p.epi_tma != 5) || et >= kBlockM) return;
   const RowMap rm = map_row(p, m_tile, et);
   long long off = -1;
-  if (rm.valid) {
+  if (rm.valid && p.epi_tma == 5) {
+    off = rm.row * p.ldo;   // plain addressing (GEMM rows or conv pixels)
+  } else if (rm.valid) {
     // ST_CONVT: input pixel (n, ih, iw) -> output pixel (n, ih*s, iw*s); the tap (kh, kw) is added per box
     const int hw = p.ct_h * p.ct_w;
     const int m = static_cast<int>(rm.row);
@@ -515,6 +529,152 @@ __device__ __forceinline__ void epilogue_tile_box(const GemmParams& p, int m_til
       }
       bulk_commit();
       if (kRedBoxes != 2) bulk_wait_read_1();  // 3 boxes: the previous box of this slice has been read out of shared memory
+    }
+    ++box_ctr;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// MODE 5, "cooperative boxes": bf16 output with bf16 residuals and / or a ReLU'd second output
+// (out = acc + bias (+ res1 + res2), out_relu = relu(out): the ResidualConvUnit / FeatureFusion epilogues, util/blocks.py:78-91,
+// 146-160, and the motion module's proj_out + residual).  The element-wise path reads and writes those tensors with
+// thread = row, 32 different lines per warp access (conv 148x148 with two residuals: 887 us against 570-600 us without).
+// Here every tensor moves through 64-byte-row boxes in shared memory like MODE 3: the slice's 128 threads fetch the
+// residual boxes with cp.async, four lanes per 64-byte row run (8 lines per warp access), ONE BOX AHEAD (the first box of
+// a tile is requested by coop_tile_begin before the wait for the accumulator); a thread then adds its own row, writes the
+// result over the res1 box (ReLU'd copy over the res2 box) and the slice copies both out the same cooperative way.
+// Per slice: 2 slots x {res1 | out, res2 | out_relu} boxes of 8 KB.  Barrier A of box k (residuals landed) is also the
+// point where every thread has finished copying out box k-1, so slot k+1 (= slot k-1) may be refilled behind it.
+__device__ __forceinline__ void coop_res_issue(const GemmParams& p, const long long* s_rowoff, int col, uint32_t box_a,
+                                               uint32_t box_b, int r) {
+  if ((p.res1 || p.res2) && col < p.N) {
+    const uint32_t chunk = static_cast<uint32_t>(r) & 3;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t row = (static_cast<uint32_t>(r) >> 2) + 32 * i;
+      const long long ro = s_rowoff[row];
+      if (ro >= 0) {
+        const uint32_t dst = row * 64 + ((chunk ^ ((row >> 1) & 3)) << 4);
+        const long long src = ro + col + chunk * 8;
+        if (p.res1) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(box_a + dst), "l"(p.res1 + src) : "memory");
+        if (p.res2) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(box_b + dst), "l"(p.res2 + src) : "memory");
+      }
+    }
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+
+// Called by every epilogue thread at the top of a tile (row-offset table of the tile staged and visible).
+template <int BN>
+__device__ __forceinline__ void coop_tile_begin(const GemmParams& p, int n_t, int r, int half, uint32_t box_base, int box_ctr,
+                                                const long long* s_rowoff) {
+  constexpr int kPer = EpiSlice<BN>::kPer;
+  if (half * kPer >= BN) return;
+  const uint32_t s = static_cast<uint32_t>(box_ctr) & 1;
+  coop_res_issue(p, s_rowoff, n_t * BN + half * kPer, box_base + s * kRedBoxBytes, box_base + (2 + s) * kRedBoxBytes, r);
+}
+
+__device__ __forceinline__ void add_bf16x8_smem(uint32_t addr, float* v) {
+  uint32_t w[4];
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(addr));
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[i]));
+    v[2 * i] += f.x, v[2 * i + 1] += f.y;
+  }
+}
+
+template <int BN>
+__device__ __forceinline__ void epilogue_tile_coop(const GemmParams& p, int n_t, uint32_t t_acc, int r, int half,
+                                                   const float* s_bias, const float* s_scale, uint32_t box_base, int& box_ctr,
+                                                   const long long* s_rowoff) {
+  constexpr int kPer = EpiSlice<BN>::kPer;
+  const int cbeg = half * kPer;
+  if (cbeg >= BN) return;
+  uint32_t raw[32];
+  __syncwarp();
+  tmem_ld32(t_acc + cbeg, raw);
+  const uint32_t sw = (static_cast<uint32_t>(r) >> 1) & 3;
+#pragma unroll 1
+  for (int c0 = cbeg; c0 < cbeg + kPer; c0 += 32) {
+    const int col = n_t * BN + c0;
+    const uint32_t s = static_cast<uint32_t>(box_ctr) & 1;
+    const uint32_t box_a = box_base + s * kRedBoxBytes, box_b = box_base + (2 + s) * kRedBoxBytes;
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    named_bar_sync(2 + half, 128);   // A: residual boxes of this box have landed; box k-1 has been copied out by everyone
+    if (c0 + 32 < cbeg + kPer)
+      coop_res_issue(p, s_rowoff, col + 32, box_base + (s ^ 1) * kRedBoxBytes, box_base + (2 + (s ^ 1)) * kRedBoxBytes, r);
+    tmem_ld_wait();
+    float v[32];
+#pragma unroll
+    for (int g = 0; g < 2; ++g) {
+      float b[16];
+      lds_f32x16(s_bias + c0 + 16 * g, b);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) v[16 * g + i] = __uint_as_float(raw[16 * g + i]) + b[i];
+      if (p.act == ACT_GELU) {
+#pragma unroll
+        for (int i = 0; i < 16; i += 2) gelu_fast2(v[16 * g + i], v[16 * g + i + 1]);
+      } else if (p.act == ACT_RELU) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[16 * g + i] = fmaxf(v[16 * g + i], 0.f);
+      }
+      if (p.scale) {
+        float sc[16];
+        lds_f32x16(s_scale + c0 + 16 * g, sc);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[16 * g + i] *= sc[i];
+      }
+    }
+    if (c0 + 32 < cbeg + kPer) {   // raw is dead: the next accumulator chunk travels behind the rest of this box
+      __syncwarp();
+      tmem_ld32(t_acc + c0 + 32, raw);
+    }
+    const uint32_t row_a = box_a + static_cast<uint32_t>(r) * 64, row_b = box_b + static_cast<uint32_t>(r) * 64;
+    if (col < p.N) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const uint32_t o = (static_cast<uint32_t>(c) ^ sw) << 4;
+        if (p.res1) add_bf16x8_smem(row_a + o, v + 8 * c);
+        if (p.res2) add_bf16x8_smem(row_b + o, v + 8 * c);
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const uint32_t o = (static_cast<uint32_t>(c) ^ sw) << 4;
+      uint32_t w[4], wr[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float a0 = v[8 * c + 2 * i], a1 = v[8 * c + 2 * i + 1];
+        __nv_bfloat162 h = __floats2bfloat162_rn(a0, a1);
+        w[i] = *reinterpret_cast<uint32_t*>(&h);
+        h = __floats2bfloat162_rn(fmaxf(a0, 0.f), fmaxf(a1, 0.f));
+        wr[i] = *reinterpret_cast<uint32_t*>(&h);
+      }
+      asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row_a + o), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
+      if (p.out_relu)
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row_b + o), "r"(wr[0]), "r"(wr[1]), "r"(wr[2]), "r"(wr[3]) : "memory");
+    }
+    named_bar_sync(2 + half, 128);   // B: the result boxes are complete
+    if (col < p.N) {
+      const uint32_t chunk = static_cast<uint32_t>(r) & 3;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t row = (static_cast<uint32_t>(r) >> 2) + 32 * i;
+        const long long ro = s_rowoff[row];
+        const uint32_t src = row * 64 + ((chunk ^ ((row >> 1) & 3)) << 4);
+        if (ro >= 0) {
+          uint4 t;
+          if (p.out) {
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(t.x), "=r"(t.y), "=r"(t.z), "=r"(t.w) : "r"(box_a + src));
+            *reinterpret_cast<uint4*>(p.out + ro + col + chunk * 8) = t;
+          }
+          if (p.out_relu) {
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(t.x), "=r"(t.y), "=r"(t.z), "=r"(t.w) : "r"(box_b + src));
+            *reinterpret_cast<uint4*>(p.out_relu + ro + col + chunk * 8) = t;
+          }
+        }
+      }
     }
     ++box_ctr;
   }

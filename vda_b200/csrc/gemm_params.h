@@ -17,7 +17,8 @@ namespace vda {
 #else
 #define VDA_HD
 #endif
-VDA_HD constexpr int epi_boxes(int epi_tma) { return epi_tma == 1 ? 2 : 3; }
+// cooperative flavour (5: bf16 residuals / ReLU'd second output): 2 slots x {res1 | out, res2 | out_relu} per slice.
+VDA_HD constexpr int epi_boxes(int epi_tma) { return epi_tma == 1 ? 2 : (epi_tma == 5 ? 4 : 3); }
 VDA_HD constexpr int epi_box_area_bytes(int epi_tma) { return 2 * epi_boxes(epi_tma) * 8 * 1024; }
 
 // A-operand addressing
@@ -37,7 +38,7 @@ struct alignas(64) GemmParams {
   int halo;         // A_CONV3X3 only: one halo patch per channel block, 9 tap-shifted descriptors (gemm.cu)
   CUtensorMap tmB;  // 2D [N,K] bf16, box 64 x BLOCK_N
   CUtensorMap tmD;  // epi_tma: 2D [N,M] f32 view of out_f32, box 16 x 128 rows, SWIZZLE_64B
-  int epi_tma;      // 1 = in-place fp32 residual update done as TMA reduce-add (gemm_epilogue.cuh)
+  int epi_tma;      // epilogue flavour (gemm_epilogue.cuh): 1 fp32 reduce-add, 2 bf16 box store, 3 ConvT scatter, 4 GEGLU, 5 cooperative boxes with bf16 residuals
   int M, N, K;      // GEMM extents (conv: M = images*H*W, K = 9*C)
   int num_k_blocks;
   int m_tiles, n_tiles;
