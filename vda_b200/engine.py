@@ -158,6 +158,7 @@ class Engine:
             self.w = Packed(model, self.device, split=self.fp32)
         self.ws = {}
         self.graphs = {}
+        self._capture_stream = None
         self.launches_per_run = {}
         self.use_graph = True
         self._warm = set()
@@ -425,7 +426,11 @@ class Engine:
             if g is None:
                 torch.cuda.current_stream().synchronize()
                 graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(graph):
+                # torch.cuda.graph keeps ONE default capture stream per process (created on the device of the first
+                # capture); a model on a second device in the same process needs a capture stream of its own device
+                if self._capture_stream is None:
+                    self._capture_stream = torch.cuda.Stream(device=self.device)
+                with torch.cuda.graph(graph, stream=self._capture_stream):
                     out = self._after_patch(T, H, W, ws, stream_ctx)
                 g = self.graphs[gkey] = (graph, out)
             g[0].replay()
