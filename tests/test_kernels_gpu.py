@@ -372,3 +372,46 @@ def test_util_shims_match_reference_golden(L):
     ss = torch.zeros(2, device="cuda")
     L.lsq_solve(sums, ss, reset=True)
     assert sums.abs().sum().item() == 0.0
+
+
+@pytest.mark.parametrize("hw,C,Tk,f32", [(1369, 1024, 32, False), (361, 1024, 32, False), (5476, 256, 32, False), (35, 64, 32, False),
+                                        (35, 192, 7, False), (130, 384, 1, False), (77, 768, 20, False), (50, 128, 32, True),
+                                        (361, 1024, 32, True), (35, 48 * 8, 13, True)])
+def test_temporal_attn_stream(L, hw, C, Tk, f32):
+    """Streaming temporal attention (video_depth_stream.py:134-153, motion_module.py:252-266): the new frame attends over
+    Tk list positions whose PE-free K / V projections sit in slot-addressed caches; checked against torch, incl. the
+    cache insert of the new frame."""
+    heads, hd, cap = 8, C // 8, 44
+    dt = torch.float32 if f32 else torch.bfloat16
+    qkv = _rand(hw, 3 * C, seed=1).to(dt)
+    kc, vc = _rand(cap, hw, C, seed=2).to(dt), _rand(cap, hw, C, seed=3).to(dt)
+    kc0, vc0 = kc.clone(), vc.clone()
+    pe_q, pe_k, pe_v = _rand(32, C, scale=0.3, seed=4), _rand(32, C, scale=0.3, seed=5), _rand(32, C, scale=0.3, seed=6)
+    g = torch.Generator().manual_seed(7)
+    slots = torch.randperm(cap, generator=g)[:32].to(torch.int32).cuda()
+    q, kn, vn = qkv[:, :C].float(), qkv[:, C:2 * C].float(), qkv[:, 2 * C:].float()
+    sl = slots[:Tk].long()
+    K = kc0[sl].float().clone()
+    V = vc0[sl].float().clone()
+    K[Tk - 1], V[Tk - 1] = kn, vn
+    qq = (q + pe_q[Tk - 1]).view(hw, heads, hd)
+    KK = (K + pe_k[:Tk, None]).view(Tk, hw, heads, hd)
+    VV = (V + pe_v[:Tk, None]).view(Tk, hw, heads, hd)
+    s = torch.einsum("nhd,tnhd->nht", qq, KK) * hd ** -0.5
+    want = torch.einsum("nht,tnhd->nhd", s.softmax(-1), VV).reshape(hw, C)
+    if f32:
+        out = torch.full((hw, 3 * C), float("nan"), device="cuda", dtype=torch.bfloat16)
+        L.temporal_attn_stream_f32(qkv, qkv[:, C:], qkv[:, 2 * C:], 3 * C, kc, vc, slots, pe_q, pe_k, pe_v, out, C, hw, heads, hd, Tk)
+        got = out[:, :C].float() + out[:, C:2 * C].float()
+        assert torch.equal(out[:, :C], out[:, 2 * C:])
+        _close(got, want, 1e-4)
+    else:
+        out = torch.full((hw, C), float("nan"), device="cuda", dtype=torch.bfloat16)
+        L.temporal_attn_stream(qkv, qkv[:, C:], qkv[:, 2 * C:], 3 * C, kc, vc, slots, pe_q, pe_k, pe_v, out, C, hw, heads, hd, Tk)
+        _close(out, want, 1e-2)
+    torch.cuda.synchronize()
+    new = int(slots[Tk - 1])
+    assert torch.equal(kc[new], qkv[:, C:2 * C]) and torch.equal(vc[new], qkv[:, 2 * C:])
+    keep = torch.ones(cap, dtype=torch.bool)
+    keep[new] = False
+    assert torch.equal(kc[keep], kc0[keep]) and torch.equal(vc[keep], vc0[keep])

@@ -454,6 +454,250 @@ __global__ void __launch_bounds__(kTWarps * 32) temporal_attn_stream_kernel(cons
   }
 }
 
+
+// Second generation of the streaming kernel.  The first one (above) gave lane p the K / V rows of cache position p: 32
+// lanes reading 16-byte pieces of 32 different cache slots plus three scalar PE loads per element -- LSU-bound, 490 us per
+// launch for the 37 x 37, C = 1024 module where the 180 MB of cache it reads are 28 us of HBM time (ncu launch list of
+// a streamed vitl frame: 8 launches = 2.3 of the frame's 6 ms).  Here a thread owns one 8-channel chunk of a token row,
+// so every cache row is read by consecutive threads as one coalesced run:
+//   phase 1  partial dot products of the chunk with the Tk cached K rows (+ projected PE) -> shared memory;
+//   phase 2  one warp per (token, head): lane p sums the head's partials of position p, softmax over the positions;
+//   phase 3  weighted sum of the Tk cached V rows (+ projected PE) with the same coalesced mapping.
+// A thread serves TB tokens with the PE chunk of a position held in registers (the PE tables would otherwise be twice
+// the cache traffic).  Block = 128 threads = `groups` token groups of C / 8 threads.
+constexpr int kTS2Threads = 128;
+template <bool F32>
+__device__ __forceinline__ void ldf8(const float* src, float (&o)[8]) {
+  const float4 a = *reinterpret_cast<const float4*>(src), b = *reinterpret_cast<const float4*>(src + 4);
+  o[0] = a.x, o[1] = a.y, o[2] = a.z, o[3] = a.w, o[4] = b.x, o[5] = b.y, o[6] = b.z, o[7] = b.w;
+}
+
+// raw 8-element row piece (16 B of bf16 or 32 B of fp32), read-only path; converted after a whole batch has been requested
+template <bool F32>
+struct Raw8 {
+  uint4 a, b;
+};
+template <bool F32>
+__device__ __forceinline__ Raw8<F32> ldraw8(const void* base, long long off) {
+  Raw8<F32> r;
+  if (F32) {
+    const uint4* s = reinterpret_cast<const uint4*>(static_cast<const float*>(base) + off);
+    r.a = __ldg(s), r.b = __ldg(s + 1);
+  } else {
+    r.a = __ldg(reinterpret_cast<const uint4*>(static_cast<const bf16*>(base) + off));
+    r.b = make_uint4(0, 0, 0, 0);
+  }
+  return r;
+}
+template <bool F32>
+__device__ __forceinline__ void cvt8(const Raw8<F32>& r, float (&o)[8]) {
+  if (F32) {
+    o[0] = __uint_as_float(r.a.x), o[1] = __uint_as_float(r.a.y), o[2] = __uint_as_float(r.a.z), o[3] = __uint_as_float(r.a.w);
+    o[4] = __uint_as_float(r.b.x), o[5] = __uint_as_float(r.b.y), o[6] = __uint_as_float(r.b.z), o[7] = __uint_as_float(r.b.w);
+  } else {
+    const uint32_t w[4] = {r.a.x, r.a.y, r.a.z, r.a.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 f = bf2(w[i]);
+      o[2 * i] = f.x, o[2 * i + 1] = f.y;
+    }
+  }
+}
+
+// The cache rows of JB positions x TB tokens are requested back to back (nothing in the loop stores, so the loads do
+// not wait for each other: the first version interleaved the new frame's cache insert with the loop and ran at one
+// dependent round trip per position, ~95 us per launch whatever the size); the new frame (position Tk - 1) is handled
+// outside the loops from knew / vnew and written to its slot there.
+template <bool F32, int TB>
+__global__ void __launch_bounds__(kTS2Threads) temporal_attn_stream2_kernel(const TemporalStreamParams p, int groups) {
+  pdl_sync();  // launched with programmatic stream serialization (common.cuh)
+  extern __shared__ __align__(16) uint8_t tsm[];
+  constexpr int JB = F32 ? 4 : 8;
+  const int lpt = p.C >> 3;            // threads per token row
+  const int used = groups * lpt;
+  const int pitch = used + 1;          // row pitch of `part`: phase 2 reads one row per lane (no bank conflicts)
+  const int hpl = p.hd >> 3;           // threads (8-channel chunks) per head
+  float* part = reinterpret_cast<float*>(tsm);   // [TB][32][pitch]
+  float* wgt = part + TB * 32 * pitch;           // [groups * TB * heads][32]
+  int* s_slot = reinterpret_cast<int*>(wgt + groups * TB * p.heads * 32);   // [32]
+  const int t = threadIdx.x;
+  const bool worker = t < used;
+  const int g = worker ? t / lpt : 0;
+  const int ch = worker ? (t - g * lpt) * 8 : 0;
+  const int head = ch / p.hd;
+  const int tok0 = (blockIdx.x * groups + g) * TB;
+  const int Tk = p.Tk, Tc = p.Tk - 1;   // Tc cached positions + the new frame
+  if (t < 32) s_slot[t] = t < Tk ? __ldg(p.slots + t) : 0;
+  __syncthreads();
+  const long long new_row0 = static_cast<long long>(s_slot[Tc]) * p.hw;
+
+  if (worker) {
+    float qv[TB][8];
+    {
+      float pq[8];
+      ldf8<F32>(p.pe_q + static_cast<long long>(Tc) * p.C + ch, pq);
+#pragma unroll
+      for (int tb = 0; tb < TB; ++tb) {
+        const int tok = tok0 + tb;
+        if (tok < p.hw) {
+          ld8<F32>(p.q, static_cast<long long>(tok) * p.ldn + ch, qv[tb]);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) qv[tb][i] += pq[i];
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) qv[tb][i] = 0.f;
+        }
+      }
+    }
+    for (int j0 = 0; j0 < Tc; j0 += JB) {
+      Raw8<F32> raw[JB][TB];
+#pragma unroll
+      for (int jj = 0; jj < JB; ++jj) {
+        const int j = j0 + jj < Tc ? j0 + jj : Tc - 1;   // clamp: the surplus loads repeat the last row
+        const long long row0 = static_cast<long long>(s_slot[j]) * p.hw;
+#pragma unroll
+        for (int tb = 0; tb < TB; ++tb) {
+          const int tok = tok0 + tb < p.hw ? tok0 + tb : p.hw - 1;
+          raw[jj][tb] = ldraw8<F32>(p.kcache, (row0 + tok) * p.C + ch);
+        }
+      }
+#pragma unroll
+      for (int jj = 0; jj < JB; ++jj) {
+        const int j = j0 + jj;
+        if (j < Tc) {
+          float pk[8];
+          ldf8<F32>(p.pe_k + static_cast<long long>(j) * p.C + ch, pk);
+#pragma unroll
+          for (int tb = 0; tb < TB; ++tb) {
+            float kf[8], dot = 0.f;
+            cvt8<F32>(raw[jj][tb], kf);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) dot = fmaf(qv[tb][i], kf[i] + pk[i], dot);
+            part[(tb * 32 + j) * pitch + t] = dot;
+          }
+        }
+      }
+    }
+    {   // the new frame: position Tc, from knew, inserted into its cache slot
+      float pk[8];
+      ldf8<F32>(p.pe_k + static_cast<long long>(Tc) * p.C + ch, pk);
+#pragma unroll
+      for (int tb = 0; tb < TB; ++tb) {
+        const int tok = tok0 + tb;
+        float dot = 0.f;
+        if (tok < p.hw) {
+          float kf[8];
+          ld8<F32>(p.knew, static_cast<long long>(tok) * p.ldn + ch, kf);
+          st8<F32>(p.kcache, (new_row0 + tok) * p.C + ch, kf);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) dot = fmaf(qv[tb][i], kf[i] + pk[i], dot);
+        }
+        part[(tb * 32 + Tc) * pitch + t] = dot;
+      }
+    }
+  }
+  __syncthreads();
+  {
+    const int warp = t >> 5, lane = t & 31;
+    const int pairs = groups * TB * p.heads;
+    for (int pr = warp; pr < pairs; pr += kTS2Threads / 32) {
+      const int g2 = pr / (TB * p.heads);
+      const int rem = pr - g2 * TB * p.heads;
+      const int tb = rem / p.heads, h = rem - tb * p.heads;
+      float s = -INFINITY;
+      if (lane < Tk) {
+        const float* src = part + (tb * 32 + lane) * pitch + g2 * lpt + h * hpl;
+        float a = 0.f;
+        for (int i = 0; i < hpl; ++i) a += src[i];
+        s = a * p.scale;
+      }
+      float m = s;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+      const float e = lane < Tk ? (F32 ? expf(s - m) : __expf(s - m)) : 0.f;
+      float l = e;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
+      wgt[pr * 32 + lane] = e / l;
+    }
+  }
+  __syncthreads();
+  if (!worker) return;
+  float acc[TB][8];
+#pragma unroll
+  for (int tb = 0; tb < TB; ++tb)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[tb][i] = 0.f;
+  const float* wrow = wgt + (g * TB * p.heads + head) * 32;   // + tb * heads * 32 + j
+  for (int j0 = 0; j0 < Tc; j0 += JB) {
+    Raw8<F32> raw[JB][TB];
+#pragma unroll
+    for (int jj = 0; jj < JB; ++jj) {
+      const int j = j0 + jj < Tc ? j0 + jj : Tc - 1;
+      const long long row0 = static_cast<long long>(s_slot[j]) * p.hw;
+#pragma unroll
+      for (int tb = 0; tb < TB; ++tb) {
+        const int tok = tok0 + tb < p.hw ? tok0 + tb : p.hw - 1;
+        raw[jj][tb] = ldraw8<F32>(p.vcache, (row0 + tok) * p.C + ch);
+      }
+    }
+#pragma unroll
+    for (int jj = 0; jj < JB; ++jj) {
+      const int j = j0 + jj;
+      if (j < Tc) {
+        float pv[8];
+        ldf8<F32>(p.pe_v + static_cast<long long>(j) * p.C + ch, pv);
+#pragma unroll
+        for (int tb = 0; tb < TB; ++tb) {
+          float vf[8];
+          cvt8<F32>(raw[jj][tb], vf);
+          const float w = wrow[tb * p.heads * 32 + j];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) acc[tb][i] = fmaf(w, vf[i] + pv[i], acc[tb][i]);
+        }
+      }
+    }
+  }
+  {
+    float pv[8];
+    ldf8<F32>(p.pe_v + static_cast<long long>(Tc) * p.C + ch, pv);
+#pragma unroll
+    for (int tb = 0; tb < TB; ++tb) {
+      const int tok = tok0 + tb;
+      if (tok < p.hw) {
+        float vf[8];
+        ld8<F32>(p.vnew, static_cast<long long>(tok) * p.ldn + ch, vf);
+        st8<F32>(p.vcache, (new_row0 + tok) * p.C + ch, vf);
+        const float w = wrow[tb * p.heads * 32 + Tc];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[tb][i] = fmaf(w, vf[i] + pv[i], acc[tb][i]);
+      }
+    }
+  }
+#pragma unroll
+  for (int tb = 0; tb < TB; ++tb) {
+    const int tok = tok0 + tb;
+    if (tok >= p.hw) continue;
+    bf16* orow = p.out + static_cast<long long>(tok) * p.ldo + ch;
+    uint32_t hi[4], lo[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const __nv_bfloat162 h2 = __floats2bfloat162_rn(acc[tb][2 * i], acc[tb][2 * i + 1]);
+      hi[i] = *reinterpret_cast<const uint32_t*>(&h2);
+      if (F32) {
+        const float2 f = __bfloat1622float2(h2);
+        const __nv_bfloat162 l2 = __floats2bfloat162_rn(acc[tb][2 * i] - f.x, acc[tb][2 * i + 1] - f.y);
+        lo[i] = *reinterpret_cast<const uint32_t*>(&l2);
+      }
+    }
+    *reinterpret_cast<uint4*>(orow) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    if (F32) {
+      *reinterpret_cast<uint4*>(orow + p.split) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+      *reinterpret_cast<uint4*>(orow + 2 * p.split) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    }
+  }
+}
+
 }  // namespace vda
 
 using namespace vda;
@@ -470,6 +714,39 @@ static int launch_temporal_stream(bool f32, const void* q, const void* knew, con
   p.out = static_cast<bf16*>(out);
   p.ldn = ldn, p.ldo = ldo, p.hw = hw, p.heads = heads, p.hd = head_dim, p.C = heads * head_dim, p.Tk = Tk, p.split = split;
   p.scale = 1.0f / sqrtf(static_cast<float>(head_dim));
+  const char* ev = getenv("VDA_TSTREAM");   // A/B knob: 1 = first-generation kernel (one warp per (token, head))
+  const int C = heads * head_dim;
+  if (!(ev && atoi(ev) == 1) && C % 8 == 0 && C / 8 <= kTS2Threads && ldo % 8 == 0 && split % 8 == 0) {
+    const int lpt = C / 8;
+    int groups = kTS2Threads / lpt;
+    if (groups > 8) groups = 8;
+    const char* etb = getenv("VDA_TSTREAM_TB");   // A/B knob: tokens per thread (2 or 4)
+    const int tb = etb && atoi(etb) == 4 ? 4 : 2;   // measured: 2 is faster for every motion-module shape (profiles/r02d_tstream_shapes.log)
+    const int used = groups * lpt;
+    const int smem2 = (tb * 32 * (used + 1) + groups * tb * heads * 32 + 32) * 4;
+    static DeviceOnce once2;
+    int& conf2 = once2.slot();
+    if (!conf2) {
+      const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+      const int mx = (4 * 32 * (kTS2Threads + 1) + 8 * 4 * 16 * 32 + 32) * 4;
+      int rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream2_kernel<false, 2>, attr, mx), "temporal stream2 smem");
+      if (!rc) rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream2_kernel<false, 4>, attr, mx), "temporal stream2 smem");
+      if (!rc) rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream2_kernel<true, 2>, attr, mx), "temporal stream2 smem");
+      if (!rc) rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream2_kernel<true, 4>, attr, mx), "temporal stream2 smem");
+      if (rc) return rc;
+      conf2 = 1;
+    }
+    const dim3 grid2((hw + groups * tb - 1) / (groups * tb));
+    const cudaStream_t st2 = static_cast<cudaStream_t>(stream);
+    cudaError_t le;
+    if (f32)
+      le = tb == 4 ? launch_pdl(temporal_attn_stream2_kernel<true, 4>, grid2, dim3(kTS2Threads), smem2, st2, p, groups)
+                   : launch_pdl(temporal_attn_stream2_kernel<true, 2>, grid2, dim3(kTS2Threads), smem2, st2, p, groups);
+    else
+      le = tb == 4 ? launch_pdl(temporal_attn_stream2_kernel<false, 4>, grid2, dim3(kTS2Threads), smem2, st2, p, groups)
+                   : launch_pdl(temporal_attn_stream2_kernel<false, 2>, grid2, dim3(kTS2Threads), smem2, st2, p, groups);
+    return check_cuda(le, "temporal_attn_stream2 launch");
+  }
   const int smem = kTWarps * 32 * (head_dim + 1) * 4;
   static DeviceOnce once;
   int& configured = once.slot();
