@@ -135,19 +135,20 @@ int vda_temporal_attn(const void* q, int ldq, const void* k, int ldk, const void
                       int hw, int heads, int head_dim, int Tq, int Tk, void* stream);
 
 /* Streaming temporal attention (video_depth_stream.py:134-153, motion_module.py:252-266): the new
- * frame (Tq = 1) attends over Tk <= 32 list positions.  kcache/vcache: [cap, hw, C] bf16 PE-free
- * projections of cached frames; slots: DEVICE int[Tk], cache slot of each list position, the last
- * entry being the slot this call stores knew/vnew into; pe_q/pe_k/pe_v: f32 [32, C] positional
- * table projected through W_q/W_k/W_v (K(n+pe) = Kn + K pe).  q/knew/vnew: [hw, ldn], out: [hw, ldo]. */
+ * frame (Tq = 1) attends over Tk <= 32 list positions.  kcache/vcache: [hw, cap, C] bf16 PE-free
+ * projections of cached frames (the cap slots of one token are adjacent: coalesced, page-local reads);
+ * slots: DEVICE int[Tk], cache slot of each list position, the last entry being the slot this call stores
+ * knew/vnew into; pe_q/pe_k/pe_v: f32 [32, C] positional table projected through W_q/W_k/W_v
+ * (K(n+pe) = Kn + K pe).  q/knew/vnew: [hw, ldn], out: [hw, ldo].  C = heads*head_dim <= 1024, head_dim % 8 == 0. */
 int vda_temporal_attn_stream(const void* q, const void* knew, const void* vnew, int ldn, void* kcache, void* vcache,
                              const int* slots, const float* pe_q, const float* pe_k, const float* pe_v, void* out,
-                             int ldo, int hw, int heads, int head_dim, int Tk, void* stream);
+                             int ldo, int hw, int heads, int head_dim, int Tk, int cap, void* stream);
 /* The same for the FP32-accuracy mode (infer_video_depth_one(..., fp32=True), video_depth_stream.py:77):
  * q/knew/vnew and the caches are f32, out is a split tensor (vda_epilogue::split) with parts `split` apart. */
 int vda_temporal_attn_stream_f32(const float* q, const float* knew, const float* vnew, int ldn, float* kcache,
                                  float* vcache, const int* slots, const float* pe_q, const float* pe_k,
                                  const float* pe_v, void* out, int ldo, int split, int hw, int heads, int head_dim,
-                                 int Tk, void* stream);
+                                 int Tk, int cap, void* stream);
 
 /* Fused depth tail (dpt_temporal.py:116-123, dpt.py:117-124): bilinear(align_corners=True) of the NHWC bf16 map
  * x [n,h,w,ldx>=C] to (H,W), 3x3 conv C->32 (w3 bf16 [32, 9*C], k=(kh,kw,c); b3) + ReLU, 1x1 conv 32->1 (w1, b1) + ReLU

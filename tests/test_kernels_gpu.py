@@ -384,15 +384,15 @@ def test_temporal_attn_stream(L, hw, C, Tk, f32):
     heads, hd, cap = 8, C // 8, 44
     dt = torch.float32 if f32 else torch.bfloat16
     qkv = _rand(hw, 3 * C, seed=1).to(dt)
-    kc, vc = _rand(cap, hw, C, seed=2).to(dt), _rand(cap, hw, C, seed=3).to(dt)
+    kc, vc = _rand(hw, cap, C, seed=2).to(dt), _rand(hw, cap, C, seed=3).to(dt)   # [hw, cap, C]
     kc0, vc0 = kc.clone(), vc.clone()
     pe_q, pe_k, pe_v = _rand(32, C, scale=0.3, seed=4), _rand(32, C, scale=0.3, seed=5), _rand(32, C, scale=0.3, seed=6)
     g = torch.Generator().manual_seed(7)
     slots = torch.randperm(cap, generator=g)[:32].to(torch.int32).cuda()
     q, kn, vn = qkv[:, :C].float(), qkv[:, C:2 * C].float(), qkv[:, 2 * C:].float()
     sl = slots[:Tk].long()
-    K = kc0[sl].float().clone()
-    V = vc0[sl].float().clone()
+    K = kc0[:, sl].float().transpose(0, 1).clone()
+    V = vc0[:, sl].float().transpose(0, 1).clone()
     K[Tk - 1], V[Tk - 1] = kn, vn
     qq = (q + pe_q[Tk - 1]).view(hw, heads, hd)
     KK = (K + pe_k[:Tk, None]).view(Tk, hw, heads, hd)
@@ -411,7 +411,7 @@ def test_temporal_attn_stream(L, hw, C, Tk, f32):
         _close(out, want, 1e-2)
     torch.cuda.synchronize()
     new = int(slots[Tk - 1])
-    assert torch.equal(kc[new], qkv[:, C:2 * C]) and torch.equal(vc[new], qkv[:, 2 * C:])
+    assert torch.equal(kc[:, new], qkv[:, C:2 * C]) and torch.equal(vc[:, new], qkv[:, 2 * C:])
     keep = torch.ones(cap, dtype=torch.bool)
     keep[new] = False
-    assert torch.equal(kc[keep], kc0[keep]) and torch.equal(vc[keep], vc0[keep])
+    assert torch.equal(kc[:, keep], kc0[:, keep]) and torch.equal(vc[:, keep], vc0[:, keep])

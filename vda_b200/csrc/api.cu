@@ -104,7 +104,10 @@ static void pick_tile(const vda_epilogue* e, int N, int m_tiles, int* bn_out, bo
       const int nt = (N + bn - 1) / bn;
       const bool forced = e->cta_pair == 2;
       if (!forced && (nt * bn - n16) * 8 > nt * bn) continue;
-      if (!forced && static_cast<long long>(m2) * nt < num_sms() / 2) continue;
+      // at least (nearly) one full wave of pair tiles: 72 tiles on 74 pairs (streaming qkv, M = 1370, N = 3072) is one
+      // wave of 256-wide tiles instead of two waves of 128-wide ones.  VDA_GEMM_WAVE_FRAC8 = 8 restores "one full wave".
+      static const int frac8 = [] { const char* e = getenv("VDA_GEMM_WAVE_FRAC8"); return e ? atoi(e) : 7; }();
+      if (!forced && static_cast<long long>(m2) * nt * 8 < static_cast<long long>(num_sms() / 2) * frac8) continue;
       *bn_out = bn, *two_out = true;
       return;
     }

@@ -330,19 +330,20 @@ static int launch_temporal_mma(const TemporalParams& p, cudaStream_t stream) {
 // the current list*, which shifts; projections are linear, so we cache the PE-free projections
 // k_c = n W_k^T, v_c = n W_v^T per frame and add the projected PE rows (pe_k[p] = PE[p] W_k^T, ...)
 // at read time.  `slots[p]` names the cache slot of list position p; slots[Tk-1] is where the new
-// frame's k_c / v_c are stored by this kernel.  One warp per (token, head); lane p owns position p.
+// frame's k_c / v_c are stored by this kernel.  Cache layout [hw, cap, C]: the rows of one token's cached frames are
+// adjacent (one DRAM page / TLB entry per token instead of one per position).
 struct TemporalStreamParams {
   const void* q;     // [hw, ldn] new frame, PE-free projection (bf16, or f32 in the FP32-accuracy mode)
   const void* knew;  // [hw, ldn]
   const void* vnew;
-  void* kcache;      // [cap, hw, C], same element type as q
+  void* kcache;      // [hw, cap, C], same element type as q
   void* vcache;
   const int* slots;  // device, Tk entries
   const float* pe_q; // [32, C] projected PE tables (fp32)
   const float* pe_k;
   const float* pe_v;
   bf16* out;         // [hw, ldo]; F32: split tensor, parts `split` apart
-  int ldn, ldo, hw, heads, hd, C, Tk, split;
+  int ldn, ldo, hw, heads, hd, C, Tk, split, cap;
   float scale;
 };
 
@@ -380,82 +381,7 @@ __device__ __forceinline__ void st8(void* base, long long off, const float (&v)[
   }
 }
 
-template <bool F32>
-__global__ void __launch_bounds__(kTWarps * 32) temporal_attn_stream_kernel(const TemporalStreamParams p) {
-  pdl_sync();  // launched with programmatic stream serialization (common.cuh)
-  extern __shared__ __align__(16) uint8_t tsm[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int unit = blockIdx.x * kTWarps + warp;
-  if (unit >= p.hw * p.heads) return;
-  const int d = unit / p.heads, head = unit - d * p.heads;
-  const int hd = p.hd, chunks = hd >> 3;
-  float* sW = reinterpret_cast<float*>(tsm) + warp * 32 * (hd + 1);  // [32][hd+1] weighted V rows
-  const int pos = lane;
-  const bool active = pos < p.Tk;
-  const bool is_new = pos == p.Tk - 1;
-  const int slot = active ? p.slots[pos] : 0;
-  const long long crow = (static_cast<long long>(slot) * p.hw + d) * p.C + head * hd;
-  const long long nrow = static_cast<long long>(d) * p.ldn + head * hd;
-  const float* peq = p.pe_q + static_cast<long long>(p.Tk - 1) * p.C + head * hd;
-  const float* pek = p.pe_k + static_cast<long long>(pos) * p.C + head * hd;
-  const float* pev = p.pe_v + static_cast<long long>(pos) * p.C + head * hd;
-  float s = 0.f;
-  if (active) {
-    for (int c = 0; c < chunks; ++c) {
-      float qf[8], kf[8];
-      ld8<F32>(p.q, nrow + c * 8, qf);
-      if (is_new) {
-        ld8<F32>(p.knew, nrow + c * 8, kf);
-        st8<F32>(p.kcache, crow + c * 8, kf);
-      } else {
-        ld8<F32>(p.kcache, crow + c * 8, kf);
-      }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) s = fmaf(qf[i] + peq[c * 8 + i], kf[i] + pek[c * 8 + i], s);
-    }
-  }
-  s = active ? s * p.scale : -INFINITY;
-  float m = s;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-  float e = active ? (F32 ? expf(s - m) : __expf(s - m)) : 0.f;
-  float l = e;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
-  const float w = e / l;
-  float* mine = sW + lane * (hd + 1);
-  if (active) {
-    for (int c = 0; c < chunks; ++c) {
-      float vf[8];
-      if (is_new) {
-        ld8<F32>(p.vnew, nrow + c * 8, vf);
-        st8<F32>(p.vcache, crow + c * 8, vf);
-      } else {
-        ld8<F32>(p.vcache, crow + c * 8, vf);
-      }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) mine[c * 8 + i] = w * (vf[i] + pev[c * 8 + i]);
-    }
-  } else {
-    for (int c = 0; c < hd; ++c) mine[c] = 0.f;
-  }
-  __syncwarp();
-  bf16* orow = p.out + static_cast<long long>(d) * p.ldo + head * hd;
-  for (int c = lane; c < hd; c += 32) {
-    float acc = 0.f;
-#pragma unroll 8
-    for (int j = 0; j < 32; ++j) acc += sW[j * (hd + 1) + c];
-    const bf16 hi = __float2bfloat16(acc);
-    orow[c] = hi;
-    if (F32) {
-      orow[c + p.split] = __float2bfloat16(acc - __bfloat162float(hi));
-      orow[c + 2 * p.split] = hi;
-    }
-  }
-}
-
-
-// Second generation of the streaming kernel.  The first one (above) gave lane p the K / V rows of cache position p: 32
+// The first version of this kernel gave lane p of a warp the K / V rows of cache position p of one (token, head): 32
 // lanes reading 16-byte pieces of 32 different cache slots plus three scalar PE loads per element -- LSU-bound, 490 us per
 // launch for the 37 x 37, C = 1024 module where the 180 MB of cache it reads are 28 us of HBM time (ncu launch list of
 // a streamed vitl frame: 8 launches = 2.3 of the frame's 6 ms).  Here a thread owns one 8-channel chunk of a token row,
@@ -512,7 +438,10 @@ template <bool F32, int TB>
 __global__ void __launch_bounds__(kTS2Threads) temporal_attn_stream2_kernel(const TemporalStreamParams p, int groups) {
   pdl_sync();  // launched with programmatic stream serialization (common.cuh)
   extern __shared__ __align__(16) uint8_t tsm[];
-  constexpr int JB = F32 ? 4 : 8;
+#ifndef VDA_TSTREAM_JB
+#define VDA_TSTREAM_JB 8
+#endif
+  constexpr int JB = F32 ? VDA_TSTREAM_JB / 2 : VDA_TSTREAM_JB;
   const int lpt = p.C >> 3;            // threads per token row
   const int used = groups * lpt;
   const int pitch = used + 1;          // row pitch of `part`: phase 2 reads one row per lane (no bank conflicts)
@@ -529,7 +458,7 @@ __global__ void __launch_bounds__(kTS2Threads) temporal_attn_stream2_kernel(cons
   const int Tk = p.Tk, Tc = p.Tk - 1;   // Tc cached positions + the new frame
   if (t < 32) s_slot[t] = t < Tk ? __ldg(p.slots + t) : 0;
   __syncthreads();
-  const long long new_row0 = static_cast<long long>(s_slot[Tc]) * p.hw;
+  const int new_slot = s_slot[Tc];
 
   if (worker) {
     float qv[TB][8];
@@ -554,11 +483,11 @@ __global__ void __launch_bounds__(kTS2Threads) temporal_attn_stream2_kernel(cons
 #pragma unroll
       for (int jj = 0; jj < JB; ++jj) {
         const int j = j0 + jj < Tc ? j0 + jj : Tc - 1;   // clamp: the surplus loads repeat the last row
-        const long long row0 = static_cast<long long>(s_slot[j]) * p.hw;
+        const int slot = s_slot[j];
 #pragma unroll
         for (int tb = 0; tb < TB; ++tb) {
           const int tok = tok0 + tb < p.hw ? tok0 + tb : p.hw - 1;
-          raw[jj][tb] = ldraw8<F32>(p.kcache, (row0 + tok) * p.C + ch);
+          raw[jj][tb] = ldraw8<F32>(p.kcache, (static_cast<long long>(tok) * p.cap + slot) * p.C + ch);
         }
       }
 #pragma unroll
@@ -588,7 +517,7 @@ __global__ void __launch_bounds__(kTS2Threads) temporal_attn_stream2_kernel(cons
         if (tok < p.hw) {
           float kf[8];
           ld8<F32>(p.knew, static_cast<long long>(tok) * p.ldn + ch, kf);
-          st8<F32>(p.kcache, (new_row0 + tok) * p.C + ch, kf);
+          st8<F32>(p.kcache, (static_cast<long long>(tok) * p.cap + new_slot) * p.C + ch, kf);
 #pragma unroll
           for (int i = 0; i < 8; ++i) dot = fmaf(qv[tb][i], kf[i] + pk[i], dot);
         }
@@ -634,11 +563,11 @@ __global__ void __launch_bounds__(kTS2Threads) temporal_attn_stream2_kernel(cons
 #pragma unroll
     for (int jj = 0; jj < JB; ++jj) {
       const int j = j0 + jj < Tc ? j0 + jj : Tc - 1;
-      const long long row0 = static_cast<long long>(s_slot[j]) * p.hw;
+      const int slot = s_slot[j];
 #pragma unroll
       for (int tb = 0; tb < TB; ++tb) {
         const int tok = tok0 + tb < p.hw ? tok0 + tb : p.hw - 1;
-        raw[jj][tb] = ldraw8<F32>(p.vcache, (row0 + tok) * p.C + ch);
+        raw[jj][tb] = ldraw8<F32>(p.vcache, (static_cast<long long>(tok) * p.cap + slot) * p.C + ch);
       }
     }
 #pragma unroll
@@ -667,7 +596,7 @@ __global__ void __launch_bounds__(kTS2Threads) temporal_attn_stream2_kernel(cons
       if (tok < p.hw) {
         float vf[8];
         ld8<F32>(p.vnew, static_cast<long long>(tok) * p.ldn + ch, vf);
-        st8<F32>(p.vcache, (new_row0 + tok) * p.C + ch, vf);
+        st8<F32>(p.vcache, (static_cast<long long>(tok) * p.cap + new_slot) * p.C + ch, vf);
         const float w = wrow[tb * p.heads * 32 + Tc];
 #pragma unroll
         for (int i = 0; i < 8; ++i) acc[tb][i] = fmaf(w, vf[i] + pv[i], acc[tb][i]);
@@ -704,85 +633,64 @@ using namespace vda;
 
 static int launch_temporal_stream(bool f32, const void* q, const void* knew, const void* vnew, int ldn, void* kcache,
                                   void* vcache, const int* slots, const float* pe_q, const float* pe_k, const float* pe_v,
-                                  void* out, int ldo, int split, int hw, int heads, int head_dim, int Tk, void* stream) {
+                                  void* out, int ldo, int split, int hw, int heads, int head_dim, int Tk, int cap, void* stream) {
+  const int C = heads * head_dim;
   if (!q || !knew || !vnew || !kcache || !vcache || !slots || !pe_q || !pe_k || !pe_v || !out || hw <= 0 || heads <= 0 ||
-      head_dim % 8 || head_dim > 128 || Tk < 1 || Tk > 32 || ldn % 8 || ldo % 2 || split < 0)
-    return set_error(-1, "vda_temporal_attn_stream: bad arguments");
+      head_dim % 8 || C / 8 > kTS2Threads || Tk < 1 || Tk > 32 || cap < Tk || ldn % 8 || ldo % 8 || split < 0 || split % 8)
+    return set_error(-1, "vda_temporal_attn_stream: bad arguments (head_dim %% 8, heads * head_dim <= 1024, Tk <= 32 <= cap, ld %% 8)");
   TemporalStreamParams p;
   p.q = q, p.knew = knew, p.vnew = vnew, p.kcache = kcache, p.vcache = vcache;
   p.slots = slots, p.pe_q = pe_q, p.pe_k = pe_k, p.pe_v = pe_v;
   p.out = static_cast<bf16*>(out);
-  p.ldn = ldn, p.ldo = ldo, p.hw = hw, p.heads = heads, p.hd = head_dim, p.C = heads * head_dim, p.Tk = Tk, p.split = split;
+  p.ldn = ldn, p.ldo = ldo, p.hw = hw, p.heads = heads, p.hd = head_dim, p.C = C, p.Tk = Tk, p.split = split, p.cap = cap;
   p.scale = 1.0f / sqrtf(static_cast<float>(head_dim));
-  const char* ev = getenv("VDA_TSTREAM");   // A/B knob: 1 = first-generation kernel (one warp per (token, head))
-  const int C = heads * head_dim;
-  if (!(ev && atoi(ev) == 1) && C % 8 == 0 && C / 8 <= kTS2Threads && ldo % 8 == 0 && split % 8 == 0) {
-    const int lpt = C / 8;
-    int groups = kTS2Threads / lpt;
-    if (groups > 8) groups = 8;
-    const char* etb = getenv("VDA_TSTREAM_TB");   // A/B knob: tokens per thread (2 or 4)
-    const int tb = etb && atoi(etb) == 4 ? 4 : 2;   // measured: 2 is faster for every motion-module shape (profiles/r02d_tstream_shapes.log)
-    const int used = groups * lpt;
-    const int smem2 = (tb * 32 * (used + 1) + groups * tb * heads * 32 + 32) * 4;
-    static DeviceOnce once2;
-    int& conf2 = once2.slot();
-    if (!conf2) {
-      const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
-      const int mx = (4 * 32 * (kTS2Threads + 1) + 8 * 4 * 16 * 32 + 32) * 4;
-      int rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream2_kernel<false, 2>, attr, mx), "temporal stream2 smem");
-      if (!rc) rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream2_kernel<false, 4>, attr, mx), "temporal stream2 smem");
-      if (!rc) rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream2_kernel<true, 2>, attr, mx), "temporal stream2 smem");
-      if (!rc) rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream2_kernel<true, 4>, attr, mx), "temporal stream2 smem");
-      if (rc) return rc;
-      conf2 = 1;
-    }
-    const dim3 grid2((hw + groups * tb - 1) / (groups * tb));
-    const cudaStream_t st2 = static_cast<cudaStream_t>(stream);
-    cudaError_t le;
-    if (f32)
-      le = tb == 4 ? launch_pdl(temporal_attn_stream2_kernel<true, 4>, grid2, dim3(kTS2Threads), smem2, st2, p, groups)
-                   : launch_pdl(temporal_attn_stream2_kernel<true, 2>, grid2, dim3(kTS2Threads), smem2, st2, p, groups);
-    else
-      le = tb == 4 ? launch_pdl(temporal_attn_stream2_kernel<false, 4>, grid2, dim3(kTS2Threads), smem2, st2, p, groups)
-                   : launch_pdl(temporal_attn_stream2_kernel<false, 2>, grid2, dim3(kTS2Threads), smem2, st2, p, groups);
-    return check_cuda(le, "temporal_attn_stream2 launch");
-  }
-  const int smem = kTWarps * 32 * (head_dim + 1) * 4;
+  const int lpt = C / 8;
+  int groups = kTS2Threads / lpt;
+  if (groups > 8) groups = 8;
+  const char* etb = getenv("VDA_TSTREAM_TB");   // A/B knob: tokens per thread (2 or 4)
+  const int tb = etb && atoi(etb) == 4 ? 4 : 2;   // measured: 2 is faster for every motion-module shape (profiles/r02d_tstream_shapes.log)
+  const int used = groups * lpt;
+  const int smem = (tb * 32 * (used + 1) + groups * tb * heads * 32 + 32) * 4;
+  const int mx = (4 * 32 * (kTS2Threads + 1) + 8 * 4 * 16 * 32 + 32) * 4;   // 129 KB
+  if (smem > mx) return set_error(-1, "vda_temporal_attn_stream: too many heads (%d)", heads);
   static DeviceOnce once;
   int& configured = once.slot();
   if (!configured) {
-    int rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             kTWarps * 32 * 129 * 4),
-                        "temporal stream smem attribute");
-    if (!rc)
-      rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           kTWarps * 32 * 129 * 4),
-                      "temporal stream smem attribute");
+    const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+    int rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream2_kernel<false, 2>, attr, mx), "temporal stream smem");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream2_kernel<false, 4>, attr, mx), "temporal stream smem");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream2_kernel<true, 2>, attr, mx), "temporal stream smem");
+    if (!rc) rc = check_cuda(cudaFuncSetAttribute(temporal_attn_stream2_kernel<true, 4>, attr, mx), "temporal stream smem");
     if (rc) return rc;
     configured = 1;
   }
-  const int units = hw * heads, grid = (units + kTWarps - 1) / kTWarps;
+  const dim3 grid((hw + groups * tb - 1) / (groups * tb));
   const cudaStream_t st = static_cast<cudaStream_t>(stream);
-  return check_cuda(f32 ? launch_pdl(temporal_attn_stream_kernel<true>, dim3(grid), dim3(kTWarps * 32), smem, st, p)
-                        : launch_pdl(temporal_attn_stream_kernel<false>, dim3(grid), dim3(kTWarps * 32), smem, st, p),
-                    "temporal_attn_stream launch");
+  cudaError_t le;
+  if (f32)
+    le = tb == 4 ? launch_pdl(temporal_attn_stream2_kernel<true, 4>, grid, dim3(kTS2Threads), smem, st, p, groups)
+                 : launch_pdl(temporal_attn_stream2_kernel<true, 2>, grid, dim3(kTS2Threads), smem, st, p, groups);
+  else
+    le = tb == 4 ? launch_pdl(temporal_attn_stream2_kernel<false, 4>, grid, dim3(kTS2Threads), smem, st, p, groups)
+                 : launch_pdl(temporal_attn_stream2_kernel<false, 2>, grid, dim3(kTS2Threads), smem, st, p, groups);
+  return check_cuda(le, "temporal_attn_stream launch");
 }
 
 extern "C" int vda_temporal_attn_stream(const void* q, const void* knew, const void* vnew, int ldn, void* kcache,
                                         void* vcache, const int* slots, const float* pe_q, const float* pe_k,
                                         const float* pe_v, void* out, int ldo, int hw, int heads, int head_dim, int Tk,
-                                        void* stream) {
+                                        int cap, void* stream) {
   return launch_temporal_stream(false, q, knew, vnew, ldn, kcache, vcache, slots, pe_q, pe_k, pe_v, out, ldo, 0, hw, heads,
-                                head_dim, Tk, stream);
+                                head_dim, Tk, cap, stream);
 }
 
 extern "C" int vda_temporal_attn_stream_f32(const float* q, const float* knew, const float* vnew, int ldn, float* kcache,
                                             float* vcache, const int* slots, const float* pe_q, const float* pe_k,
                                             const float* pe_v, void* out, int ldo, int split, int hw, int heads,
-                                            int head_dim, int Tk, void* stream) {
+                                            int head_dim, int Tk, int cap, void* stream) {
   if (split <= 0 || split % 2) return set_error(-1, "vda_temporal_attn_stream_f32: split must be the part stride");
   return launch_temporal_stream(true, q, knew, vnew, ldn, kcache, vcache, slots, pe_q, pe_k, pe_v, out, ldo, split, hw, heads,
-                                head_dim, Tk, stream);
+                                head_dim, Tk, cap, stream);
 }
 
 

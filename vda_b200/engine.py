@@ -472,7 +472,7 @@ class StreamCache:
 
     The reference keeps, per frame, the 8 post-LayerNorm hidden states feeding the 8 temporal
     attentions and re-projects K/V of all of them every frame.  Here each of the 8 attentions owns
-    a slot-addressed K/V cache [cap, hw, C] of PE-free projections; the reference's
+    a slot-addressed K/V cache [hw, cap, C] of PE-free projections; the reference's
     `frame_cache_list` becomes a list of slot numbers with identical list semantics."""
 
     CAP = 44  # the reference's list peaks at 43 entries (42 after the trim) + 1 slot in flight
@@ -487,8 +487,8 @@ class StreamCache:
         geo = [(gh * gw, w.oc[2]), (gh4 * gw4, w.oc[3]), (gh * gw, w.F), (4 * gh * gw, w.F)]
         self.fp32 = engine.fp32
         dt = torch.float32 if engine.fp32 else torch.bfloat16   # FP32-accuracy mode keeps fp32 projections
-        self.k = [[torch.zeros(self.CAP, hw, C, dtype=dt, device=dev) for _ in range(2)] for hw, C in geo]
-        self.v = [[torch.zeros(self.CAP, hw, C, dtype=dt, device=dev) for _ in range(2)] for hw, C in geo]
+        self.k = [[torch.zeros(hw, self.CAP, C, dtype=dt, device=dev) for _ in range(2)] for hw, C in geo]
+        self.v = [[torch.zeros(hw, self.CAP, C, dtype=dt, device=dev) for _ in range(2)] for hw, C in geo]
         self.slots_dev = torch.zeros(32, dtype=torch.int32, device=dev)
         self.slots_host = torch.zeros(32, dtype=torch.int32).pin_memory()
         self.Tk = 1

@@ -103,8 +103,8 @@ def _declare(lib):
         "vda_bilinear_f32": [vp, vp, i, i, i, i, i, i, vp],
         "vda_im2col_s2": [vp, vp, i, i, i, i, vp],
         "vda_temporal_attn": [vp, i, vp, i, vp, i, vp, i, i, i, i, i, i, vp],
-        "vda_temporal_attn_stream": [vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, vp],
-        "vda_temporal_attn_stream_f32": [vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, i, vp],
+        "vda_temporal_attn_stream": [vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, i, vp],
+        "vda_temporal_attn_stream_f32": [vp, vp, vp, i, vp, vp, vp, vp, vp, vp, vp, i, i, i, i, i, i, i, vp],
         "vda_preprocess_u8": [vp, i, i, i, vp, i, i, vp],
         "vda_minmax_f32": [vp, C.c_longlong, vp, vp],
         "vda_depth_colorize": [vp, C.c_longlong, vp, vp, vp, i, vp],
@@ -321,18 +321,21 @@ def temporal_attn(q, ldq, k, ldk, v, ldv, out, ldo, hw, heads, head_dim, Tq, Tk)
 
 
 def temporal_attn_stream(q, knew, vnew, ldn, kcache, vcache, slots, pe_q, pe_k, pe_v, out, ldo, hw, heads, head_dim, Tk):
+    """kcache / vcache: [hw, cap, C] (the cap slots of a token are adjacent)."""
+    assert kcache.dim() == 3 and kcache.shape[0] == hw and vcache.shape == kcache.shape
     check(load().vda_temporal_attn_stream(ptr(q), ptr(knew), ptr(vnew), ldn, ptr(kcache), ptr(vcache), ptr(slots),
                                           ptr(pe_q), ptr(pe_k), ptr(pe_v), ptr(out), ldo, hw, heads, head_dim, Tk,
-                                          stream_ptr()))
+                                          kcache.shape[1], stream_ptr()))
     _launched(1)
 
 
 def temporal_attn_stream_f32(q, knew, vnew, ldn, kcache, vcache, slots, pe_q, pe_k, pe_v, out, split, hw, heads, head_dim,
                              Tk):
     """FP32-accuracy mode: q/knew/vnew/caches f32, out split bf16 [hw, 3*split]."""
+    assert kcache.dim() == 3 and kcache.shape[0] == hw and vcache.shape == kcache.shape
     check(load().vda_temporal_attn_stream_f32(ptr(q), ptr(knew), ptr(vnew), ldn, ptr(kcache), ptr(vcache), ptr(slots),
                                               ptr(pe_q), ptr(pe_k), ptr(pe_v), ptr(out), out.shape[1], split, hw, heads,
-                                              head_dim, Tk, stream_ptr()))
+                                              head_dim, Tk, kcache.shape[1], stream_ptr()))
     _launched(1)
 
 
