@@ -394,7 +394,7 @@ __device__ __forceinline__ void st8(void* base, long long off, const float (&v)[
 constexpr int kTS2Threads = 128;
 template <bool F32>
 __device__ __forceinline__ void ldf8(const float* src, float (&o)[8]) {
-  const float4 a = *reinterpret_cast<const float4*>(src), b = *reinterpret_cast<const float4*>(src + 4);
+  const float4 a = __ldg(reinterpret_cast<const float4*>(src)), b = __ldg(reinterpret_cast<const float4*>(src + 4));
   o[0] = a.x, o[1] = a.y, o[2] = a.z, o[3] = a.w, o[4] = b.x, o[5] = b.y, o[6] = b.z, o[7] = b.w;
 }
 
@@ -490,18 +490,19 @@ __global__ void __launch_bounds__(kTS2Threads) temporal_attn_stream2_kernel(cons
           raw[jj][tb] = ldraw8<F32>(p.kcache, (static_cast<long long>(tok) * p.cap + slot) * p.C + ch);
         }
       }
+      float pe[JB][8];   // the PE chunks of the batch travel with the cache rows (an L2 round trip each otherwise)
+#pragma unroll
+      for (int jj = 0; jj < JB; ++jj) ldf8<F32>(p.pe_k + static_cast<long long>(j0 + jj < Tc ? j0 + jj : Tc - 1) * p.C + ch, pe[jj]);
 #pragma unroll
       for (int jj = 0; jj < JB; ++jj) {
         const int j = j0 + jj;
         if (j < Tc) {
-          float pk[8];
-          ldf8<F32>(p.pe_k + static_cast<long long>(j) * p.C + ch, pk);
 #pragma unroll
           for (int tb = 0; tb < TB; ++tb) {
             float kf[8], dot = 0.f;
             cvt8<F32>(raw[jj][tb], kf);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) dot = fmaf(qv[tb][i], kf[i] + pk[i], dot);
+            for (int i = 0; i < 8; ++i) dot = fmaf(qv[tb][i], kf[i] + pe[jj][i], dot);
             part[(tb * 32 + j) * pitch + t] = dot;
           }
         }
@@ -570,19 +571,20 @@ __global__ void __launch_bounds__(kTS2Threads) temporal_attn_stream2_kernel(cons
         raw[jj][tb] = ldraw8<F32>(p.vcache, (static_cast<long long>(tok) * p.cap + slot) * p.C + ch);
       }
     }
+    float pe[JB][8];
+#pragma unroll
+    for (int jj = 0; jj < JB; ++jj) ldf8<F32>(p.pe_v + static_cast<long long>(j0 + jj < Tc ? j0 + jj : Tc - 1) * p.C + ch, pe[jj]);
 #pragma unroll
     for (int jj = 0; jj < JB; ++jj) {
       const int j = j0 + jj;
       if (j < Tc) {
-        float pv[8];
-        ldf8<F32>(p.pe_v + static_cast<long long>(j) * p.C + ch, pv);
 #pragma unroll
         for (int tb = 0; tb < TB; ++tb) {
           float vf[8];
           cvt8<F32>(raw[jj][tb], vf);
           const float w = wrow[tb * p.heads * 32 + j];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) acc[tb][i] = fmaf(w, vf[i] + pv[i], acc[tb][i]);
+          for (int i = 0; i < 8; ++i) acc[tb][i] = fmaf(w, vf[i] + pe[jj][i], acc[tb][i]);
         }
       }
     }
