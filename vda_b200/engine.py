@@ -166,6 +166,9 @@ class Engine:
         self.tail_fused = os.environ.get("VDA_TAIL_FUSED", "1") == "1"
         self.tail_mode = int(os.environ.get("VDA_TAIL_MODE", "0"))
         self.tail_chunk = int(os.environ.get("VDA_TAIL_CHUNK", "1"))
+        # reassemble branches on side streams: 1 = streamed frames only (default), 2 = windows too (A/B), 0 = off
+        self.head_streams = int(os.environ.get("VDA_HEAD_STREAMS", "1"))
+        self._side = None
 
     def _ep(self, width, **kw):
         """Epilogue of a launch whose bf16 outputs / residuals are `width` channels wide (x3 parts in
@@ -300,27 +303,15 @@ class Engine:
         Fc, oc, ocp, hw = w.F, w.oc, w.ocp, gh * gw
         sp, Wd = self.fp32, self.W
         rows = T * hw
-        pr = []
-        for i in range(4):
+        gh4, gw4 = (gh - 1) // 2 + 1, (gw - 1) // 2 + 1
+        hw4 = gh4 * gw4
+
+        def proj(i):
             wk, bk = w.proj[i]
             n_i = wk.shape[0]
             p = ws.get(f"proj{i}", (rows, n_i * Wd))
             L.gemm(taps[i], wk, self._ep(n_i, bias=bk, out=p))
-            pr.append(p)
-        wk, bk, s, cop = w.ct0
-        l1 = ws.get("layer1", (T * 16 * hw, cop * Wd))
-        L.gemm(pr[0], wk, self._ep(cop, bias=bk, out=l1, store_mode=L.ST_CONVT, ct=(s, cop, gh, gw)), K=None if sp else oc[0])
-        wk, bk, s, cop = w.ct1
-        l2 = ws.get("layer2", (T * 4 * hw, cop * Wd))
-        L.gemm(pr[1], wk, self._ep(cop, bias=bk, out=l2, store_mode=L.ST_CONVT, ct=(s, cop, gh, gw)), K=None if sp else oc[1])
-        gh4, gw4 = (gh - 1) // 2 + 1, (gw - 1) // 2 + 1
-        hw4 = gh4 * gw4
-        col = ws.get("rs3_col", (T * hw4, 9 * oc[3] * Wd))
-        L.im2col_s2(pr[3], col, T, gh, gw, oc[3] * Wd)
-        l4 = ws.get("layer4", (T * hw4, oc[3] * Wd))
-        L.gemm(col, w.w_rs3, self._ep(oc[3], bias=w.b_rs3, out=l4))
-        l3m = self.motion(0, pr[2], T, hw, ws, ws.get("layer3m", (rows, oc[2] * Wd)), stream_ctx=stream_ctx)
-        l4m = self.motion(1, l4, T, hw4, ws, ws.get("layer4m", (T * hw4, oc[3] * Wd)), stream_ctx=stream_ctx)
+            return p
 
         def rn(i, src, n_h, n_w, cin):
             r = ws.get(f"rn{i}", (T * n_h * n_w, Fc * Wd))
@@ -328,14 +319,65 @@ class Engine:
             L.conv3x3(src, w.rn[i], self._ep(Fc, out=r, out_relu=rr), T, n_h, n_w, cin * Wd, Fc)
             return r, rr
 
-        r1, r1r = rn(0, l1, 4 * gh, 4 * gw, ocp[0])
-        r2, r2r = rn(1, l2, 2 * gh, 2 * gw, ocp[1])
-        r3, r3r = rn(2, l3m, gh, gw, ocp[2])
+        # The three reassemble branches that feed refinenet 3, 2 and 1 do not depend on the refinenet-4 chain.  For a
+        # streamed frame (every launch a fraction of a wave) they run on side streams inside the captured graph and
+        # join where their results are consumed; a 32-frame window fills the GPU with every launch and stays serial.
+        par = self.head_streams >= 2 or (self.head_streams == 1 and stream_ctx is not None)
+        joins = {}
+        if par:
+            main = torch.cuda.current_stream()
+            fork = torch.cuda.Event()
+            fork.record(main)
+            if self._side is None:
+                self._side = [torch.cuda.Stream(device=self.device) for _ in range(3)]
+
+        def branch(i, fn):
+            if not par:
+                return fn()
+            s = self._side[i]
+            s.wait_event(fork)
+            with torch.cuda.stream(s):
+                out = fn()
+                joins[i] = torch.cuda.Event()
+                joins[i].record(s)
+            return out
+
+        def join(i):
+            if par:
+                torch.cuda.current_stream().wait_event(joins[i])
+
+        def branch1():   # layer1: ConvTranspose x4 -> layer1_rn
+            wk, bk, s_, cop = w.ct0
+            l1 = ws.get("layer1", (T * 16 * hw, cop * Wd))
+            L.gemm(proj(0), wk, self._ep(cop, bias=bk, out=l1, store_mode=L.ST_CONVT, ct=(s_, cop, gh, gw)), K=None if sp else oc[0])
+            return rn(0, l1, 4 * gh, 4 * gw, ocp[0])
+
+        def branch2():   # layer2: ConvTranspose x2 -> layer2_rn
+            wk, bk, s_, cop = w.ct1
+            l2 = ws.get("layer2", (T * 4 * hw, cop * Wd))
+            L.gemm(proj(1), wk, self._ep(cop, bias=bk, out=l2, store_mode=L.ST_CONVT, ct=(s_, cop, gh, gw)), K=None if sp else oc[1])
+            return rn(1, l2, 2 * gh, 2 * gw, ocp[1])
+
+        def branch3():   # layer3: motion module 0 -> layer3_rn
+            l3m = self.motion(0, proj(2), T, hw, ws, ws.get("layer3m", (rows, oc[2] * Wd)), stream_ctx=stream_ctx)
+            return rn(2, l3m, gh, gw, ocp[2])
+
+        r1, r1r = branch(0, branch1)
+        r2, r2r = branch(1, branch2)
+        r3, r3r = branch(2, branch3)
+        p3_in = proj(3)
+        col = ws.get("rs3_col", (T * hw4, 9 * oc[3] * Wd))
+        L.im2col_s2(p3_in, col, T, gh, gw, oc[3] * Wd)
+        l4 = ws.get("layer4", (T * hw4, oc[3] * Wd))
+        L.gemm(col, w.w_rs3, self._ep(oc[3], bias=w.b_rs3, out=l4))
+        l4m = self.motion(1, l4, T, hw4, ws, ws.get("layer4m", (T * hw4, oc[3] * Wd)), stream_ctx=stream_ctx)
         r4, r4r = rn(3, l4m, gh4, gw4, ocp[3])
         p4 = self._fusion(4, ws, T, gh4, gw4, None, r4, r4r, (gh, gw))
         p4m = self.motion(2, p4, T, hw, ws, ws.get("path4m", (rows, Fc * Wd)), stream_ctx=stream_ctx)
+        join(2)
         p3 = self._fusion(3, ws, T, gh, gw, p4m, r3, r3r, (2 * gh, 2 * gw))
         p3m = self.motion(3, p3, T, 4 * hw, ws, ws.get("path3m", (T * 4 * hw, Fc * Wd)), stream_ctx=stream_ctx)
+        join(1)
         p2 = self._fusion(2, ws, T, 2 * gh, 2 * gw, p3m, r2, r2r, (4 * gh, 4 * gw))
         F2p = w.F2p
         Ho, Wo = gh * PATCH, gw * PATCH
@@ -351,6 +393,7 @@ class Engine:
         if sp or mode == 0:
             mode, chunk = 0, T
         fused = (not sp) and mode == 0 and self.tail_fused and L.depth_tail_supported(8 * gh, 8 * gw, Ho, Wo, F2p)
+        join(0)
         v1 = self._fusion(1, ws, T, 4 * gh, 4 * gw, p2, r1, r1r, (8 * gh, 8 * gw), upsample=(mode != 2))
         h4, w4, h8, w8 = 4 * gh, 4 * gw, 8 * gh, 8 * gw
         o1_all = None if mode == 2 else ws.get("out1", (T * h8 * w8, F2p * Wd))
