@@ -166,8 +166,8 @@ class Engine:
         self.tail_fused = os.environ.get("VDA_TAIL_FUSED", "1") == "1"
         self.tail_mode = int(os.environ.get("VDA_TAIL_MODE", "0"))
         self.tail_chunk = int(os.environ.get("VDA_TAIL_CHUNK", "1"))
-        # reassemble branches on side streams: 1 = streamed frames only (default), 2 = windows too (A/B), 0 = off
-        self.head_streams = int(os.environ.get("VDA_HEAD_STREAMS", "1"))
+        # reassemble branches on side streams: 2 = always (default), 1 = streamed frames only, 0 = off (A/B knob)
+        self.head_streams = int(os.environ.get("VDA_HEAD_STREAMS", "2"))
         self._side = None
 
     def _ep(self, width, **kw):
@@ -319,9 +319,10 @@ class Engine:
             L.conv3x3(src, w.rn[i], self._ep(Fc, out=r, out_relu=rr), T, n_h, n_w, cin * Wd, Fc)
             return r, rr
 
-        # The three reassemble branches that feed refinenet 3, 2 and 1 do not depend on the refinenet-4 chain.  For a
-        # streamed frame (every launch a fraction of a wave) they run on side streams inside the captured graph and
-        # join where their results are consumed; a 32-frame window fills the GPU with every launch and stays serial.
+        # The three reassemble branches that feed refinenet 3, 2 and 1 do not depend on the refinenet-4 chain: they run
+        # on side streams inside the captured graph and join where their results are consumed.  For a streamed frame
+        # every launch is a fraction of a wave (vitl 4.13 -> 3.97 ms per frame); in a 32-frame window only the small
+        # launches of levels 3 / 4 gain (49.37 -> 49.11 ms, profiles/r02d_ab_head_streams*.log).
         par = self.head_streams >= 2 or (self.head_streams == 1 and stream_ctx is not None)
         joins = {}
         if par:
