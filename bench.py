@@ -38,7 +38,7 @@ if ROOT not in sys.path:
 
 METRIC = "frames/sec VDA-L 518x518 32-frame windows"
 UNIT = "frames/s"
-NCU_FC1 = "r02_ncu_fc1.json"   # ncu --set full capture of the fc1 launch the roofline's `traffic` is read from
+NCU_FC1 = "r02d_ncu_fc1.json"   # ncu --set full capture of the fc1 launch the roofline's `traffic` is read from
 
 
 def parse():

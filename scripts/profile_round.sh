@@ -12,6 +12,8 @@ for op in ${OPS:-attn fc1 tailconv ln}; do
     attn) k=attn_fwd_v2 ;;
     fc1)  k=gemm_tc2 ;;
     tailconv) k=gemm_tc_kernel ;;
+    tail_fused) k=depth_tail ;;
+    attn_exact) k=attn_fwd_v2 ;;
     ln)   k=layernorm ;;
     *)    k=$op ;;
   esac

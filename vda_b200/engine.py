@@ -323,7 +323,7 @@ class Engine:
         # on side streams inside the captured graph and join where their results are consumed.  For a streamed frame
         # every launch is a fraction of a wave (vitl 4.13 -> 3.97 ms per frame); in a 32-frame window only the small
         # launches of levels 3 / 4 gain (49.37 -> 49.11 ms, profiles/r02d_ab_head_streams*.log).
-        par = self.head_streams >= 2 or (self.head_streams == 1 and stream_ctx is not None)
+        par = (self.head_streams >= 2 or (self.head_streams == 1 and stream_ctx is not None)) and L.PROFILE is None   # per-launch event timing stays serial
         joins = {}
         if par:
             main = torch.cuda.current_stream()
