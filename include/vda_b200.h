@@ -78,9 +78,10 @@ int vda_conv3x3_nhwc(const void* x, int ldx, const void* w, int n, int H, int W,
 /* Flash-style spatial attention, head_dim 64, non-causal (dinov2_layers/attention.py:53-59 / :76).
  * qk: [frames*S, 2D] bf16 (Q | K), vt: [frames*heads, 64, s_pad] bf16 (V transposed, zero padded,
  * s_pad % 8 == 0) -- both written by vda_gemm_bf16 with VDA_ST_QKV.  out: [frames*S, D] bf16.
- * fixup_flags: NULL = exact online softmax.  Otherwise frames*heads*ceil(S/128) ints, zero on entry and on return:
- * the kernel runs the optimistic softmax (offset fixed after the first KV tile, no running maximum) and a second
- * launch recomputes with the exact algorithm any query tile whose sums left the safe range -- same result, faster. */
+ * fixup_flags: NULL, or frames*heads*ceil(S/128) ints that are zero on entry and on return.  The library always runs the
+ * exact online softmax; the flags are only used by experiment builds (-DVDA_ATTN_EXPERIMENTS, VDA_ATTN_OPT=1: optimistic
+ * softmax with the offset fixed after the first KV tile + an exact fix-up pass over flagged query tiles -- same result,
+ * measured 5 % slower on B200). */
 int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int frames, int S, int heads, int s_pad,
                        int* fixup_flags, void* stream);
 

@@ -1,5 +1,7 @@
 """Attention / normalisation / resampling / alignment kernels vs plain torch fp32 references."""
 import numpy as np
+import os
+
 import pytest
 import torch
 import torch.nn.functional as F
@@ -28,6 +30,10 @@ def _close(got, want, tol=2e-2):
     assert err <= tol * max(ref, 1e-6), f"max abs err {err} vs ref max {ref}"
 
 
+# the optimistic-softmax variant exists in experiment builds only (VDA_NVCC_EXTRA=-DVDA_ATTN_EXPERIMENTS)
+_EXPERIMENTS = "VDA_ATTN_EXPERIMENTS" in os.environ.get("VDA_NVCC_EXTRA", "")
+
+
 def _attn_flags(frames, S, heads):
     return torch.zeros(frames * heads * ((S + 127) // 128), device="cuda", dtype=torch.int32)
 
@@ -37,6 +43,8 @@ def _attn_flags(frames, S, heads):
 def test_flash_attention(L, frames, S, heads, optimistic, monkeypatch):
     """optimistic: offset fixed after the first KV tile + fix-up pass (flags stay zero on well-behaved scores);
     opt-in with VDA_ATTN_OPT=1 (slower than the exact kernel on B200, kept as a measured variant)."""
+    if optimistic and not _EXPERIMENTS:
+        pytest.skip("optimistic softmax: experiment builds only")
     monkeypatch.setenv("VDA_ATTN_OPT", "1" if optimistic else "0")
     D = heads * 64
     spad = (S + 7) // 8 * 8
@@ -61,6 +69,8 @@ def test_flash_attention_optimistic_fixup(L, boost, monkeypatch):
     """Scores far above the first KV tile's maximum: a moderate jump stays inside the optimistic kernel's safe range,
     a huge one overflows its fixed offset, raises the tile's flag and is recomputed exactly by the fix-up pass.  Either
     way the result is the exact softmax and the flags are zero again afterwards."""
+    if not _EXPERIMENTS:
+        pytest.skip("optimistic softmax: experiment builds only")
     monkeypatch.setenv("VDA_ATTN_OPT", "1")
     frames, S, heads = 2, 700, 2
     D = heads * 64

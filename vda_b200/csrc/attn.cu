@@ -512,7 +512,8 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
   p.prof = g_attn_prof;
 #endif
   // A/B knobs: VDA_ATTN_POLY = 0 / 4 / 8 (default): one score pair in N evaluated with the packed polynomial exp2;
-  // VDA_ATTN_OPT = 1: optimistic softmax + fix-up pass when the caller passes flags.  OFF by default: measured on B200
+  // VDA_ATTN_OPT = 1 (experiment builds, -DVDA_ATTN_EXPERIMENTS, only; the product library always runs the exact online
+  // softmax and leaves `fixup_flags` untouched): optimistic softmax + fix-up pass when the caller passes flags.  Measured on B200
   // it is 5 % SLOWER in the window (10.5 -> 11.0 ms, profiles/r02c_ab_attn_optimistic_negative.log) although it issues a
   // third fewer instructions per KV tile and has no maximum chain.  What the phase clocks and pipe probes of round 2 show
   // (profiles/r02d_attn_v2_phase_clocks_*.log, r02d_pipe_rate_all.log, r02d_ncu_attn_phase_buckets.txt): TMEM reads are
@@ -523,9 +524,9 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
   // and CTA = 1250 per SM against the 900-1040 the MUFU pipe would allow.
   const char* ep = getenv("VDA_ATTN_POLY");
   const int poly = ep ? atoi(ep) : 8;
+#ifdef VDA_ATTN_EXPERIMENTS
   const char* eo = getenv("VDA_ATTN_OPT");
   const bool opt = fixup_flags != nullptr && eo && atoi(eo) == 1;
-#ifdef VDA_ATTN_EXPERIMENTS
   // VDA_ATTN_V = 3: persistent ping-pong kernel (attn3.cu; VDA_ATTN_PP = 0: free-running streams); 4: chained mode
   // (VDA_ATTN_IPC work items per CTA); default 2 = this file.  All measured slower (profiles/r02d_ab_attn_v3_*).
   const char* ev = getenv("VDA_ATTN_V");
@@ -548,9 +549,11 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
     int rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<8, true, true>, attr, kA2Smem), "attn smem");
     if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<4, true, true>, attr, kA2Smem), "attn smem");
     if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0, true, true>, attr, kA2Smem), "attn smem");
+#ifdef VDA_ATTN_EXPERIMENTS
     if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<8, true, true, true>, attr, kA2Smem), "attn smem");
     if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<0, true, true, true>, attr, kA2Smem), "attn smem");
     if (!rc) rc = check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<8, true, true, false, true>, attr, kA2Smem), "attn smem");
+#endif
     if (rc) return rc;
     configured = 1;
   }
@@ -564,14 +567,14 @@ extern "C" int vda_flash_attn_fwd(const void* qk, const void* vt, void* out, int
     check_cuda(cudaFuncSetAttribute(attn_fwd_v2_kernel<8, true, true, false, false, true>,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize, smem), "attn smem");
     le = launch_pdl(attn_fwd_v2_kernel<8, true, true, false, false, true>, grid, dim3(kAttThreads), smem, st, p);
-  } else
-#endif
-  if (opt) {
+  } else if (opt) {
     le = poly == 0 ? launch_pdl(attn_fwd_v2_kernel<0, true, true, true>, grid, dim3(kAttThreads), kA2Smem, st, p)
                    : launch_pdl(attn_fwd_v2_kernel<8, true, true, true>, grid, dim3(kAttThreads), kA2Smem, st, p);
     if (le == cudaSuccess)   // fix-up pass: exact kernel on the flagged query tiles only (normally none)
       le = launch_pdl(attn_fwd_v2_kernel<8, true, true, false, true>, grid, dim3(kAttThreads), kA2Smem, st, p);
-  } else if (poly == 8) {
+  } else
+#endif
+  if (poly == 8) {
     le = launch_pdl(attn_fwd_v2_kernel<8, true, true>, grid, dim3(kAttThreads), kA2Smem, st, p);
   } else if (poly == 4) {
     le = launch_pdl(attn_fwd_v2_kernel<4, true, true>, grid, dim3(kAttThreads), kA2Smem, st, p);

@@ -162,10 +162,7 @@ class Engine:
         self.launches_per_run = {}
         self.use_graph = True
         self._warm = set()
-        # tail chunking (see head()): A/B knobs VDA_TAIL_MODE / VDA_TAIL_CHUNK
         self.tail_fused = os.environ.get("VDA_TAIL_FUSED", "1") == "1"
-        self.tail_mode = int(os.environ.get("VDA_TAIL_MODE", "0"))
-        self.tail_chunk = int(os.environ.get("VDA_TAIL_CHUNK", "1"))
         # reassemble branches on side streams: 2 = always (default), 1 = streamed frames only, 0 = off (A/B knob)
         self.head_streams = int(os.environ.get("VDA_HEAD_STREAMS", "2"))
         self._side = None
@@ -206,7 +203,6 @@ class Engine:
         else:
             qk = ws.get("qk", (M, 2 * D))
             vt = ws.get("vt", (T * heads, 64, spad), zero=True)
-            aflags = ws.get("attn_flags", (T * heads * ((S + 127) // 128),), torch.int32, zero=True)
         taps = []
         for i, b in enumerate(w.blocks):
             L.layernorm(tok, b["n1w"], b["n1b"], xn, 1e-6, C=D, split=int(sp))
@@ -216,7 +212,7 @@ class Engine:
             else:
                 L.gemm(xn, b["wqkv"], L.make_epilogue(bias=b["bqkv"], out=qk, ldo=2 * D, store_mode=L.ST_QKV,
                                                       qkv=(vt, D, heads, S, spad)))
-                L.flash_attn(qk, vt, ao, T, S, heads, spad, aflags)
+                L.flash_attn(qk, vt, ao, T, S, heads, spad)
             L.gemm(ao, b["wproj"], L.make_epilogue(bias=b["bproj"], scale=b["g1"], res_f32=tok, out_f32=tok, ldo=D))
             L.layernorm(tok, b["n2w"], b["n2b"], xn, 1e-6, C=D, split=int(sp))
             L.gemm(xn, b["w1"], self._ep(4 * D, bias=b["b1"], out=h1, act=L.ACT_GELU))
@@ -383,42 +379,24 @@ class Engine:
         F2p = w.F2p
         Ho, Wo = gh * PATCH, gw * PATCH
         depth = ws.get("depth", (T, Ho, Wo), torch.float32)
-        sp_f, sp_2 = (Fc if sp else 0), (F2p if sp else 0)
+        sp_2 = F2p if sp else 0
         # Tail = refinenet1's upsample (x2) -> output_conv1 3x3 -> upsample to the input size -> 3x3(->32)+ReLU+1x1+ReLU
-        # (dpt_temporal.py:96-123).  Each stage is a bandwidth-heavy map (1.4 / 0.7 / 2.2 GB per vitl window) that the
-        # next stage reads exactly once, so the chain runs over chunks of `tail_chunk` frames through buffers of ONE
-        # chunk that every chunk reuses: a stage's output is still in the 126 MB L2 when the next stage reads it and
-        # is overwritten before it is ever written back (the reference micro-batches the same stages by 4 frames,
-        # :96-123, to cap memory).  tail_mode 0: whole-window launches; 1: only the last pair chunked; 2: all four.
-        mode, chunk = self.tail_mode, max(1, min(self.tail_chunk, T))
-        if sp or mode == 0:
-            mode, chunk = 0, T
-        fused = (not sp) and mode == 0 and self.tail_fused and L.depth_tail_supported(8 * gh, 8 * gw, Ho, Wo, F2p)
+        # (dpt_temporal.py:96-123).  The last pair is ONE tcgen05 kernel (csrc/depth_tail.cu): the upsampled map (2.2 GB
+        # per vitl window) is built tile by tile in shared memory and never touches HBM.  (Running the unfused pair per
+        # frame group through one L2-sized buffer was measured slower: profiles/r02a_ab_tail_chunking_negative.log.)
+        fused = (not sp) and self.tail_fused and L.depth_tail_supported(8 * gh, 8 * gw, Ho, Wo, F2p)
         join(0)
-        v1 = self._fusion(1, ws, T, 4 * gh, 4 * gw, p2, r1, r1r, (8 * gh, 8 * gw), upsample=(mode != 2))
-        h4, w4, h8, w8 = 4 * gh, 4 * gw, 8 * gh, 8 * gw
-        o1_all = None if mode == 2 else ws.get("out1", (T * h8 * w8, F2p * Wd))
-        if mode != 2:
-            L.conv3x3(v1, w.w_oc1, self._ep(F2p, bias=w.b_oc1, out=o1_all), T, h8, w8, Fc * Wd, F2p)
-        for f0 in range(0, T, chunk):
-            n = min(chunk, T - f0)
-            if mode == 2:
-                up = ws.get("tail_up", (chunk * h8 * w8, Fc * Wd))
-                L.bilinear_nhwc(v1[f0 * h4 * w4:], up, n, h4, w4, h8, w8, Fc, ldx=Fc * Wd, ldo=Fc * Wd, split_in=sp_f,
-                                split_out=sp_f)
-                o1 = ws.get("tail_o1", (chunk * h8 * w8, F2p * Wd))
-                L.conv3x3(up, w.w_oc1, self._ep(F2p, bias=w.b_oc1, out=o1), n, h8, w8, Fc * Wd, F2p)
-            else:
-                o1 = o1_all[f0 * h8 * w8:]
-            if fused:
-                # upsample + 3x3(->32) + ReLU + 1x1 + ReLU in one tcgen05 kernel (csrc/depth_tail.cu): the upsampled
-                # map (2.2 GB per vitl window) is built tile by tile in shared memory and never touches HBM
-                L.depth_tail(o1, w.w_oc2, w.b_oc2, w.w_last, w.b_last, depth[f0:], n, h8, w8, Ho, Wo, F2p)
-                continue
-            up2 = ws.get("out1_up", (chunk * Ho * Wo, F2p * Wd))
-            L.bilinear_nhwc(o1, up2, n, h8, w8, Ho, Wo, F2p, ldx=F2p * Wd, ldo=F2p * Wd, split_in=sp_2, split_out=sp_2)
-            L.conv3x3(up2, w.w_oc2, L.make_epilogue(bias=w.b_oc2, out_f32=depth[f0:], w2=w.w_last, b2=w.b_last,
-                                                    store_mode=L.ST_HEADDOT), n, Ho, Wo, F2p * Wd, 32)
+        v1 = self._fusion(1, ws, T, 4 * gh, 4 * gw, p2, r1, r1r, (8 * gh, 8 * gw))
+        h8, w8 = 8 * gh, 8 * gw
+        o1 = ws.get("out1", (T * h8 * w8, F2p * Wd))
+        L.conv3x3(v1, w.w_oc1, self._ep(F2p, bias=w.b_oc1, out=o1), T, h8, w8, Fc * Wd, F2p)
+        if fused:
+            L.depth_tail(o1, w.w_oc2, w.b_oc2, w.w_last, w.b_last, depth, T, h8, w8, Ho, Wo, F2p)
+        else:   # FP32-accuracy mode (split tensors) and upsampling ratios the fused kernel does not take
+            up2 = ws.get("out1_up", (T * Ho * Wo, F2p * Wd))
+            L.bilinear_nhwc(o1, up2, T, h8, w8, Ho, Wo, F2p, ldx=F2p * Wd, ldo=F2p * Wd, split_in=sp_2, split_out=sp_2)
+            L.conv3x3(up2, w.w_oc2, L.make_epilogue(bias=w.b_oc2, out_f32=depth, w2=w.w_last, b2=w.b_last,
+                                                    store_mode=L.ST_HEADDOT), T, Ho, Wo, F2p * Wd, 32)
         return depth
 
     # ------------------------------------------------------------------ whole window

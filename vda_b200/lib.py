@@ -200,10 +200,11 @@ def conv3x3(x, w, epi, n, H, W, Cin, Cout, ldx=None):
 
 
 def flash_attn(qk, vt, out, frames, S, heads, s_pad, flags=None):
-    """flags: int32 [frames*heads*ceil(S/128)] zeros (stays zero) -> optimistic softmax + fix-up pass; None -> exact."""
+    """Exact online softmax.  flags (int32 [frames*heads*ceil(S/128)] zeros) only matter to experiment builds of the
+    library (-DVDA_ATTN_EXPERIMENTS with VDA_ATTN_OPT=1: optimistic softmax + fix-up pass)."""
     with _timed("attn", 4.0 * frames * heads * S * S * 64):
         check(load().vda_flash_attn_fwd(ptr(qk), ptr(vt), ptr(out), frames, S, heads, s_pad, ptr(flags), stream_ptr()))
-    _launched(1 if flags is None else 2)
+    _launched(1)
 
 
 def depth_tail_supported(h, w, H, W, C):
