@@ -334,9 +334,11 @@ def video_extra(model, frames, world, rank, dist, torch, dev, mode, reps=1):
         dt_local = time.perf_counter() - t0
         tl = dict(model.last_timing)
         if world > 1:
-            t = torch.tensor([dt_local, dt_local - tl["seconds_to_last_forward"]], dtype=torch.float64, device=dev)
+            # tail = slowest rank's total minus the LAST forward of any rank (a rank that has no window in the last
+            # round would otherwise report that whole idle round as "after its last forward")
+            t = torch.tensor([dt_local, tl["seconds_to_last_forward"]], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            dt, tail = float(t[0]), float(t[1])
+            dt, tail = float(t[0]), max(float(t[0]) - float(t[1]), 0.0)
         else:
             dt, tail = dt_local, dt_local - tl["seconds_to_last_forward"]
         if rep > 0 and (best is None or dt < best):
@@ -348,7 +350,7 @@ def video_extra(model, frames, world, rank, dist, torch, dev, mode, reps=1):
            "windows": n_win, "rounds": timing["rounds"], "n_gpus": world,
            "result": {"sharded": "each rank keeps the frames of its own windows", "rank0": "rank 0 receives every frame"}[
                "sharded" if mode == "sharded" else "rank0"] if world > 1 else "single process",
-           "seconds_after_last_forward_max_over_ranks": timing["seconds_after_last_forward"],
+           "seconds_after_last_forward_of_any_rank": timing["seconds_after_last_forward"],
            "share_after_last_forward": timing["seconds_after_last_forward"] / best,
            "h2d_bytes": int(frames[0].nbytes) * 32 * timing["rounds"], "d2h_bytes": int(n) * frames.shape[1] * frames.shape[2] * 4}
     if rank == 0 and depth is not None and mode != "sharded":
