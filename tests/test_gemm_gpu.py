@@ -274,3 +274,76 @@ def test_gemm_throughput_report(L, capsys):
             print(f"\n[gemm] M={M} N={N} K={K}: {ms:.3f} ms = {2 * M * N * K / ms / 1e9:.0f} TFLOP/s "
                   f"(cuBLAS {ms_ref:.3f} ms = {2 * M * N * K / ms_ref / 1e9:.0f} TFLOP/s)")
         _close(out, a.float() @ w.float().T)
+
+
+def _guarded(rows, cols, fill=float("nan")):
+    """bf16 [rows, cols] view inside a buffer with sentinel bands on both sides (scattered stores must stay inside)."""
+    pad = 4096
+    buf = torch.full((pad + rows * cols + pad,), 7.0, device="cuda", dtype=torch.bfloat16)
+    view = buf[pad:pad + rows * cols].view(rows, cols)
+    view.fill_(fill)
+    return buf, view, pad
+
+
+def _guards_intact(buf, pad):
+    return bool((buf[:pad] == 7.0).all()) and bool((buf[-pad:] == 7.0).all())
+
+
+@pytest.mark.parametrize("M,N,K,pair", [(999, 256, 256, 0), (1370, 1024, 1024, 0), (130, 96, 192, 0), (5000, 64, 64, 0),
+                                        (700, 512, 128, 2), (43808, 256, 256, 0), (257, 32, 64, 1)])
+@pytest.mark.parametrize("combo", ["r1", "r2", "r1r2", "relu_only", "r1_relu", "r1r2_relu", "relu_no_out"])
+def test_gemm_cooperative_box_epilogue(L, M, N, K, pair, combo):
+    """bf16 residuals and / or a ReLU'd second output through the cooperative-box epilogue (MODE 5): every combination,
+    ragged M, N smaller than a tile, 1-CTA and CTA-pair kernels; outputs NaN-filled between sentinel bands."""
+    a = _rand(M, K, seed=1).bfloat16()
+    w = _rand(N, K, scale=K ** -0.5, seed=2).bfloat16()
+    b = _rand(N, seed=3)
+    r1 = _rand(M, N, seed=4).bfloat16() if "r1" in combo else None
+    r2 = _rand(M, N, seed=5).bfloat16() if "r2" in combo else None
+    want = a.float() @ w.float().T + b
+    if r1 is not None:
+        want = want + r1.float()
+    if r2 is not None:
+        want = want + r2.float()
+    bo, out, pad = _guarded(M, N)
+    br, out_relu, _ = _guarded(M, N)
+    use_out = combo != "relu_no_out"
+    use_relu = "relu" in combo
+    L.gemm(a, w, L.make_epilogue(bias=b, res1=r1, res2=r2, out=out if use_out else None,
+                                 out_relu=out_relu if use_relu else None, ldo=N, cta_pair=pair))
+    torch.cuda.synchronize()
+    if use_out:
+        _close(out, want)
+    if use_relu:
+        _close(out_relu, want.relu())
+    assert _guards_intact(bo, pad) and _guards_intact(br, pad)
+
+
+@pytest.mark.parametrize("n,H,W,C,Cout", [(2, 19, 19, 64, 64), (1, 37, 37, 128, 256), (2, 74, 74, 256, 256), (1, 5, 200, 192, 128),
+                                          (1, 148, 148, 64, 32)])
+@pytest.mark.parametrize("combo", ["r1r2_relu", "r2", "relu_only"])
+def test_conv3x3_cooperative_box_epilogue(L, n, H, W, C, Cout, combo):
+    """The FeatureFusion / ResidualConvUnit epilogues (util/blocks.py:78-91, 146-160) on maps whose sizes are not
+    multiples of the pixel tile, incl. the CTA-pair halo mode (Cout 128 / 256)."""
+    x = _rand(n, C, H, W, seed=1).bfloat16()
+    wt = _rand(Cout, C, 3, 3, scale=(9 * C) ** -0.5, seed=2).bfloat16()
+    b = _rand(Cout, seed=3)
+    r1 = _rand(n, H, W, Cout, seed=4).bfloat16() if "r1" in combo else None
+    r2 = _rand(n, H, W, Cout, seed=5).bfloat16() if "r2" in combo else None
+    want = F.conv2d(x.float(), wt.float(), b, padding=1).permute(0, 2, 3, 1)
+    if r1 is not None:
+        want = want + r1.float()
+    if r2 is not None:
+        want = want + r2.float()
+    xn = x.permute(0, 2, 3, 1).contiguous()
+    wk = wt.permute(0, 2, 3, 1).reshape(Cout, 9 * C).contiguous()
+    bo, out, pad = _guarded(n * H * W, Cout)
+    br, out_relu, _ = _guarded(n * H * W, Cout)
+    use_relu = "relu" in combo
+    L.conv3x3(xn, wk, L.make_epilogue(bias=b, res1=r1, res2=r2, out=out, out_relu=out_relu if use_relu else None, ldo=Cout),
+              n, H, W, C, Cout)
+    torch.cuda.synchronize()
+    _close(out.view(n, H, W, Cout), want)
+    if use_relu:
+        _close(out_relu.view(n, H, W, Cout), want.relu())
+    assert _guards_intact(bo, pad) and _guards_intact(br, pad)
