@@ -160,6 +160,35 @@ def test_forward_pipelined_matches_forward():
         assert g.is_pinned() and torch.allclose(g, w_, rtol=1e-4, atol=1e-6)
 
 
+@pytest.mark.parametrize("arch,T,H,W", [("vits", 4, 70, 98), ("vitl", 32, 518, 518)])
+def test_head_side_streams_match_serial_head(arch, T, H, W):
+    """The reassemble branches run on side streams inside the captured graph (engine.head): the result must be the
+    serial head's, replay after replay (a missing join would show up as a race).  Not bitwise: the tail split-K of the
+    large proj / fc2 launches adds its partial sums into the fp32 residual in an order that is not fixed, and 24 bf16
+    blocks amplify that (two replays of the SAME serial graph differ by up to ~1 % of the maximum at single pixels of a
+    random-init vitl window), so the yardstick is the serial graph's own replay-to-replay difference."""
+    model, _ = build(arch)
+    x = G.window_input(T, H, W, seed=3)[0].cuda()
+    eng = model.engine()
+
+    def mean_rel(u, v):
+        return float((u - v).abs().mean() / v.abs().mean())
+
+    with torch.no_grad():
+        eng.head_streams = 0
+        eng.graphs.clear()
+        want = [eng.forward(x).clone() for _ in range(3)]
+        noise = max(mean_rel(want[1], want[0]), mean_rel(want[2], want[0]))
+        eng.head_streams = 2
+        eng.graphs.clear()
+        for _ in range(4):
+            got = eng.forward(x).clone()
+            # a race (missing join) gives errors of the order of the signal; the budget is 5x the serial replay noise,
+            # at least 3e-3 (a third of the 1e-2 parity budget)
+            assert mean_rel(got, want[0]) <= max(5.0 * noise, 3e-3), (mean_rel(got, want[0]), noise)
+    eng.graphs.clear()
+
+
 @pytest.mark.parametrize("n_frames", [1, 5, 22, 23, 33, 55])
 def test_video_driver_ragged_lengths_vs_oracle(n_frames):
     """Edge cases of the window composition (video_depth.py:92-118): a single frame, clips shorter than one
