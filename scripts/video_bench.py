@@ -25,7 +25,7 @@ ap.add_argument("--width", type=int, default=518)
 ap.add_argument("--input-size", type=int, default=518)
 ap.add_argument("--metric", action="store_true")
 ap.add_argument("--reps", type=int, default=2)
-ap.add_argument("--result-rank", default="all", help="all: every rank returns the full result; 0: only rank 0 does; both: time one after the other")
+ap.add_argument("--result-rank", default="all", help="all: every rank returns the full result; 0: only rank 0 does; sharded: every rank keeps its own frames; both: all, then 0")
 a = ap.parse_args()
 
 world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -50,7 +50,10 @@ from vda_b200 import parallel
 
 modes = ["all", "0"] if a.result_rank == "both" else [a.result_rank]
 for mode in modes:
-    parallel.set_result_rank(None if mode == "all" else int(mode))
+    if mode == "sharded":
+        parallel.set_result_sharded()
+    else:
+        parallel.set_result_rank(None if mode == "all" else int(mode))
     times = []
     for rep in range(a.reps + 1):
         if world > 1:
@@ -62,6 +65,12 @@ for mode in modes:
         if world > 1:
             dist.barrier()
         times.append(time.perf_counter() - t0)
+        tr = model.last_timing.get("trace")
+        if tr is not None and rep == a.reps and rank in (0, world // 2, world - 1):   # VDA_VIDEO_TRACE=1: per-round times
+            for j, r in enumerate(tr):
+                print(f"trace mode={mode} rank {rank} round {j}: host " + " ".join(f"{k}={v:.1f}" for k, v in r["host_ms"].items())
+                      + " | device " + " ".join(f"{k}={v:.1f}" for k, v in r["device_ms"].items()), flush=True)
+            print(f"trace mode={mode} rank {rank} total {times[-1] * 1e3:.1f} ms, device {model.last_timing['seconds_device'] * 1e3:.1f} ms", flush=True)
     best = min(times[1:])
     if rank == 0:
         n_win = len(window_frame_indices(a.frames))

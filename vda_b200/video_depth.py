@@ -8,6 +8,7 @@ What differs is underneath: every window is a fixed launch sequence of libvda_b2
 GPU; the sequential scale/shift alignment and the cross-fade run as GPU kernels without host
 synchronisation; one device->host copy returns the result.
 """
+import os
 import time
 from concurrent.futures import ThreadPoolExecutor
 
@@ -286,25 +287,51 @@ class VideoDepthAnything(nn.Module):
             x, raws = bufs[1], bufs[2]
             scan = parallel.WindowScan(len(wins), h0, w0, GpuAlignOps(dev), self.metric)
             prev_k = None
+            trace = [] if os.environ.get("VDA_VIDEO_TRACE") == "1" else None   # per-round host / device times (ms)
             for j in range(timing["rounds"]):
                 k = j * world + rank
                 raw = None
+                h = [time.perf_counter()] if trace is not None else None
+                ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)] if trace is not None else None
+                if trace is not None:
+                    ev[0].record()
                 if k < len(wins):
                     feeder.fill(frames, wins[k], x, KEYFRAMES if prev_k is not None and prev_k == k - 1 else None)
                     prev_k = k
+                    if trace is not None:
+                        h.append(time.perf_counter())
+                        ev[1].record()
                     d = eng.forward(x)
                     raw = raws[j & 1]
                     L.bilinear_f32(d, raw, INFER_LEN, nh, nw, h0, w0)
                     e_last = torch.cuda.Event(enable_timing=True)
                     e_last.record()
+                elif trace is not None:
+                    h.append(time.perf_counter())
+                    ev[1].record()
+                if trace is not None:
+                    h.append(time.perf_counter())
+                    ev[2].record()
                 for lo, maps in scan.push(j, raw):
                     if sink is not None:
                         sink(lo, maps)
+                if trace is not None:
+                    h.append(time.perf_counter())
+                    ev[3].record()
                 if end_of_round is not None:
                     end_of_round()
+                if trace is not None:
+                    h.append(time.perf_counter())
+                    trace.append((h, ev))
             main.synchronize()
             timing["seconds_device"] = time.perf_counter() - t0
             timing["seconds_to_last_forward"] = e_begin.elapsed_time(e_last) * 1e-3
+            if trace is not None:
+                timing["trace"] = [{"host_ms": {"fill": (h[1] - h[0]) * 1e3, "forward_enqueue": (h[2] - h[1]) * 1e3,
+                                                "push_enqueue": (h[3] - h[2]) * 1e3, "end_of_round": (h[4] - h[3]) * 1e3},
+                                    "device_ms": {"since_begin": e_begin.elapsed_time(ev[0]), "fill": ev[0].elapsed_time(ev[1]),
+                                                  "forward": ev[1].elapsed_time(ev[2]), "push": ev[2].elapsed_time(ev[3])}}
+                                   for h, ev in trace]
         return scan
 
     def _downloader(self, dev, h0, w0, up, slots):
