@@ -388,7 +388,7 @@ _POOL = None
 def _copy_pool():
     global _POOL
     if _POOL is None:
-        _POOL = ThreadPoolExecutor(max_workers=HostDownloader.THREADS)
+        _POOL = ThreadPoolExecutor(max_workers=HostDownloader.MAX_THREADS)
     return _POOL
 
 
@@ -400,7 +400,8 @@ class HostDownloader:
     stream before the copy."""
 
     FRAMES = INFER_LEN
-    THREADS = 4
+    THREADS = 4          # host copy threads per drain; MAX_THREADS when this rank alone collects a multi-rank result
+    MAX_THREADS = 8
 
     def __init__(self, dev, h0, w0, up=None, slots=2):
         self.key = (str(dev), h0, w0, up, slots)
@@ -413,6 +414,8 @@ class HostDownloader:
 
     def begin(self, out):
         self.out = out
+        # one rank collecting every rank's frames drains world x more bytes per round while the other ranks' hosts idle
+        self.threads = self.MAX_THREADS if (parallel.active() and isinstance(parallel.result_mode(), int)) else self.THREADS
         self.pending = [None] * len(self.ring)
         self.turn = 0                         # pushes so far; push i uses slot i % len(ring)
         self.prev_start = self.round_start = 0  # pushes [round_start, turn) belong to the round being enqueued
@@ -423,9 +426,9 @@ class HostDownloader:
             ev.synchronize()
             src = self.ring[t].numpy()
             if m >= 8:      # numpy releases the GIL while copying: a few threads triple the host copy rate
-                cuts = [m * i // self.THREADS for i in range(self.THREADS + 1)]
+                cuts = [m * i // self.threads for i in range(self.threads + 1)]
                 list(_copy_pool().map(lambda i: self.out[lo + cuts[i]:lo + cuts[i + 1]].__setitem__(
-                    slice(None), src[cuts[i]:cuts[i + 1]]), range(self.THREADS)))
+                    slice(None), src[cuts[i]:cuts[i + 1]]), range(self.threads)))
             else:
                 self.out[lo:lo + m] = src[:m]
             self.pending[t] = None
