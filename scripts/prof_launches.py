@@ -7,10 +7,11 @@ from vda_b200.video_depth import MODEL_CONFIGS, randomize_zero_init_
 from video_depth_anything.video_depth import VideoDepthAnything
 
 arch = sys.argv[1] if len(sys.argv) > 1 else "vitl"
+fp32 = len(sys.argv) > 2 and sys.argv[2] == "fp32"   # FP32-accuracy mode (split-bf16 products)
 torch.manual_seed(0); torch.set_grad_enabled(False)
 m = randomize_zero_init_(VideoDepthAnything(**MODEL_CONFIGS[arch])).cuda().eval()
 x = torch.randn(32, 3, 518, 518, device="cuda")
-eng = m.engine()
+eng = m.engine(fp32)
 for _ in range(2): eng.forward(x)
 best = None
 for rep in range(3):

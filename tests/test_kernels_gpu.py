@@ -145,7 +145,8 @@ def test_layernorm_skip_cls_and_pe(L):
     _close(out, (base.view(T, hw, C) + pe[:T, None]).view(-1, C), 1e-2)
 
 
-@pytest.mark.parametrize("n,h,w,C", [(3, 19, 19, 1024), (2, 37, 37, 256), (4, 5, 7, 192), (2, 10, 10, 64)])
+@pytest.mark.parametrize("n,h,w,C", [(3, 19, 19, 1024), (2, 37, 37, 256), (4, 5, 7, 192), (2, 10, 10, 64), (2, 37, 37, 384), (3, 19, 19, 768),
+                                     (1, 74, 74, 128), (32, 37, 37, 1024)])
 def test_groupnorm_nhwc(L, n, h, w, C):
     x = (_rand(n, C, h, w, scale=2.0, seed=1) + 1.0).bfloat16()
     g, b = _rand(C, seed=2), _rand(C, seed=3)

@@ -126,35 +126,61 @@ __global__ void __launch_bounds__(256, VDA_LN_MINBLOCKS) layernorm_kernel(const 
 }
 
 // ------------------------------------------------------------------ GroupNorm (NHWC, 32 groups)
-// stats: one block per (image, row-chunk); thread t owns channel pair 2t; per-group partial sums
-// go through shared memory then one double atomicAdd per (group, block).
-__global__ void groupnorm_stats_kernel(const bf16* __restrict__ x, double* __restrict__ stats, int hw, int C, int ldx,
-                                       int rows_per_block, int split) {
+// stats: one block per (image, row chunk).  A thread owns 8 consecutive channels (one 16-byte load per row; the first
+// version read one bf16 pair per thread and row and hit shared-memory atomics once per row) of every rpp-th row of the
+// chunk, keeps its sums in registers, and only at the end adds them into the block's 64 partials (shared-memory atomics)
+// and the block adds those into the fp64 sums of the image (64 global atomics per block, ~4 blocks per SM in the grid).
+__global__ void __launch_bounds__(256) groupnorm_stats_kernel(const bf16* __restrict__ x, double* __restrict__ stats, int hw, int C,
+                                                              int ldx, int rows_per_block, int split) {
   __shared__ float sh[64];
   const int img = blockIdx.y;
   const int r0 = blockIdx.x * rows_per_block;
   const int r1 = min(hw, r0 + rows_per_block);
-  for (int i = threadIdx.x; i < 64; i += blockDim.x) sh[i] = 0.f;
+  if (threadIdx.x < 64) sh[threadIdx.x] = 0.f;
   __syncthreads();
+  const int c8 = C >> 3;                 // threads per row
+  const int rpp = 256 / c8;              // rows per pass of the block
+  const int tr = threadIdx.x / c8, c = (threadIdx.x - tr * c8) << 3;
   const int cg = C / 32;
-  for (int c = threadIdx.x * 2; c < C; c += blockDim.x * 2) {
-    float s = 0.f, ss = 0.f;
-    for (int r = r0; r < r1; ++r) {
-      const float2 t = ld_pair(x + (static_cast<long long>(img) * hw + r) * ldx + c, split);
-      s += t.x + t.y;
-      ss += t.x * t.x + t.y * t.y;
+  if (tr < rpp) {
+    float s[4] = {0.f, 0.f, 0.f, 0.f}, ss[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int r = r0 + tr; r < r1; r += rpp) {
+      const bf16* src = x + (static_cast<long long>(img) * hw + r) * ldx + c;
+      const uint4 hi = __ldg(reinterpret_cast<const uint4*>(src));
+      uint4 lo = make_uint4(0, 0, 0, 0);
+      if (split) lo = __ldg(reinterpret_cast<const uint4*>(src + split));
+      const uint32_t* ph = &hi.x;
+      const uint32_t* pl = &lo.x;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(ph + i));
+        if (split) {
+          const float2 l = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(pl + i));
+          t.x += l.x, t.y += l.y;
+        }
+        s[i] += t.x + t.y;
+        ss[i] += t.x * t.x + t.y * t.y;
+      }
     }
-    const int g = c / cg;
-    atomicAdd(&sh[2 * g], s);
-    atomicAdd(&sh[2 * g + 1], ss);
+    if (cg % 8 == 0) {   // the 8 channels lie in one group
+      const int g = c / cg;
+      atomicAdd(&sh[2 * g], (s[0] + s[1]) + (s[2] + s[3]));
+      atomicAdd(&sh[2 * g + 1], (ss[0] + ss[1]) + (ss[2] + ss[3]));
+    } else {         // cg is even (C % 64 == 0): a pair never straddles a group, an 8-channel chunk may (cg = 2, 4, 12, 24 ...)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int g = (c + 2 * i) / cg;
+        atomicAdd(&sh[2 * g], s[i]);
+        atomicAdd(&sh[2 * g + 1], ss[i]);
+      }
+    }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < 64; i += blockDim.x)
-    atomicAdd(&stats[static_cast<long long>(img) * 64 + i], static_cast<double>(sh[i]));
+  if (threadIdx.x < 64) atomicAdd(&stats[static_cast<long long>(img) * 64 + threadIdx.x], static_cast<double>(sh[threadIdx.x]));
 }
 
-// mean / rstd per (image, group) from the fp64 sums, once (the apply kernel used to redo the fp64
-// divisions per element pair, which made it 6x slower than its HBM time).
+// mean / rstd per (image, group) from the fp64 sums, once (redoing the fp64 divisions in the apply pass was measured
+// slower even at one pair of divisions per thread: gn74 81.8 -> 90.2 us).
 __global__ void groupnorm_finalize_kernel(const double* __restrict__ stats, float2* __restrict__ mr, int total, int hw,
                                           int C, float eps) {
   pdl_sync();  // launched with programmatic stream serialization (common.cuh)
@@ -166,40 +192,47 @@ __global__ void groupnorm_finalize_kernel(const double* __restrict__ stats, floa
   mr[i] = make_float2(static_cast<float>(mean), rsqrtf(static_cast<float>(var > 0 ? var : 0) + eps));
 }
 
-// One thread per (pixel, 8 channels): 16-byte loads and stores (8 channels never straddle a group: C/32 % 8 == 0
-// or C/32 in {2, 4} handled per pair).
-__global__ void groupnorm_apply_kernel(const bf16* __restrict__ x, const float2* __restrict__ mr,
-                                       const float* __restrict__ gamma, const float* __restrict__ beta,
-                                       bf16* __restrict__ out, int hw, int C, int ldx, long long total_oct, int split) {
+// One thread per (pixel, 8 channels): 16-byte loads and stores; mean / rstd are looked up per channel pair unless
+// C/32 % 8 == 0 (a pair never straddles a group, an 8-channel chunk may).  A block covers 256 / (C/8) consecutive pixels, so pixel and chunk come from two
+// small 32-bit divisions of threadIdx (the first version divided a 64-bit linear index twice per thread).
+__global__ void __launch_bounds__(256) groupnorm_apply_kernel(const bf16* __restrict__ x, const float2* __restrict__ mr,
+                                                              const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                              bf16* __restrict__ out, int hw, int C, int ldx, long long total_oct,
+                                                              int split) {
   pdl_sync();  // launched with programmatic stream serialization (common.cuh)
-  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (idx >= total_oct) return;
-  const int c8 = C >> 3;
-  const long long pix = idx / c8;
-  const int c = static_cast<int>(idx - pix * c8) << 3;
-  const int img = static_cast<int>(pix / hw);
+  const unsigned c8 = static_cast<unsigned>(C) >> 3;
+  const unsigned ppb = 256u / c8;                      // pixels per block
+  const unsigned tp = threadIdx.x / c8;
+  if (tp >= ppb) return;
+  const int c = static_cast<int>(threadIdx.x - tp * c8) << 3;
+  const long long pix = static_cast<long long>(blockIdx.x) * ppb + tp;
+  if (pix * c8 >= total_oct) return;
+  const int img = static_cast<int>(static_cast<unsigned>(pix) / static_cast<unsigned>(hw));   // pixels < 2^32
   const int cg = C / 32;
   const bf16* src = x + pix * ldx + c;
   bf16* dst = out + pix * (split ? 3 * C : C) + c;
   const uint4 hi = __ldg(reinterpret_cast<const uint4*>(src));
   uint4 lo = make_uint4(0, 0, 0, 0);
   if (split) lo = __ldg(reinterpret_cast<const uint4*>(src + split));
+  const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c + 4));
+  const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + c)), b1 = __ldg(reinterpret_cast<const float4*>(beta + c + 4));
+  const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+  const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
   const uint32_t* ph = &hi.x;
   const uint32_t* pl = &lo.x;
   float r[8];
+  float2 m = __ldg(mr + img * 32 + c / cg);
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     const int cc = c + 2 * i;
-    const float2 m = __ldg(mr + img * 32 + cc / cg);
+    if (cg % 8 != 0 && i > 0) m = __ldg(mr + img * 32 + cc / cg);   // a chunk may straddle groups (cg = 2, 4, 12, 24 ...)
     float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(ph + i));
     if (split) {
       const float2 l = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(pl + i));
       t.x += l.x, t.y += l.y;
     }
-    const float2 g = __ldg(reinterpret_cast<const float2*>(gamma + cc));
-    const float2 b = __ldg(reinterpret_cast<const float2*>(beta + cc));
-    r[2 * i] = (t.x - m.x) * m.y * g.x + b.x;
-    r[2 * i + 1] = (t.y - m.x) * m.y * g.y + b.y;
+    r[2 * i] = (t.x - m.x) * m.y * gg[2 * i] + bb[2 * i];
+    r[2 * i + 1] = (t.y - m.x) * m.y * gg[2 * i + 1] + bb[2 * i + 1];
   }
   if (split) {
 #pragma unroll
@@ -493,16 +526,22 @@ int vda_layernorm(const void* x, int x_is_f32, const float* gamma, const float* 
 
 int vda_groupnorm_nhwc(const void* x, int ldx, const float* gamma, const float* beta, void* out, double* stats_ws,
                        int n, int hw, int C, float eps, int split, void* stream) {
-  if (!x || !out || !stats_ws || C % 64 || n <= 0 || hw <= 0) return set_error(-1, "vda_groupnorm_nhwc: bad arguments (C%%64)");
+  if (!x || !out || !stats_ws || C % 64 || ldx % 8 || split % 8 || n <= 0 || hw <= 0)
+    return set_error(-1, "vda_groupnorm_nhwc: bad arguments (C%%64, ldx%%8)");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc = check_cuda(cudaMemsetAsync(stats_ws, 0, sizeof(double) * 64 * n, st), "groupnorm memset");
   if (rc) return rc;
-  const int rows_per_block = 32;
+  if (C > 2048) return set_error(-1, "vda_groupnorm_nhwc: C <= 2048");
+  // ~4 blocks per SM over the whole launch, at least one pass of rows per block
+  const int rpp = 256 / (C / 8);
+  int chunks = (4 * num_sms() + n - 1) / n;
+  if (chunks > (hw + rpp - 1) / rpp) chunks = (hw + rpp - 1) / rpp;
+  if (chunks < 1) chunks = 1;
+  const int rows_per_block = (hw + chunks - 1) / chunks;
   dim3 grid((hw + rows_per_block - 1) / rows_per_block, n);
-  const int threads = C / 2 < 512 ? C / 2 : 512;
-  groupnorm_stats_kernel<<<grid, threads, 0, st>>>(static_cast<const bf16*>(x), stats_ws, hw, C, ldx, rows_per_block, split);
-  // stats_ws: 64*n doubles of sums, reused in place for the 32*n float2 (mean, rstd) pairs behind them
-  float2* mr = reinterpret_cast<float2*>(stats_ws + 64 * n) ;
+  groupnorm_stats_kernel<<<grid, 256, 0, st>>>(static_cast<const bf16*>(x), stats_ws, hw, C, ldx, rows_per_block, split);
+  // stats_ws: 64*n doubles of sums, the 32*n float2 (mean, rstd) pairs behind them
+  float2* mr = reinterpret_cast<float2*>(stats_ws + 64 * n);
   rc = check_cuda(cudaGetLastError(), "groupnorm stats launch");  // plain launch: it follows a memset node
   if (rc) return rc;
   rc = check_cuda(launch_pdl(groupnorm_finalize_kernel, dim3((32 * n + 127) / 128), dim3(128), 0, st, stats_ws, mr, 32 * n, hw,
@@ -510,7 +549,9 @@ int vda_groupnorm_nhwc(const void* x, int ldx, const float* gamma, const float* 
                   "groupnorm finalize launch");
   if (rc) return rc;
   const long long total = static_cast<long long>(n) * hw * (C / 8);
-  return check_cuda(launch_pdl(groupnorm_apply_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), 0, st,
+  if (static_cast<long long>(n) * hw >= (1LL << 32)) return set_error(-1, "vda_groupnorm_nhwc: n * hw < 2^32");
+  const long long ppb = 256 / (C / 8);
+  return check_cuda(launch_pdl(groupnorm_apply_kernel, dim3(static_cast<unsigned>((static_cast<long long>(n) * hw + ppb - 1) / ppb)), dim3(256), 0, st,
                                static_cast<const bf16*>(x), mr, gamma, beta, static_cast<bf16*>(out), hw, C, ldx, total, split),
                     "groupnorm launch");
 }
