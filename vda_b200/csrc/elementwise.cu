@@ -128,16 +128,15 @@ __global__ void __launch_bounds__(256, VDA_LN_MINBLOCKS) layernorm_kernel(const 
 // ------------------------------------------------------------------ GroupNorm (NHWC, 32 groups)
 // stats: one block per (image, row chunk).  A thread owns 8 consecutive channels (one 16-byte load per row; the first
 // version read one bf16 pair per thread and row and hit shared-memory atomics once per row) of every rpp-th row of the
-// chunk, keeps its sums in registers, and only at the end adds them into the block's 64 partials (shared-memory atomics)
-// and the block adds those into the fp64 sums of the image (64 global atomics per block, ~4 blocks per SM in the grid).
+// chunk, keeps its sums in registers, and at the end the block reduces them in a FIXED order to its 64 partials, which go
+// into the fp64 sums of the image (64 global fp64 atomics per block, ~4 blocks per SM in the grid).
 __global__ void __launch_bounds__(256) groupnorm_stats_kernel(const bf16* __restrict__ x, double* __restrict__ stats, int hw, int C,
                                                               int ldx, int rows_per_block, int split) {
   __shared__ float sh[64];
+  __shared__ float part[256 * 8];        // per thread: (sum, sum of squares) of its 4 channel pairs
   const int img = blockIdx.y;
   const int r0 = blockIdx.x * rows_per_block;
   const int r1 = min(hw, r0 + rows_per_block);
-  if (threadIdx.x < 64) sh[threadIdx.x] = 0.f;
-  __syncthreads();
   const int c8 = C >> 3;                 // threads per row
   const int rpp = 256 / c8;              // rows per pass of the block
   const int tr = threadIdx.x / c8, c = (threadIdx.x - tr * c8) << 3;
@@ -162,18 +161,22 @@ __global__ void __launch_bounds__(256) groupnorm_stats_kernel(const bf16* __rest
         ss[i] += t.x * t.x + t.y * t.y;
       }
     }
-    if (cg % 8 == 0) {   // the 8 channels lie in one group
-      const int g = c / cg;
-      atomicAdd(&sh[2 * g], (s[0] + s[1]) + (s[2] + s[3]));
-      atomicAdd(&sh[2 * g + 1], (ss[0] + ss[1]) + (ss[2] + ss[3]));
-    } else {         // cg is even (C % 64 == 0): a pair never straddles a group, an 8-channel chunk may (cg = 2, 4, 12, 24 ...)
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int g = (c + 2 * i) / cg;
-        atomicAdd(&sh[2 * g], s[i]);
-        atomicAdd(&sh[2 * g + 1], ss[i]);
-      }
+    for (int i = 0; i < 4; ++i) {
+      part[(threadIdx.x * 4 + i) * 2] = s[i];
+      part[(threadIdx.x * 4 + i) * 2 + 1] = ss[i];
     }
+  }
+  __syncthreads();
+  // fixed-order reduction (shared-memory float atomics would make the sums, and through bf16 roundings the whole
+  // frame, differ from run to run): thread (g, k) adds the pair partials of group g over rows and pairs in order
+  if (threadIdx.x < 64) {
+    const int g = threadIdx.x >> 1, k = threadIdx.x & 1;
+    const int p0 = g * (cg >> 1), p1 = p0 + (cg >> 1);     // channel pairs of the group (cg is even)
+    float acc = 0.f;
+    for (int row = 0; row < rpp; ++row)
+      for (int pr = p0; pr < p1; ++pr) acc += part[((row * c8 + (pr >> 2)) * 4 + (pr & 3)) * 2 + k];
+    sh[threadIdx.x] = acc;
   }
   __syncthreads();
   if (threadIdx.x < 64) atomicAdd(&stats[static_cast<long long>(img) * 64 + threadIdx.x], static_cast<double>(sh[threadIdx.x]));
