@@ -219,10 +219,12 @@ def test_video_driver_original_size_upscale_vs_oracle():
     got, fps = model.infer_video_depth(frames, 24, input_size=v["input_size"], device="cuda", original_width=ow,
                                        original_height=oh)
     assert fps == 24 and got.shape == (9, oh, ow)
+    again, _ = model.infer_video_depth(frames, 24, input_size=v["input_size"], device="cuda")
+    noise = np.abs(again - base).max() / np.abs(base).max()      # 0 unless the order of an atomic sum moved a rounding
     want = O.upscale_to_original(base, oh, ow)
     err = np.abs(got - want).max() / np.abs(want).max()
-    print(f"original-size upscale: max rel err {err:.2e}")
-    assert err <= 2e-6
+    print(f"original-size upscale: max rel err {err:.2e} (run-to-run noise of the model {noise:.1e})")
+    assert err <= 2e-6 + 3 * noise
     # only one of the two given: ignored, like the reference
     same, _ = model.infer_video_depth(frames, 24, input_size=v["input_size"], device="cuda", original_width=ow)
     assert same.shape == base.shape
