@@ -50,12 +50,15 @@ template <typename TIn, int MAXV>
 __global__ void __launch_bounds__(256, VDA_LN_MINBLOCKS) layernorm_kernel(const TIn* __restrict__ x, const float* __restrict__ gamma,
                                  const float* __restrict__ beta, bf16* __restrict__ out, bf16* __restrict__ out_nope,
                                  const float* __restrict__ pe, int rows, int C, float eps, int S, int skip,
-                                 int pe_rows_per_t, int pe_T, int split) {
+                                 int pe_rows_per_t, int pe_T, int split, int reverse) {
   pdl_sync();  // launched with programmatic stream serialization (common.cuh)
   // each lane owns MAXV/2 groups of 4 consecutive channels: 16-byte fp32 loads, 8-byte bf16 stores
   constexpr int kQ = MAXV / 2;
   const int warps_per_block = blockDim.x >> 5;
-  const int row = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+  // reverse: last rows first.  The producer in front of a LayerNorm (a reduce-add GEMM walking its m-tiles upwards)
+  // leaves the LAST rows it wrote in L2; starting there reads them before they are evicted.
+  const int blk = reverse ? static_cast<int>(gridDim.x - 1 - blockIdx.x) : static_cast<int>(blockIdx.x);
+  const int row = blk * warps_per_block + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= rows) return;
   const int f = row / S, s = row - f * S;
@@ -476,11 +479,12 @@ static int launch_ln(const void* x, const float* gamma, const float* beta, void*
                      int rows, int C, float eps, int S, int skip, int pe_rows_per_t, int pe_T, int split, cudaStream_t st) {
   const int warps = 8;
   dim3 grid((rows + warps - 1) / warps), block(warps * 32);
+  static const int reverse = [] { const char* e = getenv("VDA_LN_REVERSE"); return e ? atoi(e) : 1; }();  // A/B knob (profiles/r02f_ab_VDA_LN_REVERSE.log)
   cudaError_t le = cudaSuccess;
 #define VDA_LN(MAXV)                                                                                              \
   le = launch_pdl(layernorm_kernel<TIn, MAXV>, grid, block, 0, st, static_cast<const TIn*>(x), gamma, beta,       \
                   static_cast<bf16*>(out), static_cast<bf16*>(out_nope), pe, rows, C, eps, S, skip, pe_rows_per_t, \
-                  pe_T, split ? C : 0)
+                  pe_T, split ? C : 0, reverse)
   if (C <= 256) VDA_LN(4);
   else if (C <= 512) VDA_LN(8);
   else if (C <= 1024) VDA_LN(16);
